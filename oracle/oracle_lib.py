@@ -1,0 +1,269 @@
+"""ctypes binding of oracle/libpf_oracle.so -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+``--impl reference`` legs may import this module (see pf_oracle.cpp header).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libpf_oracle.so")
+
+COV = {
+    "exponential": 0,
+    "gaussian": 1,
+    "spherical": 2,
+    "separableExponential": 3,
+    "matern32": 4,
+    "matern52": 5,
+    "dampedOscillation": 6,
+    "gammaExponential": 7,
+    "cauchy": 8,
+    "generalizedCauchy": 9,
+    "cubic": 10,
+    "whiteNoise": 11,
+}
+ANISO = {"none": 0, "axiparallel": 1, "geometric": 2}
+TRANSFORM = {"none": 0, "logNormal": 1, "foldedNormal": 2, "sign": 3, "boxCox": 4}
+
+
+class OrcCfg(C.Structure):
+    _fields_ = [
+        ("dim", C.c_int),
+        ("cells", C.c_uint * 3),
+        ("ext", C.c_double * 3),
+        ("factor", C.c_uint),
+        ("cov", C.c_int),
+        ("variance", C.c_double),
+        ("p0", C.c_double),
+        ("p1", C.c_double),
+        ("aniso", C.c_int),
+        ("corr", C.c_double * 9),
+        ("threshold", C.c_double),
+        ("approximate", C.c_int),
+        ("matrix_backend", C.c_int),
+        ("field_backend", C.c_int),
+        ("transposed", C.c_int),
+        ("cg_iterations", C.c_uint),
+        ("threads", C.c_int),
+    ]
+
+
+def build(force=False):
+    """Compile the oracle with the committed Makefile (gcc only)."""
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(
+        os.path.join(_HERE, "pf_oracle.cpp")
+    ):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = C.CDLL(_SO)
+        L.orc_last_error.restype = C.c_char_p
+        L.orc_lambda_size.restype = C.c_size_t
+        L.orc_noise_entries.restype = C.c_size_t
+        L.orc_lambda_size.argtypes = [C.POINTER(OrcCfg)]
+        L.orc_noise_entries.argtypes = [C.POINTER(OrcCfg)]
+        dp = C.POINTER(C.c_double)
+        L.orc_eigenvalues.argtypes = [C.POINTER(OrcCfg), dp, C.POINTER(C.c_int), dp, C.c_int]
+        L.orc_lambda_natural.argtypes = [C.POINTER(OrcCfg), dp, dp]
+        L.orc_generate_from_noise.argtypes = [C.POINTER(OrcCfg), dp, dp, dp, dp]
+        L.orc_reference_noise.argtypes = [C.c_uint, C.c_size_t, dp]
+        L.orc_generate_uncorrelated.argtypes = [C.c_uint, C.c_size_t, dp]
+        L.orc_multiply.argtypes = [C.POINTER(OrcCfg), dp, C.c_int, dp, dp]
+        L.orc_multiply_inverse.argtypes = [C.POINTER(OrcCfg), dp, dp, dp, C.POINTER(C.c_uint)]
+        L.orc_transform.argtypes = [C.c_int, C.c_double, C.c_size_t, dp]
+        L.orc_torus_covariance.argtypes = [C.POINTER(OrcCfg), dp]
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _check(rc):
+    if rc != 0:
+        raise RuntimeError(lib().orc_last_error().decode())
+
+
+class Oracle:
+    """One reference configuration (single rank).
+
+    Defaults follow the reference's backend selection
+    (matrix.hh:1668-1767, randomfield.hh:151-162): 1D -> DFT matrix + DFT
+    field backend; nD iso/axiparallel -> DCT matrix + R2C field; nD geometric
+    -> R2C matrix + R2C field; transposed layout only in 3D
+    (fieldtraits.hh:226-264).
+    """
+
+    def __init__(
+        self,
+        cells,
+        extensions=None,
+        covariance="exponential",
+        corr_length=0.05,
+        variance=1.0,
+        anisotropy="none",
+        factor=2,
+        threshold=1e-14,
+        approximate=False,
+        matrix_backend=None,
+        field_backend=None,
+        transposed=None,
+        cg_iterations=100,
+        threads=1,
+        p0=0.0,
+        p1=0.0,
+    ):
+        cells = list(cells)
+        dim = len(cells)
+        self.dim = dim
+        self.cells = cells
+        self.factor = factor
+        self.n = [factor * c for c in cells]
+        cfg = OrcCfg()
+        cfg.dim = dim
+        ext = list(extensions) if extensions is not None else [1.0] * dim
+        for i in range(dim):
+            cfg.cells[i] = cells[i]
+            cfg.ext[i] = ext[i]
+        cfg.factor = factor
+        cfg.cov = COV[covariance]
+        cfg.variance = variance
+        cfg.p0, cfg.p1 = p0, p1
+        cfg.aniso = ANISO[anisotropy]
+        cl = np.atleast_1d(np.asarray(corr_length, dtype=np.float64)).ravel()
+        need = {0: 1, 1: dim, 2: dim * dim}[cfg.aniso]
+        if cl.size != need:
+            raise ValueError("corrLength arity %d, expected %d" % (cl.size, need))
+        for i in range(cl.size):
+            cfg.corr[i] = cl[i]
+        cfg.threshold = threshold
+        cfg.approximate = int(approximate)
+        if matrix_backend is None:
+            matrix_backend = "DFT" if dim == 1 else ("R2C" if anisotropy == "geometric" else "DCT")
+        if field_backend is None:
+            field_backend = "DFT" if dim == 1 else "R2C"
+        cfg.matrix_backend = {"DCT": 0, "R2C": 1, "DFT": 2}[matrix_backend]
+        cfg.field_backend = {"R2C": 0, "DFT": 1}[field_backend]
+        cfg.transposed = int(dim == 3) if transposed is None else int(transposed)
+        cfg.cg_iterations = cg_iterations
+        cfg.threads = threads
+        self.cfg = cfg
+        self.matrix_backend = matrix_backend
+        self.field_backend = field_backend
+        self._lambda = None
+        self.stats = None
+
+    # -- sizes -----------------------------------------------------------
+    @property
+    def domain_size(self):
+        return int(np.prod(self.cells))
+
+    @property
+    def noise_entries(self):
+        return int(lib().orc_noise_entries(C.byref(self.cfg)))
+
+    @property
+    def lambda_size(self):
+        return int(lib().orc_lambda_size(C.byref(self.cfg)))
+
+    # -- eigenvalues ------------------------------------------------------
+    def eigenvalues(self, census_quirk=False):
+        lam = np.empty(self.lambda_size, dtype=np.float64)
+        counts = (C.c_int * 3)()
+        smallest = C.c_double()
+        rc = lib().orc_eigenvalues(
+            C.byref(self.cfg), _dp(lam), counts, C.byref(smallest), int(census_quirk)
+        )
+        self.stats = dict(small=counts[0], zero=counts[1], negative=counts[2], smallest=smallest.value)
+        _check(rc)
+        self._lambda = lam
+        return lam
+
+    def lambda_stored(self):
+        if self._lambda is None:
+            self.eigenvalues()
+        return self._lambda
+
+    def lambda_natural(self):
+        """lambda on the field backend's index set in natural (k0,k1,k2) order."""
+        lam = self.lambda_stored()
+        n = self.n + [1] * (3 - self.dim)
+        b0 = n[0] if self.field_backend == "DFT" else n[0] // 2 + 1
+        out = np.empty(b0 * n[1] * n[2], dtype=np.float64)
+        _check(lib().orc_lambda_natural(C.byref(self.cfg), _dp(lam), _dp(out)))
+        return out.reshape(n[2], n[1], b0)
+
+    def torus_covariance(self):
+        n = self.n + [1] * (3 - self.dim)
+        out = np.empty(n[0] * n[1] * n[2], dtype=np.float64)
+        _check(lib().orc_torus_covariance(C.byref(self.cfg), _dp(out)))
+        return out.reshape(n[2], n[1], n[0])
+
+    # -- generate ----------------------------------------------------------
+    def reference_noise(self, seed):
+        noise = np.empty(2 * self.noise_entries, dtype=np.float64)
+        _check(lib().orc_reference_noise(C.c_uint(seed), self.noise_entries, _dp(noise)))
+        return noise
+
+    def generate_from_noise(self, noise, want_spare=False):
+        lam = self.lambda_stored()
+        noise = np.ascontiguousarray(noise, dtype=np.float64)
+        assert noise.size == 2 * self.noise_entries
+        out = np.empty(self.domain_size, dtype=np.float64)
+        spare = np.empty(self.domain_size, dtype=np.float64) if want_spare else None
+        _check(
+            lib().orc_generate_from_noise(
+                C.byref(self.cfg), _dp(lam), _dp(noise), _dp(out), _dp(spare) if want_spare else None
+            )
+        )
+        shape = tuple(reversed(self.cells))
+        if want_spare:
+            return out.reshape(shape), spare.reshape(shape)
+        return out.reshape(shape)
+
+    def generate(self, seed, want_spare=False):
+        return self.generate_from_noise(self.reference_noise(seed), want_spare)
+
+    # -- operators ----------------------------------------------------------
+    def multiply(self, x, op="matrix"):
+        lam = self.lambda_stored()
+        x = np.ascontiguousarray(x, dtype=np.float64).ravel()
+        out = np.empty_like(x)
+        opi = {"matrix": 0, "root": 1, "inverse_ext": 2}[op]
+        _check(lib().orc_multiply(C.byref(self.cfg), _dp(lam), opi, _dp(x), _dp(out)))
+        return out.reshape(tuple(reversed(self.cells)))
+
+    def multiply_inverse(self, x):
+        lam = self.lambda_stored()
+        x = np.ascontiguousarray(x, dtype=np.float64).ravel()
+        out = np.empty_like(x)
+        it = C.c_uint()
+        _check(lib().orc_multiply_inverse(C.byref(self.cfg), _dp(lam), _dp(x), _dp(out), C.byref(it)))
+        self.cg_iterations_used = it.value
+        return out.reshape(tuple(reversed(self.cells)))
+
+
+def generate_uncorrelated(seed, n):
+    out = np.empty(n, dtype=np.float64)
+    _check(lib().orc_generate_uncorrelated(C.c_uint(seed), n, _dp(out)))
+    return out
+
+
+def transform(kind, values, boxcox_lambda=0.0):
+    v = np.array(values, dtype=np.float64).ravel().copy()
+    _check(lib().orc_transform(TRANSFORM[kind], boxcox_lambda, v.size, _dp(v)))
+    return v.reshape(np.shape(values))
