@@ -1,0 +1,445 @@
+"""dune-parafields_b200 -- B200-native circulant-embedding sampler.
+
+Python plumbing over the C ABI of ``csrc/libparafields_cuda.so``
+(``include/parafields_cuda.h``).  The product is the CUDA library and the
+C++17 headers under ``include/``; this module exists for the tests, the
+benchmark and ``torch.distributed`` launches.  It never falls back to a CPU
+implementation: if the shared library is missing or no CUDA device is
+present, calls raise.
+
+The package directory name contains a hyphen (it is the reference's project
+name), so import it with::
+
+    import importlib
+    pfb = importlib.import_module("dune-parafields_b200")
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "libparafields_cuda.so")
+INCLUDE_DIR = os.path.join(os.path.dirname(_HERE), "include")
+
+COVARIANCE = {
+    "exponential": 0,
+    "gaussian": 1,
+    "spherical": 2,
+    "separableExponential": 3,
+    "matern32": 4,
+    "matern52": 5,
+    "dampedOscillation": 6,
+    "gammaExponential": 7,
+    "cauchy": 8,
+    "generalizedCauchy": 9,
+    "cubic": 10,
+    "whiteNoise": 11,
+}
+ANISOTROPY = {"none": 0, "axiparallel": 1, "geometric": 2}
+TRANSFORM = {"none": 0, "logNormal": 1, "foldedNormal": 2, "sign": 3, "boxCox": 4}
+OP = {"matrix": 0, "root": 1, "inverse_ext": 2}
+LAMBDA_NATURAL, LAMBDA_REFERENCE = 0, 1
+
+PF_OK, PF_ERR_INVALID, PF_ERR_NEGATIVE_EIGENVALUES, PF_ERR_CUDA, PF_ERR_NOMEM = range(5)
+
+# every entry point declared in include/parafields_cuda.h
+ABI_SYMBOLS = [
+    "pf_version",
+    "pf_last_error",
+    "pf_device_count",
+    "pf_device_info",
+    "pf_desc_default",
+    "pf_plan_create",
+    "pf_plan_destroy",
+    "pf_plan_set_stream",
+    "pf_plan_synchronize",
+    "pf_plan_launch_count",
+    "pf_domain_size",
+    "pf_extended_size",
+    "pf_noise_entries",
+    "pf_compute_eigenvalues",
+    "pf_eigenvalue_count",
+    "pf_get_eigenvalues",
+    "pf_generate",
+    "pf_generate_batch",
+    "pf_generate_from_noise",
+    "pf_generate_uncorrelated",
+    "pf_set_variance_as_field",
+    "pf_apply",
+    "pf_solve",
+    "pf_transform",
+    "pf_vec_axpy",
+    "pf_vec_scale",
+    "pf_vec_dot",
+    "pf_vec_norm1",
+    "pf_vec_norminf",
+    "pf_device_alloc",
+    "pf_device_free",
+    "pf_memcpy",
+]
+
+
+class PfDesc(C.Structure):
+    _fields_ = [
+        ("dim", C.c_int),
+        ("cells", C.c_uint * 3),
+        ("extensions", C.c_double * 3),
+        ("embedding_factor", C.c_uint),
+        ("covariance", C.c_int),
+        ("variance", C.c_double),
+        ("cov_param", C.c_double * 2),
+        ("anisotropy", C.c_int),
+        ("corr_length", C.c_double * 9),
+        ("threshold", C.c_double),
+        ("approximate", C.c_int),
+        ("periodic", C.c_int),
+        ("transform", C.c_int),
+        ("boxcox_lambda", C.c_double),
+        ("cg_iterations", C.c_uint),
+        ("parity_mode", C.c_int),
+        ("rng_mode", C.c_int),
+        ("census_quirk", C.c_int),
+        ("max_factor", C.c_uint),
+        ("device", C.c_int),
+    ]
+
+
+class PfEigStats(C.Structure):
+    _fields_ = [
+        ("small_count", C.c_ulonglong),
+        ("zero_count", C.c_ulonglong),
+        ("negative_count", C.c_ulonglong),
+        ("smallest", C.c_double),
+        ("factor_used", C.c_uint),
+    ]
+
+
+class PfError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+def build(verbose=False):
+    """Compile csrc/ into libparafields_cuda.so (nvcc, sm_100a, -lineinfo)."""
+    jobs = str(max(1, min(10, os.cpu_count() or 1)))
+    cmd = ["make", "-C", CSRC, "-j", jobs]
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if verbose or out.returncode != 0:
+        print(out.stdout)
+    if out.returncode != 0:
+        raise RuntimeError("building libparafields_cuda.so failed")
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library; fail loudly if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "%s not found: build it with `make -C %s` (nvcc, sm_100a). "
+            "There is no CPU fallback." % (LIB_PATH, CSRC)
+        )
+    L = C.CDLL(LIB_PATH)
+    vp, dp, sz = C.c_void_p, C.c_void_p, C.c_size_t
+    L.pf_version.restype = C.c_char_p
+    L.pf_last_error.restype = C.c_char_p
+    L.pf_device_info.argtypes = [C.c_int, C.c_char_p, C.POINTER(C.c_int), C.POINTER(sz)]
+    L.pf_desc_default.argtypes = [C.POINTER(PfDesc)]
+    L.pf_desc_default.restype = None
+    L.pf_plan_create.argtypes = [C.POINTER(PfDesc), C.POINTER(vp)]
+    L.pf_plan_destroy.argtypes = [vp]
+    L.pf_plan_set_stream.argtypes = [vp, vp]
+    L.pf_plan_synchronize.argtypes = [vp]
+    L.pf_plan_launch_count.argtypes = [vp]
+    L.pf_plan_launch_count.restype = C.c_ulonglong
+    for f in (L.pf_domain_size, L.pf_extended_size, L.pf_noise_entries):
+        f.argtypes = [vp]
+        f.restype = sz
+    L.pf_compute_eigenvalues.argtypes = [vp, C.POINTER(PfEigStats)]
+    L.pf_eigenvalue_count.argtypes = [vp, C.c_int]
+    L.pf_eigenvalue_count.restype = sz
+    L.pf_get_eigenvalues.argtypes = [vp, dp, sz, C.c_int]
+    L.pf_generate.argtypes = [vp, C.c_uint64, C.c_uint64, dp, C.c_int]
+    L.pf_generate_batch.argtypes = [vp, C.c_uint64, C.c_uint64, sz, dp, C.c_int]
+    L.pf_generate_from_noise.argtypes = [vp, dp, dp, dp]
+    L.pf_generate_uncorrelated.argtypes = [vp, C.c_uint64, dp]
+    L.pf_set_variance_as_field.argtypes = [vp, dp]
+    L.pf_apply.argtypes = [vp, C.c_int, dp, dp]
+    L.pf_solve.argtypes = [vp, dp, dp, C.POINTER(C.c_uint)]
+    L.pf_transform.argtypes = [vp, dp, dp, sz]
+    L.pf_vec_axpy.argtypes = [vp, sz, C.c_double, dp, dp]
+    L.pf_vec_scale.argtypes = [vp, sz, C.c_double, dp]
+    L.pf_vec_dot.argtypes = [vp, sz, dp, dp, C.POINTER(C.c_double)]
+    L.pf_vec_norm1.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
+    L.pf_vec_norminf.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
+    L.pf_device_alloc.argtypes = [vp, sz, C.POINTER(vp)]
+    L.pf_device_free.argtypes = [vp, vp]
+    L.pf_memcpy.argtypes = [vp, vp, vp, sz]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise PfError(rc, lib().pf_last_error().decode())
+
+
+def _ptr(a):
+    """Address of a numpy array, a torch tensor (host or CUDA) or a raw int."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):  # torch tensor
+        assert a.is_contiguous()
+        return a.data_ptr()
+    raise TypeError("unsupported buffer type %r" % type(a))
+
+
+def make_desc(
+    cells,
+    extensions=None,
+    covariance="exponential",
+    corr_length=0.05,
+    variance=1.0,
+    anisotropy="none",
+    factor=2,
+    threshold=1e-14,
+    approximate=False,
+    periodic=False,
+    transform="none",
+    boxcox_lambda=0.0,
+    cg_iterations=100,
+    parity_mode="reference",
+    rng_mode="fast",
+    census_quirk=False,
+    max_factor=0,
+    device=-1,
+    cov_param=(0.0, 0.0),
+):
+    d = PfDesc()
+    lib().pf_desc_default(C.byref(d))
+    cells = list(cells)
+    dim = len(cells)
+    d.dim = dim
+    ext = list(extensions) if extensions is not None else [1.0] * dim
+    for i in range(dim):
+        d.cells[i] = int(cells[i])
+        d.extensions[i] = float(ext[i])
+    d.embedding_factor = factor
+    d.covariance = COVARIANCE[covariance]
+    d.variance = variance
+    d.cov_param[0], d.cov_param[1] = cov_param
+    d.anisotropy = ANISOTROPY[anisotropy]
+    cl = np.atleast_1d(np.asarray(corr_length, dtype=np.float64)).ravel()
+    need = {0: 1, 1: dim, 2: dim * dim}[d.anisotropy]
+    if cl.size != need:
+        raise ValueError("stochastic.corrLength needs %d values for anisotropy %s" % (need, anisotropy))
+    for i in range(cl.size):
+        d.corr_length[i] = cl[i]
+    d.threshold = threshold
+    d.approximate = int(approximate)
+    d.periodic = int(periodic)
+    d.transform = TRANSFORM[transform]
+    d.boxcox_lambda = boxcox_lambda
+    d.cg_iterations = cg_iterations
+    d.parity_mode = {"reference": 0, "corrected": 1}[parity_mode]
+    d.rng_mode = {"fast": 0, "fp64": 1}[rng_mode]
+    d.census_quirk = int(census_quirk)
+    d.max_factor = max_factor
+    d.device = device
+    return d
+
+
+class Plan:
+    """Owner of one pf_plan (the CUDA counterpart of parafields::Matrix)."""
+
+    def __init__(self, cells, **kw):
+        self.cells = list(cells)
+        self.dim = len(self.cells)
+        self.desc = make_desc(cells, **kw)
+        self._h = C.c_void_p()
+        _check(lib().pf_plan_create(C.byref(self.desc), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().pf_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- plumbing ---------------------------------------------------------
+    def set_stream(self, stream):
+        """stream: torch.cuda.Stream, raw cudaStream_t int, or None."""
+        h = 0 if stream is None else getattr(stream, "cuda_stream", stream)
+        _check(lib().pf_plan_set_stream(self._h, C.c_void_p(h)))
+
+    def synchronize(self):
+        _check(lib().pf_plan_synchronize(self._h))
+
+    @property
+    def launch_count(self):
+        return int(lib().pf_plan_launch_count(self._h))
+
+    @property
+    def domain_size(self):
+        return int(lib().pf_domain_size(self._h))
+
+    @property
+    def extended_size(self):
+        return int(lib().pf_extended_size(self._h))
+
+    @property
+    def noise_entries(self):
+        return int(lib().pf_noise_entries(self._h))
+
+    @property
+    def shape(self):
+        return tuple(reversed(self.cells))
+
+    # -- eigenvalues ---------------------------------------------------------
+    def compute_eigenvalues(self):
+        st = PfEigStats()
+        rc = lib().pf_compute_eigenvalues(self._h, C.byref(st))
+        self.stats = dict(
+            small=int(st.small_count),
+            zero=int(st.zero_count),
+            negative=int(st.negative_count),
+            smallest=float(st.smallest),
+            factor_used=int(st.factor_used),
+        )
+        _check(rc)
+        return self.stats
+
+    def eigenvalues(self, layout=LAMBDA_NATURAL):
+        n = int(lib().pf_eigenvalue_count(self._h, layout))
+        out = np.empty(n, dtype=np.float64)
+        _check(lib().pf_get_eigenvalues(self._h, _ptr(out), n, layout))
+        return out
+
+    # -- sampling ------------------------------------------------------------
+    def generate(self, seed, realization=0, out=None, apply_transform=False):
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float64)
+        _check(lib().pf_generate(self._h, seed, realization, _ptr(out), int(apply_transform)))
+        return out
+
+    def generate_batch(self, seed, first, count, out=None, apply_transform=False):
+        if out is None:
+            out = np.empty((count,) + self.shape, dtype=np.float64)
+        _check(lib().pf_generate_batch(self._h, seed, first, count, _ptr(out), int(apply_transform)))
+        return out
+
+    def generate_from_noise(self, noise, out=None, spare=None):
+        if isinstance(noise, np.ndarray):
+            noise = np.ascontiguousarray(noise, dtype=np.float64)
+            assert noise.size == 2 * self.noise_entries
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float64)
+        _check(lib().pf_generate_from_noise(self._h, _ptr(noise), _ptr(out), _ptr(spare)))
+        return out
+
+    def generate_uncorrelated(self, seed, out=None):
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float64)
+        _check(lib().pf_generate_uncorrelated(self._h, seed, _ptr(out)))
+        return out
+
+    def variance_field(self, out=None):
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float64)
+        _check(lib().pf_set_variance_as_field(self._h, _ptr(out)))
+        return out
+
+    # -- operators -------------------------------------------------------------
+    def apply(self, op, x, out=None):
+        if isinstance(x, np.ndarray):
+            x = np.ascontiguousarray(x, dtype=np.float64)
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float64)
+        _check(lib().pf_apply(self._h, OP[op], _ptr(x), _ptr(out)))
+        return out
+
+    def solve(self, b, out=None):
+        if isinstance(b, np.ndarray):
+            b = np.ascontiguousarray(b, dtype=np.float64)
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float64)
+        it = C.c_uint()
+        _check(lib().pf_solve(self._h, _ptr(b), _ptr(out), C.byref(it)))
+        self.cg_iterations_used = it.value
+        return out
+
+    def transform(self, x, out=None):
+        if isinstance(x, np.ndarray):
+            x = np.ascontiguousarray(x, dtype=np.float64)
+            n = x.size
+            if out is None:
+                out = np.empty_like(x)
+        else:
+            n = x.numel()
+        _check(lib().pf_transform(self._h, _ptr(x), _ptr(out), n))
+        return out
+
+    # -- vector space -----------------------------------------------------------
+    def axpy(self, alpha, x, y):
+        n = x.size if isinstance(x, np.ndarray) else x.numel()
+        _check(lib().pf_vec_axpy(self._h, n, alpha, _ptr(x), _ptr(y)))
+        return y
+
+    def scale(self, alpha, x):
+        n = x.size if isinstance(x, np.ndarray) else x.numel()
+        _check(lib().pf_vec_scale(self._h, n, alpha, _ptr(x)))
+        return x
+
+    def _red(self, fn, x, y=None):
+        n = x.size if isinstance(x, np.ndarray) else x.numel()
+        r = C.c_double()
+        if y is None:
+            _check(fn(self._h, n, _ptr(x), C.byref(r)))
+        else:
+            _check(fn(self._h, n, _ptr(x), _ptr(y), C.byref(r)))
+        return r.value
+
+    def dot(self, x, y):
+        return self._red(lib().pf_vec_dot, x, y)
+
+    def norm1(self, x):
+        return self._red(lib().pf_vec_norm1, x)
+
+    def norminf(self, x):
+        return self._red(lib().pf_vec_norminf, x)
+
+
+def device_count():
+    return int(lib().pf_device_count())
+
+
+def device_info(device=0):
+    name = C.create_string_buffer(256)
+    sm = C.c_int()
+    mem = C.c_size_t()
+    _check(lib().pf_device_info(device, name, C.byref(sm), C.byref(mem)))
+    return dict(name=name.value.decode(), sm_count=sm.value, mem_bytes=mem.value)

@@ -1,0 +1,1674 @@
+// pf_api.cu -- plan object, pass orchestration and the C ABI of
+// libparafields_cuda.so (include/parafields_cuda.h).
+//
+// Host-side counterpart of parafields::Matrix (matrix.hh:59-1663): it owns the
+// eigenvalue tables and work buffers in HBM and strings the pass kernels of
+// pf_kernels.cuh together.  No CPU fallback exists: every compute entry point
+// needs a CUDA device.
+#include "../../include/parafields_cuda.h"
+#include "pf_args.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+using pf::PassArgs;
+typedef double2 cplx;
+
+// launchers instantiated per line length in pf_inst.cu
+#define PF_DECL(n)                                                             \
+  extern "C" int pf_launch_n##n(int, const PassArgs*, const void*, cudaStream_t);
+PF_DECL(2)
+PF_DECL(4)
+PF_DECL(8)
+PF_DECL(16)
+PF_DECL(32)
+PF_DECL(64)
+PF_DECL(128)
+PF_DECL(256)
+PF_DECL(512)
+PF_DECL(1024)
+
+namespace {
+
+thread_local std::string g_err;
+
+int
+fail(int code, const std::string& msg)
+{
+  g_err = msg;
+  return code;
+}
+
+#define PF_CUDA(call)                                                          \
+  do {                                                                         \
+    cudaError_t e__ = (call);                                                  \
+    if (e__ != cudaSuccess)                                                    \
+      return fail(PF_ERR_CUDA, std::string(#call) + ": " +                     \
+                                 cudaGetErrorString(e__));                     \
+  } while (0)
+
+#define PF_TRY(call)                                                           \
+  do {                                                                         \
+    int rc__ = (call);                                                         \
+    if (rc__ != 0)                                                             \
+      return rc__;                                                             \
+  } while (0)
+
+typedef int (*launch_fn)(int, const PassArgs*, const void*, cudaStream_t);
+
+launch_fn
+launcher_for(long long n)
+{
+  switch (n) {
+    case 2:
+      return pf_launch_n2;
+    case 4:
+      return pf_launch_n4;
+    case 8:
+      return pf_launch_n8;
+    case 16:
+      return pf_launch_n16;
+    case 32:
+      return pf_launch_n32;
+    case 64:
+      return pf_launch_n64;
+    case 128:
+      return pf_launch_n128;
+    case 256:
+      return pf_launch_n256;
+    case 512:
+      return pf_launch_n512;
+    case 1024:
+      return pf_launch_n1024;
+  }
+  return nullptr;
+}
+
+bool
+is_device_ptr(const void* p)
+{
+  if (!p)
+    return false;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+// ---------------------------------------------------------------------------
+// small elementwise / reduction kernels
+// ---------------------------------------------------------------------------
+__global__ void
+k_derive_table(const double* __restrict__ lam, double* __restrict__ out,
+               size_t n, int mode)
+{
+  // mode 0: sqrt(l)/sqrt(2)   1: sqrt(l)   2: 1/l
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  const double l = lam[i];
+  double r;
+  if (mode == 0)
+    r = sqrt(l) / sqrt(2.);
+  else if (mode == 1)
+    r = sqrt(l);
+  else
+    r = 1. / l;
+  out[i] = r;
+}
+
+struct GatherArgs
+{
+  int dim;
+  long long n[3];       // extended cells
+  long long ob[3];      // output bounds
+  int transposed;       // output order k0,(k2,k1) instead of k0,(k1,k2)
+  int compact;          // table mirrors a / e
+  long long m0, P;      // table geometry
+};
+
+// eigenvalue table -> user layout (PF_LAMBDA_NATURAL / PF_LAMBDA_REFERENCE)
+__global__ void
+k_gather_lambda(const double* __restrict__ lam, double* __restrict__ out,
+                GatherArgs g, size_t total)
+{
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total)
+    return;
+  long long k[3] = { 0, 0, 0 };
+  size_t r = i;
+  if (g.dim == 3 && g.transposed) {
+    k[0] = r % g.ob[0];
+    r /= g.ob[0];
+    k[2] = r % g.ob[2];
+    r /= g.ob[2];
+    k[1] = r;
+  } else {
+    for (int d = 0; d < g.dim; d++) {
+      k[d] = r % g.ob[d];
+      r /= g.ob[d];
+    }
+  }
+  // mirror into the stored range
+  long long km[3];
+  for (int d = 0; d < 3; d++)
+    km[d] = (g.compact && k[d] > g.n[d] / 2) ? g.n[d] - k[d] : k[d];
+  double v;
+  if (g.dim == 3)
+    v = lam[(km[1] * g.m0 + k[0]) * g.P + km[2]];
+  else if (g.dim == 2)
+    v = lam[k[0] * g.P + km[1]];
+  else
+    v = lam[k[0]];
+  out[i] = v;
+}
+
+__global__ void
+k_axpy(size_t n, double alpha, const double* __restrict__ x,
+       double* __restrict__ y)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    y[i] += alpha * x[i];
+}
+__global__ void
+k_scale(size_t n, double alpha, double* __restrict__ x)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    x[i] *= alpha;
+}
+__global__ void
+k_fill(size_t n, double v, double* __restrict__ x)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    x[i] = v;
+}
+// r = b - Mx
+__global__ void
+k_residual(size_t n, const double* __restrict__ b, const double* __restrict__ Mx,
+           double* __restrict__ r)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    r[i] = b[i] - Mx[i];
+}
+// d = z + beta d
+__global__ void
+k_direction(size_t n, double beta, const double* __restrict__ z,
+            double* __restrict__ d)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    d[i] = z[i] + beta * d[i];
+}
+__global__ void
+k_transform(size_t n, const double* __restrict__ in, double* __restrict__ out,
+            int kind, double lambda)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    double v = in[i];
+    switch (kind) {
+      case 1:
+        v = exp(v);
+        break;
+      case 2:
+        v = fabs(v);
+        break;
+      case 3:
+        v = v < 0. ? -1. : 1.;
+        break;
+      case 4:
+        v = pow(v * lambda + 1, -lambda);
+        break;
+    }
+    out[i] = v;
+  }
+}
+
+// reductions: mode 0 dot(x,y), 1 sum|x|, 2 max|x|, 3 sum x*(0.5*y - z),
+// 4 max|x| > 1e-10 flag (as max)
+constexpr int RED_BLOCKS = 592; // 4 per SM
+constexpr int RED_THREADS = 256;
+
+__device__ __forceinline__ double
+red_combine(double a, double b, int mode)
+{
+  return (mode == 2) ? fmax(a, b) : a + b;
+}
+
+__global__ void
+k_reduce1(size_t n, const double* __restrict__ x, const double* __restrict__ y,
+          const double* __restrict__ z, int mode, double* __restrict__ partial)
+{
+  double acc = 0.;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    double t;
+    if (mode == 0)
+      t = x[i] * y[i];
+    else if (mode == 1)
+      t = fabs(x[i]);
+    else if (mode == 2)
+      t = fabs(x[i]);
+    else
+      t = x[i] * (0.5 * y[i] - z[i]);
+    acc = red_combine(acc, t, mode);
+  }
+  __shared__ double sh[RED_THREADS / 32];
+  for (int o = 16; o > 0; o >>= 1)
+    acc = red_combine(acc, __shfl_xor_sync(0xffffffffu, acc, o), mode);
+  if ((threadIdx.x & 31) == 0)
+    sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r = sh[0];
+    for (int w = 1; w < RED_THREADS / 32; w++)
+      r = red_combine(r, sh[w], mode);
+    partial[blockIdx.x] = r;
+  }
+}
+__global__ void
+k_reduce2(int nb, const double* __restrict__ partial, int mode,
+          double* __restrict__ result)
+{
+  // single block, fixed order: deterministic
+  __shared__ double sh[RED_THREADS];
+  double acc = 0.;
+  for (int i = threadIdx.x; i < nb; i += RED_THREADS)
+    acc = red_combine(acc, partial[i], mode);
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = RED_THREADS / 2; s > 0; s >>= 1) {
+    if (threadIdx.x < s)
+      sh[threadIdx.x] = red_combine(sh[threadIdx.x], sh[threadIdx.x + s], mode);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0)
+    result[0] = sh[0];
+}
+
+// iid N(0,1) per cell, device Philox (Matrix::generateUncorrelatedField)
+__global__ void
+k_uncorrelated(size_t n, unsigned long long seed, double* __restrict__ out);
+
+} // namespace
+
+#include "pf_rng.cuh"
+
+namespace {
+
+__global__ void
+k_uncorrelated(size_t n, unsigned long long seed, double* __restrict__ out)
+{
+  // one Philox call -> two (r1,r2) pairs -> four cells
+  const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t i = 4 * q;
+  if (i >= n)
+    return;
+  const uint4 w = pf::philox4x32_10(q, 0xFFFFFFFFFFFFFFFFull, seed);
+  const double2 a = pf::box_muller_f64(w.x, w.y);
+  const double2 b = pf::box_muller_f64(w.z, w.w);
+  out[i] = a.x;
+  if (i + 1 < n)
+    out[i + 1] = a.y;
+  if (i + 2 < n)
+    out[i + 2] = b.x;
+  if (i + 3 < n)
+    out[i + 3] = b.y;
+}
+
+inline unsigned
+grid_for(size_t n, int threads = 256)
+{
+  size_t b = (n + threads - 1) / threads;
+  return (unsigned)std::min<size_t>(b, 148 * 16);
+}
+
+} // namespace
+
+// ===========================================================================
+// plan
+// ===========================================================================
+struct pf_plan
+{
+  pf_desc d;
+  int dim = 0;
+  long long c[3] = { 1, 1, 1 }, n[3] = { 1, 1, 1 };
+  long long m0 = 1, m0p = 1;
+  unsigned factor = 2;
+  bool compact = false;   // DCT matrix backend semantics (iso / axiparallel)
+  bool hermitian = false; // R2C field backend (dim > 1); 1D uses DFT backends
+  long long rows = 0, P = 0; // table rows and row pitch
+  size_t tab_elems = 0;
+  size_t D = 1, Next = 1;
+
+  double* lam = nullptr;
+  double* sig_gen = nullptr;
+  double* sig = nullptr;
+  double* inv = nullptr;
+  std::map<long long, cplx*> tw; // twiddle tables per line length
+  cplx* Y = nullptr;
+  cplx* Z = nullptr;
+  cplx* V = nullptr;
+  double* spare = nullptr;
+  bool spare_valid = false;
+  double* dev_io[2] = { nullptr, nullptr }; // staging for host fields
+  double* dev_in = nullptr;
+  double* cg[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+  double* red_partial = nullptr; // RED_BLOCKS + 8 doubles
+  unsigned long long* census = nullptr; // 4 x u64
+  pf_eig_stats stats{};
+  bool eig_valid = false;
+  cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_done[2] = { nullptr, nullptr }, ev_copied[2] = { nullptr, nullptr };
+  unsigned long long launches = 0;
+  pf::CovParams cov{};
+  int device = 0;
+};
+
+namespace {
+
+template <class T>
+int
+dev_alloc(T** p, size_t count)
+{
+  if (*p)
+    return 0;
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(PF_ERR_NOMEM, std::string("cudaMalloc of ") +
+                                std::to_string(count * sizeof(T)) +
+                                " bytes failed: " + cudaGetErrorString(e));
+  }
+  *p = reinterpret_cast<T*>(q);
+  return 0;
+}
+template <class T>
+void
+dev_free(T** p)
+{
+  if (*p)
+    cudaFree(*p);
+  *p = nullptr;
+}
+
+void
+free_sized(pf_plan* pl)
+{
+  dev_free(&pl->lam);
+  dev_free(&pl->sig_gen);
+  dev_free(&pl->sig);
+  dev_free(&pl->inv);
+  dev_free(&pl->Y);
+  dev_free(&pl->Z);
+  dev_free(&pl->V);
+  dev_free(&pl->spare);
+  pl->spare_valid = false;
+  pl->eig_valid = false;
+}
+
+bool
+supported_n(long long n)
+{
+  return launcher_for(n) != nullptr;
+}
+
+// sizes, fieldtraits.hh:214-311 (single device = single rank)
+int
+plan_resize(pf_plan* pl)
+{
+  free_sized(pl);
+  const pf_desc& d = pl->d;
+  pl->D = 1;
+  pl->Next = 1;
+  for (int i = 0; i < 3; i++) {
+    pl->c[i] = pl->n[i] = 1;
+  }
+  for (int i = 0; i < pl->dim; i++) {
+    pl->c[i] = d.cells[i];
+    pl->n[i] = (long long)pl->factor * d.cells[i];
+    if (!supported_n(pl->n[i]))
+      return fail(PF_ERR_INVALID,
+                  "unsupported extended size " + std::to_string(pl->n[i]) +
+                    " in dimension " + std::to_string(i) +
+                    " (this build supports powers of two, 2..1024)");
+    pl->D *= pl->c[i];
+    pl->Next *= pl->n[i];
+  }
+  pl->hermitian = pl->dim > 1;
+  pl->compact = pl->dim > 1 && d.anisotropy != PF_ANISO_GEOMETRIC;
+  pl->m0 = pl->hermitian ? pl->n[0] / 2 + 1 : pl->n[0];
+  pl->m0p = (pl->m0 + 7) / 8 * 8;
+  if (pl->dim == 3) {
+    pl->rows = (pl->compact ? pl->n[1] / 2 + 1 : pl->n[1]) * pl->m0;
+    pl->P = pl->compact ? pl->n[2] / 2 + 1 : pl->n[2];
+  } else if (pl->dim == 2) {
+    pl->rows = pl->m0;
+    pl->P = pl->compact ? pl->n[1] / 2 + 1 : pl->n[1];
+  } else {
+    pl->rows = 1;
+    pl->P = pl->n[0];
+  }
+  pl->tab_elems = (size_t)pl->rows * pl->P;
+
+  // covariance parameters (matrix.hh:624-648, covariance.hh:17-136)
+  pf::CovParams& cv = pl->cov;
+  memset(&cv, 0, sizeof(cv));
+  cv.dim = pl->dim;
+  cv.cov = d.covariance;
+  cv.aniso = d.anisotropy;
+  cv.variance = d.variance;
+  cv.p0 = d.cov_param[0];
+  cv.p1 = d.cov_param[1];
+  for (int i = 0; i < pl->dim; i++) {
+    cv.h[i] = d.extensions[i] / d.cells[i];
+    cv.half[i] = 0.5 * d.extensions[i] * pl->factor;
+    cv.period[i] = d.extensions[i] * pl->factor;
+  }
+  const int dim = pl->dim;
+  if (d.anisotropy == PF_ANISO_NONE) {
+    cv.g[0] = 1. / d.corr_length[0];
+  } else if (d.anisotropy == PF_ANISO_AXIPARALLEL) {
+    for (int i = 0; i < dim; i++)
+      cv.g[i] = 1. / d.corr_length[i];
+  } else {
+    // GeneralMatrix, covariance.hh:92-125: adjugate / determinant, same
+    // operation order as the reference
+    const double* copy = d.corr_length;
+    double* m = cv.g;
+    if (dim == 3) {
+      m[0] = copy[4] * copy[8] - copy[5] * copy[7];
+      m[1] = copy[2] * copy[7] - copy[1] * copy[8];
+      m[2] = copy[1] * copy[5] - copy[2] * copy[4];
+      m[3] = copy[5] * copy[6] - copy[3] * copy[8];
+      m[4] = copy[0] * copy[8] - copy[2] * copy[6];
+      m[5] = copy[2] * copy[3] - copy[0] * copy[5];
+      m[6] = copy[3] * copy[7] - copy[4] * copy[6];
+      m[7] = copy[1] * copy[6] - copy[0] * copy[7];
+      m[8] = copy[0] * copy[4] - copy[1] * copy[3];
+      const double det = copy[0] * (copy[4] * copy[8] - copy[5] * copy[7]) -
+                         copy[1] * (copy[3] * copy[8] - copy[5] * copy[6]) +
+                         copy[2] * (copy[3] * copy[7] - copy[4] * copy[6]);
+      for (int i = 0; i < 9; i++)
+        m[i] /= det;
+    } else if (dim == 2) {
+      m[0] = copy[3];
+      m[1] = -copy[1];
+      m[2] = -copy[2];
+      m[3] = copy[0];
+      const double det = copy[0] * copy[3] - copy[1] * copy[2];
+      for (int i = 0; i < 4; i++)
+        m[i] /= det;
+    } else {
+      m[0] = 1. / copy[0];
+    }
+  }
+  return 0;
+}
+
+// per-N inter-pass twiddle table [R2][32] = exp(-2 pi i r k / N)
+int
+twiddles(pf_plan* pl, long long N, const cplx** out)
+{
+  auto it = pl->tw.find(N);
+  if (it != pl->tw.end()) {
+    *out = it->second;
+    return 0;
+  }
+  cplx* dptr = nullptr;
+  const long long R2 = N >= 64 ? N / 32 : 0;
+  std::vector<cplx> h((size_t)std::max<long long>(R2 * 32, 1));
+  h[0] = make_double2(1., 0.);
+  for (long long r = 0; r < R2; r++)
+    for (long long k = 0; k < 32; k++) {
+      const long double a =
+        -2.0L * 3.14159265358979323846264338327950288L * (long double)(r * k) /
+        (long double)N;
+      h[r * 32 + k] = make_double2((double)cosl(a), (double)sinl(a));
+    }
+  PF_TRY(dev_alloc(&dptr, h.size()));
+  PF_CUDA(cudaMemcpyAsync(dptr, h.data(), h.size() * sizeof(cplx),
+                          cudaMemcpyHostToDevice, pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  pl->tw[N] = dptr;
+  *out = dptr;
+  return 0;
+}
+
+int
+run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
+{
+  launch_fn fn = launcher_for(N);
+  if (!fn)
+    return fail(PF_ERR_INVALID, "no kernel for line length " + std::to_string(N));
+  const cplx* tw = nullptr;
+  PF_TRY(twiddles(pl, N, &tw));
+  const int e = fn(kind, &a, tw, pl->stream);
+  if (e != 0)
+    return fail(PF_ERR_CUDA, std::string("kernel launch failed: ") +
+                               cudaGetErrorString((cudaError_t)e));
+  pl->launches++;
+  return 0;
+}
+
+PassArgs
+blank_args()
+{
+  PassArgs a;
+  memset(&a, 0, sizeof(a));
+  a.scale = 1.0;
+  a.na_self = a.nb_self = 1;
+  a.cov_axis_a = a.cov_axis_b = -1;
+  return a;
+}
+
+// ---------------------------------------------------------------------------
+// eigenvalues: Matrix::fillTransformedMatrix, matrix.hh:232-331
+// ---------------------------------------------------------------------------
+int
+eigen_once(pf_plan* pl)
+{
+  const long long* n = pl->n;
+  const long long m0 = pl->m0;
+  PF_TRY(dev_alloc(&pl->lam, pl->tab_elems));
+  PF_TRY(dev_alloc(&pl->census, 4));
+  {
+    unsigned long long init[4] = { 0, 0, 0, 0xFFFFFFFFFFFFFFFFull };
+    PF_CUDA(cudaMemcpyAsync(pl->census, init, sizeof(init),
+                            cudaMemcpyHostToDevice, pl->stream));
+  }
+  const double invN = 1.0 / (double)pl->Next;
+  if (pl->dim == 1) {
+    PassArgs a = blank_args();
+    a.A = 1;
+    a.B = 1;
+    a.cov = pl->cov;
+    a.out = pl->lam;
+    a.out_pitch = n[0];
+    a.keep = (int)n[0];
+    a.scale = invN;
+    a.census = pl->census;
+    a.smallest_bits = pl->census + 3;
+    a.threshold = pl->d.threshold;
+    PF_TRY(run_pass(pl, n[0], pf::K_LAMBDA_COV, a));
+  } else if (pl->dim == 2) {
+    cplx* U = nullptr;
+    PF_TRY(dev_alloc(&U, (size_t)m0 * n[1]));
+    PassArgs a = blank_args();
+    a.A = (int)n[1];
+    a.B = 1;
+    a.cov = pl->cov;
+    a.cov_axis_a = 1;
+    a.out = U;
+    a.osb = 0;
+    a.ose = n[1];
+    a.keep = (int)m0;
+    int rc = run_pass(pl, n[0], pf::K_R2C_COV, a);
+    if (rc == 0) {
+      PassArgs e = blank_args();
+      e.A = (int)m0;
+      e.B = 1;
+      e.in = U;
+      e.isa = n[1];
+      e.n_valid = (int)n[1];
+      e.out = pl->lam;
+      e.out_pitch = pl->P;
+      e.keep = (int)pl->P;
+      e.scale = invN;
+      e.census = pl->census;
+      e.smallest_bits = pl->census + 3;
+      e.threshold = pl->d.threshold;
+      rc = run_pass(pl, n[1], pf::K_LAMBDA, e);
+    }
+    cudaStreamSynchronize(pl->stream);
+    cudaFree(U);
+    PF_TRY(rc);
+  } else {
+    const long long R1 = pl->compact ? n[1] / 2 + 1 : n[1];
+    cplx *U = nullptr, *V = nullptr;
+    PF_TRY(dev_alloc(&U, (size_t)n[2] * m0 * n[1]));
+    int rc = dev_alloc(&V, (size_t)R1 * m0 * n[2]);
+    if (rc == 0) {
+      PassArgs a = blank_args(); // E0: x0 lines, (a,b) = (x1,x2)
+      a.A = (int)n[1];
+      a.B = (int)n[2];
+      a.cov = pl->cov;
+      a.cov_axis_a = 1;
+      a.cov_axis_b = 2;
+      a.out = U; // U[x2][k0][x1]
+      a.osb = m0 * n[1];
+      a.ose = n[1];
+      a.keep = (int)m0;
+      rc = run_pass(pl, n[0], pf::K_R2C_COV, a);
+    }
+    if (rc == 0) {
+      PassArgs a = blank_args(); // E1: x1 lines, (a,b) = (x2,k0)
+      a.A = (int)n[2];
+      a.B = (int)m0;
+      a.in = U;
+      a.isa = m0 * n[1];
+      a.isb = n[1];
+      a.n_valid = (int)n[1];
+      a.out = V; // V[k1][k0][x2]
+      a.osb = n[2];
+      a.ose = m0 * n[2];
+      a.keep = (int)R1;
+      rc = run_pass(pl, n[1], pf::K_C2T_FWD, a);
+    }
+    if (rc == 0) {
+      PassArgs e = blank_args(); // E2: x2 lines
+      e.A = (int)(R1 * m0);
+      e.B = 1;
+      e.in = V;
+      e.isa = n[2];
+      e.n_valid = (int)n[2];
+      e.out = pl->lam;
+      e.out_pitch = pl->P;
+      e.keep = (int)pl->P;
+      e.scale = invN;
+      e.census = pl->census;
+      e.smallest_bits = pl->census + 3;
+      e.threshold = pl->d.threshold;
+      rc = run_pass(pl, n[2], pf::K_LAMBDA, e);
+    }
+    cudaStreamSynchronize(pl->stream);
+    cudaFree(U);
+    cudaFree(V);
+    PF_TRY(rc);
+  }
+  unsigned long long res[4];
+  PF_CUDA(cudaMemcpyAsync(res, pl->census, sizeof(res), cudaMemcpyDeviceToHost,
+                          pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  pl->stats.small_count = res[0];
+  pl->stats.zero_count = res[1];
+  pl->stats.negative_count = res[2];
+  unsigned long long bits = res[3];
+  bits = (bits >> 63) ? (bits & 0x7FFFFFFFFFFFFFFFull) : ~bits;
+  double sm;
+  memcpy(&sm, &bits, sizeof(sm));
+  pl->stats.smallest = sm;
+  pl->stats.factor_used = pl->factor;
+  return 0;
+}
+
+int
+ensure_eigen(pf_plan* pl)
+{
+  if (pl->eig_valid)
+    return 0;
+  for (;;) {
+    PF_TRY(eigen_once(pl));
+    if (pl->stats.negative_count > 0 && !pl->d.approximate) {
+      if (pl->d.max_factor && pl->factor * 2 <= pl->d.max_factor &&
+          !pl->d.periodic) {
+        pl->factor *= 2; // embedding-factor retry (new behaviour, off by
+                         // default; the reference only throws)
+        PF_TRY(plan_resize(pl));
+        continue;
+      }
+      dev_free(&pl->lam);
+      return fail(PF_ERR_NEGATIVE_EIGENVALUES,
+                  "negative eigenvalues in covariance matrix");
+    }
+    break;
+  }
+  pl->eig_valid = true;
+  return 0;
+}
+
+int
+ensure_table(pf_plan* pl, double** tab, int mode)
+{
+  PF_TRY(ensure_eigen(pl));
+  if (*tab)
+    return 0;
+  PF_TRY(dev_alloc(tab, pl->tab_elems));
+  k_derive_table<<<(unsigned)((pl->tab_elems + 255) / 256), 256, 0, pl->stream>>>(
+    pl->lam, *tab, pl->tab_elems, mode);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return 0;
+}
+
+int
+ensure_work(pf_plan* pl)
+{
+  if (pl->dim == 3) {
+    PF_TRY(dev_alloc(&pl->Y, (size_t)pl->m0 * pl->c[2] * pl->n[1]));
+    PF_TRY(dev_alloc(&pl->Z, (size_t)pl->c[2] * pl->c[1] * pl->m0p));
+  } else if (pl->dim == 2) {
+    PF_TRY(dev_alloc(&pl->Z, (size_t)pl->c[1] * pl->m0p));
+  }
+  return 0;
+}
+
+// table addressing shared by pass A and the fused spectral pass
+void
+set_table(const pf_plan* pl, PassArgs& a, const double* tab)
+{
+  a.tab = tab;
+  a.tab_pitch = pl->P;
+  if (pl->dim == 3) {
+    a.rma = pl->m0;
+    a.rmb = 1;
+    a.tab_mirror_a = pl->compact ? (int)pl->n[1] : 0;
+    a.tab_mirror_e = pl->compact ? 1 : 0;
+  } else if (pl->dim == 2) {
+    a.rma = 1;
+    a.rmb = 0;
+    a.tab_mirror_a = 0;
+    a.tab_mirror_e = pl->compact ? 1 : 0;
+  } else {
+    a.rma = a.rmb = 0;
+    a.tab_mirror_a = 0;
+    a.tab_mirror_e = 0;
+  }
+}
+
+// inverse passes B and C (3D) / C (2D) from Y / Z into a device field
+int
+inverse_tail(pf_plan* pl, double* out_dev, int transform)
+{
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  if (pl->dim == 3) {
+    PassArgs b = blank_args(); // pass B: k1 lines, (a,b) = (k0, x2)
+    b.A = (int)pl->m0;
+    b.B = (int)c[2];
+    b.in = pl->Y;
+    b.isa = c[2] * n[1];
+    b.isb = n[1];
+    b.n_valid = (int)n[1];
+    b.out = pl->Z; // Z[x2][x1][k0]
+    b.osb = c[1] * pl->m0p;
+    b.ose = pl->m0p;
+    b.keep = (int)c[1];
+    PF_TRY(run_pass(pl, n[1], pf::K_C2T_INV, b));
+  }
+  PassArgs cc = blank_args(); // pass C
+  cc.A = (int)(pl->dim == 3 ? c[1] * c[2] : c[1]);
+  cc.B = 1;
+  cc.in = pl->Z;
+  cc.isa = pl->m0p;
+  cc.out = out_dev;
+  cc.out_pitch = c[0];
+  cc.keep = (int)c[0];
+  cc.transform = transform;
+  cc.tparam = pl->d.boxcox_lambda;
+  PF_TRY(run_pass(pl, n[0], pf::K_C2R, cc));
+  return 0;
+}
+
+// Matrix::generateField (matrix.hh:343-438) into device memory
+int
+generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
+             unsigned long long realization, const double2* noise_dev,
+             double* out_dev, double* spare_dev, int transform)
+{
+  PF_TRY(ensure_table(pl, &pl->sig_gen, pl->hermitian ? 0 : 1));
+  PF_TRY(ensure_work(pl));
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  PassArgs a = blank_args();
+  set_table(pl, a, pl->sig_gen);
+  a.noise_kind = noise_kind;
+  a.seed = seed;
+  a.realization = realization;
+  a.noise = noise_dev;
+  a.hermitian = pl->hermitian ? 1 : 0;
+  a.corrected = pl->d.parity_mode == 1;
+  if (pl->dim == 3) {
+    a.A = (int)n[1]; // a = k1, b = k0, e = k2
+    a.B = (int)m0;
+    a.cma = m0 * (n[2] / 2);
+    a.cmb = 1;
+    a.cme = m0;
+    a.ima = m0 * n[2]; // s = k0 + m0*(k2 + n2*k1), r2cfieldbackend.hh:190-199
+    a.imb = 1;
+    a.ime = m0;
+    a.na_self = (int)n[1];
+    a.nb_self = (int)n[0];
+    a.plane_axis = 1;
+    a.out = pl->Y; // Y[k0][x2][k1]
+    a.osb = c[2] * n[1];
+    a.ose = n[1];
+    a.keep = (int)c[2];
+    PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
+    PF_TRY(inverse_tail(pl, out_dev, transform));
+  } else if (pl->dim == 2) {
+    a.A = (int)m0; // a = k0, e = k1
+    a.B = 1;
+    a.cma = 1;
+    a.cmb = 0;
+    a.cme = m0;
+    a.ima = 1; // s = k0 + m0*k1
+    a.imb = 0;
+    a.ime = m0;
+    a.na_self = (int)n[0];
+    a.nb_self = 1;
+    a.plane_axis = 0;
+    a.out = pl->Z; // Z[x1][k0]
+    a.osb = 0;
+    a.ose = pl->m0p;
+    a.keep = (int)c[1];
+    PF_TRY(run_pass(pl, n[1], pf::K_GEN_TILE, a));
+    PF_TRY(inverse_tail(pl, out_dev, transform));
+  } else {
+    a.A = 1;
+    a.B = 1;
+    a.cme = 1;
+    a.ime = 1;
+    a.out = out_dev;
+    a.out2 = spare_dev;
+    a.out_pitch = c[0];
+    a.keep = (int)c[0];
+    a.transform = transform;
+    a.tparam = pl->d.boxcox_lambda;
+    PF_TRY(run_pass(pl, n[0], pf::K_GEN_REIM, a));
+  }
+  return 0;
+}
+
+// multiplyExtended / multiplyRootExtended / multiplyInverseExtended
+// (matrix.hh:1459-1662) on device fields; in_dev may equal out_dev
+int
+apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
+{
+  double** tabp = op == PF_OP_MATRIX ? &pl->lam
+                  : op == PF_OP_ROOT ? &pl->sig
+                                     : &pl->inv;
+  if (op == PF_OP_MATRIX)
+    PF_TRY(ensure_eigen(pl));
+  else
+    PF_TRY(ensure_table(pl, tabp, op == PF_OP_ROOT ? 1 : 2));
+  PF_TRY(ensure_work(pl));
+  const double* tab = *tabp;
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  const double invN = 1.0 / (double)pl->Next;
+  if (pl->dim == 3) {
+    PF_TRY(dev_alloc(&pl->V, (size_t)n[1] * m0 * c[2]));
+    cplx* Up = pl->Z; // pruned U[c2][m0][c1] fits in Z (c2*c1*m0p)
+    PassArgs f0 = blank_args(); // F0: x0 lines, (a,b) = (x1,x2)
+    f0.A = (int)c[1];
+    f0.B = (int)c[2];
+    f0.in = in_dev;
+    f0.isa = c[0];
+    f0.isb = c[1] * c[0];
+    f0.n_valid = (int)c[0];
+    f0.out = Up;
+    f0.osb = m0 * c[1];
+    f0.ose = c[1];
+    f0.keep = (int)m0;
+    PF_TRY(run_pass(pl, n[0], pf::K_R2C_LOAD, f0));
+    PassArgs f1 = blank_args(); // F1: x1 lines, (a,b) = (x2,k0)
+    f1.A = (int)c[2];
+    f1.B = (int)m0;
+    f1.in = Up;
+    f1.isa = m0 * c[1];
+    f1.isb = c[1];
+    f1.n_valid = (int)c[1];
+    f1.out = pl->V; // V[k1][k0][x2<c2]
+    f1.osb = c[2];
+    f1.ose = m0 * c[2];
+    f1.keep = (int)n[1];
+    PF_TRY(run_pass(pl, n[1], pf::K_C2T_FWD, f1));
+    PassArgs s = blank_args(); // F2 * g + A: x2 lines, (a,b) = (k1,k0)
+    set_table(pl, s, tab);
+    s.A = (int)n[1];
+    s.B = (int)m0;
+    s.in = pl->V;
+    s.isa = m0 * c[2];
+    s.isb = c[2];
+    s.n_valid = (int)c[2];
+    s.scale = invN;
+    s.out = pl->Y;
+    s.osb = c[2] * n[1];
+    s.ose = n[1];
+    s.keep = (int)c[2];
+    PF_TRY(run_pass(pl, n[2], pf::K_SPEC_TILE, s));
+    PF_TRY(inverse_tail(pl, out_dev, 0));
+  } else if (pl->dim == 2) {
+    PF_TRY(dev_alloc(&pl->V, (size_t)m0 * c[1]));
+    PassArgs f0 = blank_args(); // F0: x0 lines, a = x1
+    f0.A = (int)c[1];
+    f0.B = 1;
+    f0.in = in_dev;
+    f0.isa = c[0];
+    f0.n_valid = (int)c[0];
+    f0.out = pl->V; // U[k0][x1<c1]
+    f0.osb = 0;
+    f0.ose = c[1];
+    f0.keep = (int)m0;
+    PF_TRY(run_pass(pl, n[0], pf::K_R2C_LOAD, f0));
+    PassArgs s = blank_args(); // x1 lines, a = k0
+    set_table(pl, s, tab);
+    s.A = (int)m0;
+    s.B = 1;
+    s.in = pl->V;
+    s.isa = c[1];
+    s.n_valid = (int)c[1];
+    s.scale = invN;
+    s.out = pl->Z;
+    s.osb = 0;
+    s.ose = pl->m0p;
+    s.keep = (int)c[1];
+    PF_TRY(run_pass(pl, n[1], pf::K_SPEC_TILE, s));
+    PF_TRY(inverse_tail(pl, out_dev, 0));
+  } else {
+    PassArgs s = blank_args();
+    set_table(pl, s, tab);
+    s.A = 1;
+    s.B = 1;
+    s.in = in_dev;
+    s.n_valid = (int)c[0];
+    s.scale = invN;
+    s.out = out_dev;
+    s.out_pitch = c[0];
+    s.keep = (int)c[0];
+    PF_TRY(run_pass(pl, n[0], pf::K_SPEC_REIM, s));
+  }
+  return 0;
+}
+
+int
+reduce_dev(pf_plan* pl, size_t nn, const double* x, const double* y,
+           const double* z, int mode, double* result_host)
+{
+  PF_TRY(dev_alloc(&pl->red_partial, RED_BLOCKS + 8));
+  const int nb = (int)std::min<size_t>(RED_BLOCKS, (nn + RED_THREADS - 1) / RED_THREADS);
+  k_reduce1<<<std::max(nb, 1), RED_THREADS, 0, pl->stream>>>(nn, x, y, z, mode,
+                                                           pl->red_partial);
+  k_reduce2<<<1, RED_THREADS, 0, pl->stream>>>(std::max(nb, 1), pl->red_partial,
+                                               mode, pl->red_partial + RED_BLOCKS);
+  PF_CUDA(cudaGetLastError());
+  pl->launches += 2;
+  PF_CUDA(cudaMemcpyAsync(result_host, pl->red_partial + RED_BLOCKS,
+                          sizeof(double), cudaMemcpyDeviceToHost, pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+// staging of host arrays
+struct Staged
+{
+  pf_plan* pl;
+  const double* dev = nullptr;
+  double* owned = nullptr;
+  ~Staged()
+  {
+    if (owned)
+      cudaFree(owned);
+  }
+};
+
+int
+stage_in(pf_plan* pl, const double* p, size_t nn, Staged& s)
+{
+  s.pl = pl;
+  if (is_device_ptr(p)) {
+    s.dev = p;
+    return 0;
+  }
+  PF_TRY(dev_alloc(&s.owned, nn));
+  PF_CUDA(cudaMemcpyAsync(s.owned, p, nn * sizeof(double),
+                          cudaMemcpyHostToDevice, pl->stream));
+  s.dev = s.owned;
+  return 0;
+}
+
+int
+check_plan(const pf_plan* pl)
+{
+  if (!pl)
+    return fail(PF_ERR_INVALID, "null plan");
+  cudaError_t e = cudaSetDevice(pl->device);
+  if (e != cudaSuccess)
+    return fail(PF_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+} // namespace
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" {
+
+const char*
+pf_version(void)
+{
+  return "parafields-b200 0.1 (sm_100a)";
+}
+
+const char*
+pf_last_error(void)
+{
+  return g_err.c_str();
+}
+
+int
+pf_device_count(void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int
+pf_device_info(int device, char* name, int* sm_count, size_t* mem_bytes)
+{
+  cudaDeviceProp prop;
+  PF_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (name) {
+    strncpy(name, prop.name, 255);
+    name[255] = 0;
+  }
+  if (sm_count)
+    *sm_count = prop.multiProcessorCount;
+  if (mem_bytes)
+    *mem_bytes = prop.totalGlobalMem;
+  return 0;
+}
+
+void
+pf_desc_default(pf_desc* d)
+{
+  memset(d, 0, sizeof(*d));
+  d->dim = 2;
+  for (int i = 0; i < 3; i++) {
+    d->cells[i] = 1;
+    d->extensions[i] = 1.0;
+  }
+  d->embedding_factor = 2;     // fieldtraits.hh:182
+  d->covariance = PF_COV_EXPONENTIAL;
+  d->variance = 1.0;
+  d->anisotropy = PF_ANISO_NONE;
+  d->corr_length[0] = 0.1;
+  d->threshold = 1e-14;        // matrix.hh:284
+  d->cg_iterations = 100;      // fieldtraits.hh:178
+  d->device = -1;
+}
+
+int
+pf_plan_create(const pf_desc* desc, pf_plan** out)
+{
+  if (!desc || !out)
+    return fail(PF_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (desc->dim < 1 || desc->dim > 3)
+    return fail(PF_ERR_INVALID, "dimension must be 1, 2 or 3");
+  if (desc->covariance < 0 || desc->covariance > PF_COV_WHITE_NOISE)
+    return fail(PF_ERR_INVALID, "covariance structure not known");
+  if (desc->anisotropy < 0 || desc->anisotropy > 2)
+    return fail(PF_ERR_INVALID,
+                "stochastic.anisotropy must be \"none\", \"axiparallel\" or "
+                "\"geometric\"");
+  if (desc->transform < 0 || desc->transform > 4)
+    return fail(PF_ERR_INVALID, "transform type not known");
+  // covariance.hh argument checks
+  if (desc->covariance == PF_COV_CUBIC && desc->dim == 3)
+    return fail(PF_ERR_INVALID, "cubic covariance only applicable in 1D or 2D");
+  if (desc->covariance == PF_COV_GAMMA_EXPONENTIAL &&
+      (desc->cov_param[0] < 0. || desc->cov_param[0] > 2.))
+    return fail(PF_ERR_INVALID, "exponent gamma has to be between 0 and 2");
+  if (desc->covariance == PF_COV_GENERALIZED_CAUCHY) {
+    if (desc->cov_param[0] <= 0. || desc->cov_param[0] > 2.)
+      return fail(PF_ERR_INVALID,
+                  "generalized Cauchy alpha has to be in range (0,2]");
+    if (desc->cov_param[1] <= 0.)
+      return fail(PF_ERR_INVALID, "generalized Cauchy beta has to be positive");
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(PF_ERR_CUDA, "no CUDA device available (there is no CPU "
+                             "fallback in libparafields_cuda)");
+  }
+  pf_plan* pl = new pf_plan();
+  pl->d = *desc;
+  pl->dim = desc->dim;
+  if (desc->device >= 0)
+    pl->device = desc->device;
+  else
+    cudaGetDevice(&pl->device);
+  if (cudaSetDevice(pl->device) != cudaSuccess) {
+    delete pl;
+    return fail(PF_ERR_CUDA, "cudaSetDevice failed");
+  }
+  pl->factor = desc->embedding_factor ? desc->embedding_factor : 2;
+  if (desc->periodic)
+    pl->factor = 1; // fieldtraits.hh:196-202
+  int rc = plan_resize(pl);
+  if (rc != 0) {
+    delete pl;
+    return rc;
+  }
+  cudaStreamCreateWithFlags(&pl->copy_stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 2; i++) {
+    cudaEventCreateWithFlags(&pl->ev_done[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&pl->ev_copied[i], cudaEventDisableTiming);
+  }
+  *out = pl;
+  return 0;
+}
+
+int
+pf_plan_destroy(pf_plan* pl)
+{
+  if (!pl)
+    return 0;
+  cudaSetDevice(pl->device);
+  cudaDeviceSynchronize();
+  free_sized(pl);
+  for (auto& kv : pl->tw)
+    cudaFree(kv.second);
+  dev_free(&pl->dev_io[0]);
+  dev_free(&pl->dev_io[1]);
+  dev_free(&pl->dev_in);
+  for (int i = 0; i < 6; i++)
+    dev_free(&pl->cg[i]);
+  dev_free(&pl->red_partial);
+  dev_free(&pl->census);
+  if (pl->copy_stream)
+    cudaStreamDestroy(pl->copy_stream);
+  for (int i = 0; i < 2; i++) {
+    if (pl->ev_done[i])
+      cudaEventDestroy(pl->ev_done[i]);
+    if (pl->ev_copied[i])
+      cudaEventDestroy(pl->ev_copied[i]);
+  }
+  delete pl;
+  return 0;
+}
+
+int
+pf_plan_set_stream(pf_plan* pl, void* stream)
+{
+  PF_TRY(check_plan(pl));
+  pl->stream = reinterpret_cast<cudaStream_t>(stream);
+  return 0;
+}
+
+int
+pf_plan_synchronize(pf_plan* pl)
+{
+  PF_TRY(check_plan(pl));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+unsigned long long
+pf_plan_launch_count(const pf_plan* pl)
+{
+  return pl ? pl->launches : 0;
+}
+
+size_t
+pf_domain_size(const pf_plan* pl)
+{
+  return pl ? pl->D : 0;
+}
+size_t
+pf_extended_size(const pf_plan* pl)
+{
+  return pl ? pl->Next : 0;
+}
+size_t
+pf_noise_entries(const pf_plan* pl)
+{
+  if (!pl)
+    return 0;
+  return (size_t)pl->m0 * pl->n[1] * pl->n[2];
+}
+
+int
+pf_compute_eigenvalues(pf_plan* pl, pf_eig_stats* stats)
+{
+  PF_TRY(check_plan(pl));
+  int rc = ensure_eigen(pl);
+  if (stats)
+    *stats = pl->stats;
+  return rc;
+}
+
+size_t
+pf_eigenvalue_count(const pf_plan* pl, int layout)
+{
+  if (!pl)
+    return 0;
+  size_t r = 1;
+  for (int i = 0; i < pl->dim; i++) {
+    if (layout == PF_LAMBDA_NATURAL || !pl->compact)
+      r *= (i == 0 ? pl->m0 : pl->n[i]);
+    else
+      r *= pl->n[i] / 2 + 1;
+  }
+  return r;
+}
+
+int
+pf_get_eigenvalues(pf_plan* pl, double* out, size_t count, int layout)
+{
+  PF_TRY(check_plan(pl));
+  PF_TRY(ensure_eigen(pl));
+  const size_t total = pf_eigenvalue_count(pl, layout);
+  if (count < total)
+    return fail(PF_ERR_INVALID, "eigenvalue buffer too small");
+  GatherArgs g;
+  memset(&g, 0, sizeof(g));
+  g.dim = pl->dim;
+  for (int i = 0; i < 3; i++) {
+    g.n[i] = pl->n[i];
+    g.ob[i] = 1;
+  }
+  for (int i = 0; i < pl->dim; i++) {
+    if (layout == PF_LAMBDA_NATURAL || !pl->compact)
+      g.ob[i] = (i == 0 ? pl->m0 : pl->n[i]);
+    else
+      g.ob[i] = pl->n[i] / 2 + 1;
+  }
+  // fftw.transposed: storage has the last two dims swapped in 3D
+  // (dctmatrixbackend.hh:221-231, r2cmatrixbackend.hh transposeIfNeeded)
+  g.transposed = (layout == PF_LAMBDA_REFERENCE && pl->dim == 3) ? 1 : 0;
+  g.compact = pl->compact ? 1 : 0;
+  g.m0 = pl->m0;
+  g.P = pl->P;
+  const bool dev = is_device_ptr(out);
+  double* dst = out;
+  double* tmp = nullptr;
+  if (!dev) {
+    PF_TRY(dev_alloc(&tmp, total));
+    dst = tmp;
+  }
+  k_gather_lambda<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
+    pl->lam, dst, g, total);
+  cudaError_t e = cudaGetLastError();
+  pl->launches++;
+  if (e == cudaSuccess && !dev)
+    e = cudaMemcpyAsync(out, tmp, total * sizeof(double),
+                        cudaMemcpyDeviceToHost, pl->stream);
+  if (e == cudaSuccess && !dev)
+    e = cudaStreamSynchronize(pl->stream);
+  if (tmp)
+    cudaFree(tmp);
+  if (e != cudaSuccess)
+    return fail(PF_ERR_CUDA, cudaGetErrorString(e));
+  return 0;
+}
+
+int
+pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
+                  double* out, int apply_transform)
+{
+  PF_TRY(check_plan(pl));
+  if (!out)
+    return fail(PF_ERR_INVALID, "null output");
+  const int tr = apply_transform ? pl->d.transform : 0;
+  const int nk = pl->d.rng_mode == 1 ? pf::NOISE_PHILOX_F64 : pf::NOISE_PHILOX_FAST;
+  const bool dev = is_device_ptr(out);
+  if (pl->dim == 1) {
+    // DFT backend: one transform yields two fields (matrix.hh:428-437)
+    PF_TRY(dev_alloc(&pl->spare, pl->D));
+    PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+    for (size_t r = 0; r < count; r++) {
+      double* o = out + r * pl->D;
+      double* dst = dev ? o : pl->dev_io[0];
+      if (pl->spare_valid) {
+        if (tr) {
+          k_transform<<<grid_for(pl->D), 256, 0, pl->stream>>>(
+            pl->D, pl->spare, dst, tr, pl->d.boxcox_lambda);
+          pl->launches++;
+        } else
+          PF_CUDA(cudaMemcpyAsync(dst, pl->spare, pl->D * sizeof(double),
+                                  cudaMemcpyDeviceToDevice, pl->stream));
+        pl->spare_valid = false;
+      } else {
+        PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, dst, pl->spare, tr));
+        pl->spare_valid = true;
+      }
+      if (!dev) {
+        PF_CUDA(cudaMemcpyAsync(o, dst, pl->D * sizeof(double),
+                                cudaMemcpyDeviceToHost, pl->stream));
+        PF_CUDA(cudaStreamSynchronize(pl->stream));
+      }
+    }
+    return 0;
+  }
+  if (dev) {
+    for (size_t r = 0; r < count; r++)
+      PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->D,
+                          nullptr, tr));
+    return 0;
+  }
+  // host output: double-buffered so that the D2H copy of realization r
+  // overlaps the kernels of realization r+1 (needs pinned host memory to
+  // overlap; pageable memory still works, serialised by the runtime)
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  if (count > 1)
+    PF_TRY(dev_alloc(&pl->dev_io[1], pl->D));
+  for (size_t r = 0; r < count; r++) {
+    const int s = (int)(r & 1);
+    if (r >= 2)
+      PF_CUDA(cudaStreamWaitEvent(pl->stream, pl->ev_copied[s], 0));
+    PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, pl->dev_io[s], nullptr, tr));
+    PF_CUDA(cudaEventRecord(pl->ev_done[s], pl->stream));
+    PF_CUDA(cudaStreamWaitEvent(pl->copy_stream, pl->ev_done[s], 0));
+    PF_CUDA(cudaMemcpyAsync(out + r * pl->D, pl->dev_io[s],
+                            pl->D * sizeof(double), cudaMemcpyDeviceToHost,
+                            pl->copy_stream));
+    PF_CUDA(cudaEventRecord(pl->ev_copied[s], pl->copy_stream));
+  }
+  PF_CUDA(cudaStreamSynchronize(pl->copy_stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+int
+pf_generate(pf_plan* pl, uint64_t seed, uint64_t realization, double* out,
+            int apply_transform)
+{
+  return pf_generate_batch(pl, seed, realization, 1, out, apply_transform);
+}
+
+int
+pf_generate_from_noise(pf_plan* pl, const double* noise, double* out,
+                       double* spare)
+{
+  PF_TRY(check_plan(pl));
+  if (!noise || !out)
+    return fail(PF_ERR_INVALID, "null argument");
+  const size_t ne = pf_noise_entries(pl);
+  Staged sn;
+  PF_TRY(stage_in(pl, noise, 2 * ne, sn));
+  const bool dev = is_device_ptr(out);
+  const bool sdev = is_device_ptr(spare);
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  double* dst = dev ? out : pl->dev_io[0];
+  double* sp = nullptr;
+  if (pl->dim == 1) {
+    PF_TRY(dev_alloc(&pl->spare, pl->D));
+    sp = (spare && sdev) ? spare : pl->spare;
+  }
+  PF_TRY(generate_dev(pl, pf::NOISE_INJECTED, 0, 0,
+                      reinterpret_cast<const double2*>(sn.dev), dst, sp, 0));
+  if (!dev)
+    PF_CUDA(cudaMemcpyAsync(out, dst, pl->D * sizeof(double),
+                            cudaMemcpyDeviceToHost, pl->stream));
+  if (spare && !sdev && pl->dim == 1)
+    PF_CUDA(cudaMemcpyAsync(spare, sp, pl->D * sizeof(double),
+                            cudaMemcpyDeviceToHost, pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+int
+pf_generate_uncorrelated(pf_plan* pl, uint64_t seed, double* out)
+{
+  PF_TRY(check_plan(pl));
+  const bool dev = is_device_ptr(out);
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  double* dst = dev ? out : pl->dev_io[0];
+  const size_t q = (pl->D + 3) / 4;
+  k_uncorrelated<<<(unsigned)((q + 255) / 256), 256, 0, pl->stream>>>(pl->D, seed, dst);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  if (!dev) {
+    PF_CUDA(cudaMemcpyAsync(out, dst, pl->D * sizeof(double),
+                            cudaMemcpyDeviceToHost, pl->stream));
+    PF_CUDA(cudaStreamSynchronize(pl->stream));
+  }
+  return 0;
+}
+
+int
+pf_set_variance_as_field(pf_plan* pl, double* out)
+{
+  PF_TRY(check_plan(pl));
+  if (is_device_ptr(out)) {
+    k_fill<<<grid_for(pl->D), 256, 0, pl->stream>>>(pl->D, pl->d.variance, out);
+    PF_CUDA(cudaGetLastError());
+    pl->launches++;
+  } else {
+    for (size_t i = 0; i < pl->D; i++)
+      out[i] = pl->d.variance;
+  }
+  return 0;
+}
+
+int
+pf_apply(pf_plan* pl, int op, const double* in, double* out)
+{
+  PF_TRY(check_plan(pl));
+  if (op < 0 || op > 2 || !in || !out)
+    return fail(PF_ERR_INVALID, "bad argument");
+  Staged si;
+  PF_TRY(stage_in(pl, in, pl->D, si));
+  const bool dev = is_device_ptr(out);
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  double* dst = dev ? out : pl->dev_io[0];
+  PF_TRY(apply_dev(pl, op, si.dev, dst));
+  if (!dev)
+    PF_CUDA(cudaMemcpyAsync(out, dst, pl->D * sizeof(double),
+                            cudaMemcpyDeviceToHost, pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+// Matrix::multiplyInverse + innerCG (matrix.hh:198-215,1331-1448).  All
+// vectors stay in HBM; only the scalars of the recurrence visit the host.
+int
+pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
+{
+  PF_TRY(check_plan(pl));
+  if (!in || !out)
+    return fail(PF_ERR_INVALID, "null argument");
+  const size_t D = pl->D;
+  Staged si;
+  PF_TRY(stage_in(pl, in, D, si));
+  const double* b = si.dev; // "solution"
+  for (int i = 0; i < 6; i++)
+    PF_TRY(dev_alloc(&pl->cg[i], D));
+  double* x = pl->cg[0];   // iter
+  double* Mx = pl->cg[1];  // matrixTimesIter
+  double* r = pl->cg[2];   // residual
+  double* z = pl->cg[3];   // precResidual
+  double* dir = pl->cg[4]; // direction
+  double* Md = pl->cg[5];  // matrixTimesDirection
+  unsigned count = 0;
+  double maxabs = 0.;
+  PF_TRY(reduce_dev(pl, D, b, nullptr, nullptr, 2, &maxabs));
+  const unsigned g = grid_for(D);
+  if (!(maxabs > 1e-10)) {
+    // fieldZero: return the input unchanged (matrix.hh:202-207)
+    PF_CUDA(cudaMemcpyAsync(x, b, D * sizeof(double), cudaMemcpyDeviceToDevice,
+                            pl->stream));
+  } else {
+    PF_TRY(apply_dev(pl, PF_OP_INVERSE_EXT, b, x));
+    PF_TRY(apply_dev(pl, PF_OP_MATRIX, x, Mx));
+    k_residual<<<g, 256, 0, pl->stream>>>(D, b, Mx, r);
+    pl->launches++;
+    PF_TRY(apply_dev(pl, PF_OP_INVERSE_EXT, r, z));
+    PF_CUDA(cudaMemcpyAsync(dir, z, D * sizeof(double), cudaMemcpyDeviceToDevice,
+                            pl->stream));
+    double scalarProd, scalarProd2, firstValue;
+    PF_TRY(reduce_dev(pl, D, z, r, nullptr, 0, &scalarProd));
+    PF_TRY(reduce_dev(pl, D, r, r, nullptr, 0, &scalarProd2));
+    bool converged = std::sqrt(std::fabs(scalarProd2)) < 1e-6;
+    PF_TRY(reduce_dev(pl, D, x, Mx, b, 3, &firstValue));
+    while (!converged && count < pl->d.cg_iterations) {
+      PF_TRY(apply_dev(pl, PF_OP_MATRIX, dir, Md));
+      double alphaDenominator, oldValue, value;
+      PF_TRY(reduce_dev(pl, D, dir, Md, nullptr, 0, &alphaDenominator));
+      const double alpha = scalarProd / alphaDenominator;
+      PF_TRY(reduce_dev(pl, D, x, Mx, b, 3, &oldValue));
+      k_axpy<<<g, 256, 0, pl->stream>>>(D, alpha, dir, x);
+      k_axpy<<<g, 256, 0, pl->stream>>>(D, alpha, Md, Mx);
+      pl->launches += 2;
+      PF_TRY(reduce_dev(pl, D, x, Mx, b, 3, &value));
+      k_residual<<<g, 256, 0, pl->stream>>>(D, b, Mx, r);
+      pl->launches++;
+      PF_TRY(apply_dev(pl, PF_OP_INVERSE_EXT, r, z));
+      double beta = 1. / scalarProd;
+      PF_TRY(reduce_dev(pl, D, z, r, nullptr, 0, &scalarProd));
+      beta *= scalarProd;
+      k_direction<<<g, 256, 0, pl->stream>>>(D, beta, z, dir);
+      pl->launches++;
+      if (value != firstValue) {
+        if (std::fabs(value - oldValue) / std::fabs(value - firstValue) < 1e-16)
+          converged = true;
+      }
+      count++;
+    }
+  }
+  if (iterations)
+    *iterations = count;
+  PF_CUDA(cudaMemcpyAsync(out, x, D * sizeof(double),
+                          is_device_ptr(out) ? cudaMemcpyDeviceToDevice
+                                             : cudaMemcpyDeviceToHost,
+                          pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+int
+pf_transform(pf_plan* pl, const double* in, double* out, size_t nn)
+{
+  PF_TRY(check_plan(pl));
+  Staged si;
+  PF_TRY(stage_in(pl, in, nn, si));
+  const bool dev = is_device_ptr(out);
+  double* tmp = nullptr;
+  if (!dev)
+    PF_TRY(dev_alloc(&tmp, nn));
+  double* dst = dev ? out : tmp;
+  k_transform<<<grid_for(nn), 256, 0, pl->stream>>>(nn, si.dev, dst,
+                                                   pl->d.transform,
+                                                   pl->d.boxcox_lambda);
+  cudaError_t e = cudaGetLastError();
+  pl->launches++;
+  if (e == cudaSuccess && !dev)
+    e = cudaMemcpyAsync(out, dst, nn * sizeof(double), cudaMemcpyDeviceToHost,
+                        pl->stream);
+  if (e == cudaSuccess)
+    e = cudaStreamSynchronize(pl->stream);
+  if (tmp)
+    cudaFree(tmp);
+  if (e != cudaSuccess)
+    return fail(PF_ERR_CUDA, cudaGetErrorString(e));
+  return 0;
+}
+
+int
+pf_vec_axpy(pf_plan* pl, size_t nn, double alpha, const double* x, double* y)
+{
+  PF_TRY(check_plan(pl));
+  if (is_device_ptr(x) && is_device_ptr(y)) {
+    k_axpy<<<grid_for(nn), 256, 0, pl->stream>>>(nn, alpha, x, y);
+    PF_CUDA(cudaGetLastError());
+    pl->launches++;
+    return 0;
+  }
+  if (is_device_ptr(x) || is_device_ptr(y))
+    return fail(PF_ERR_INVALID, "pf_vec_axpy: x and y must live in the same memory space");
+  for (size_t i = 0; i < nn; i++)
+    y[i] += alpha * x[i];
+  return 0;
+}
+
+int
+pf_vec_scale(pf_plan* pl, size_t nn, double alpha, double* x)
+{
+  PF_TRY(check_plan(pl));
+  if (is_device_ptr(x)) {
+    k_scale<<<grid_for(nn), 256, 0, pl->stream>>>(nn, alpha, x);
+    PF_CUDA(cudaGetLastError());
+    pl->launches++;
+    return 0;
+  }
+  for (size_t i = 0; i < nn; i++)
+    x[i] *= alpha;
+  return 0;
+}
+
+static int
+vec_reduce(pf_plan* pl, size_t nn, const double* x, const double* y, int mode,
+           double* result)
+{
+  PF_TRY(check_plan(pl));
+  Staged sx, sy;
+  PF_TRY(stage_in(pl, x, nn, sx));
+  if (y)
+    PF_TRY(stage_in(pl, y, nn, sy));
+  return reduce_dev(pl, nn, sx.dev, y ? sy.dev : nullptr, nullptr, mode, result);
+}
+
+int
+pf_vec_dot(pf_plan* pl, size_t nn, const double* x, const double* y,
+           double* result)
+{
+  return vec_reduce(pl, nn, x, y, 0, result);
+}
+int
+pf_vec_norm1(pf_plan* pl, size_t nn, const double* x, double* result)
+{
+  return vec_reduce(pl, nn, x, nullptr, 1, result);
+}
+int
+pf_vec_norminf(pf_plan* pl, size_t nn, const double* x, double* result)
+{
+  return vec_reduce(pl, nn, x, nullptr, 2, result);
+}
+
+int
+pf_device_alloc(pf_plan* pl, size_t bytes, void** ptr)
+{
+  PF_TRY(check_plan(pl));
+  cudaError_t e = cudaMalloc(ptr, bytes);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(PF_ERR_NOMEM, cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+int
+pf_device_free(pf_plan* pl, void* ptr)
+{
+  PF_TRY(check_plan(pl));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  PF_CUDA(cudaFree(ptr));
+  return 0;
+}
+
+int
+pf_memcpy(pf_plan* pl, void* dst, const void* src, size_t bytes)
+{
+  PF_TRY(check_plan(pl));
+  PF_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,106 @@
+// pf_inst.cu -- instantiates every pass kernel for one line length PF_N
+// (compiled once per N: -DPF_N=2 ... 1024) and exports one launcher.
+#include "pf_kernels.cuh"
+
+#ifndef PF_N
+#error "compile with -DPF_N=<line length>"
+#endif
+
+#define PF_CAT2(a, b) a##b
+#define PF_CAT(a, b) PF_CAT2(a, b)
+
+namespace pf {
+
+template <class Kern>
+static cudaError_t
+launch(Kern kern, const PassArgs& a, const cplx* tw2, long long blocks,
+       size_t smem, cudaStream_t st)
+{
+  if (blocks <= 0)
+    return cudaSuccess;
+  if (blocks > 0x7fffffffLL)
+    return cudaErrorInvalidConfiguration;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(
+      kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess)
+      return e;
+  }
+  kern<<<(unsigned)blocks, PF_THREADS, smem, st>>>(a, tw2);
+  return cudaGetLastError();
+}
+
+} // namespace pf
+
+using namespace pf;
+
+extern "C" int PF_CAT(pf_launch_n, PF_N)(int kind, const PassArgs* ap,
+                                         const void* tw2v, cudaStream_t st)
+{
+  constexpr int N = PF_N;
+  using K = KCfg<N>;
+  const PassArgs& a = *ap;
+  const cplx* tw2 = reinterpret_cast<const cplx*>(tw2v);
+  const long long ntA = (a.A + K::LPC - 1) / K::LPC;
+  const long long ntA2 = (a.A + 2 * K::LPC - 1) / (2 * K::LPC);
+  const long long nlines = (long long)a.A * a.B;
+  cudaError_t e = cudaErrorInvalidValue;
+  switch (kind) {
+    case K_GEN_TILE: {
+      const size_t sm = K::smem_tile(a.keep);
+      const long long nb = ntA * a.B;
+      if (a.noise_kind == NOISE_PHILOX_FAST)
+        e = launch(k_gen_tile<N, NOISE_PHILOX_FAST>, a, tw2, nb, sm, st);
+      else if (a.noise_kind == NOISE_PHILOX_F64)
+        e = launch(k_gen_tile<N, NOISE_PHILOX_F64>, a, tw2, nb, sm, st);
+      else
+        e = launch(k_gen_tile<N, NOISE_INJECTED>, a, tw2, nb, sm, st);
+      break;
+    }
+    case K_GEN_REIM: {
+      const size_t sm = K::exch_bytes;
+      const long long nb = ntA * a.B;
+      if (a.noise_kind == NOISE_PHILOX_FAST)
+        e = launch(k_gen_reim<N, NOISE_PHILOX_FAST>, a, tw2, nb, sm, st);
+      else if (a.noise_kind == NOISE_PHILOX_F64)
+        e = launch(k_gen_reim<N, NOISE_PHILOX_F64>, a, tw2, nb, sm, st);
+      else
+        e = launch(k_gen_reim<N, NOISE_INJECTED>, a, tw2, nb, sm, st);
+      break;
+    }
+    case K_C2T_INV:
+      e = launch(k_c2t<N, +1>, a, tw2, ntA * a.B, K::smem_tile(a.keep), st);
+      break;
+    case K_C2T_FWD:
+      e = launch(k_c2t<N, -1>, a, tw2, ntA * a.B, K::smem_tile(a.keep), st);
+      break;
+    case K_C2R:
+      e = launch(k_c2r<N>, a, tw2,
+                 ((nlines + 1) / 2 + K::LPC - 1) / K::LPC, K::exch_bytes, st);
+      break;
+    case K_R2C_LOAD:
+      e = launch(k_r2c<N, false>, a, tw2, ntA2 * a.B, K::smem_r2c(), st);
+      break;
+    case K_R2C_COV:
+      e = launch(k_r2c<N, true>, a, tw2, ntA2 * a.B, K::smem_r2c(), st);
+      break;
+    case K_LAMBDA:
+      e = launch(k_lambda<N, false>, a, tw2, (nlines + K::LPC - 1) / K::LPC,
+                 K::exch_bytes, st);
+      break;
+    case K_LAMBDA_COV:
+      e = launch(k_lambda<N, true>, a, tw2, (nlines + K::LPC - 1) / K::LPC,
+                 K::exch_bytes, st);
+      break;
+    case K_SPEC_TILE:
+      e = launch(k_spec<N, false>, a, tw2, ntA * a.B, K::smem_tile(a.keep),
+                 st);
+      break;
+    case K_SPEC_REIM:
+      e = launch(k_spec<N, true>, a, tw2, ntA * a.B, K::exch_bytes, st);
+      break;
+    default:
+      break;
+  }
+  return (int)e;
+}

@@ -1,0 +1,612 @@
+// pf_kernels.cuh -- the pass kernels of the circulant-embedding hot path.
+//
+// Every kernel processes "lines" of N complex doubles with the warp-level
+// FFT of pf_fft.cuh and differs only in how a line is produced (loader) and
+// consumed (storer).  Layout cycle (3D):
+//
+//   generate : sigma[k1][k0][k2] --A--> Y[k0][x2][k1] --B--> Z[x2][x1][k0]
+//              --C--> field[x2][x1][x0]
+//   forward  : field[x2][x1][x0] --F0--> U[x2][k0][x1] --F1--> V[k1][k0][x2]
+//              --F2 (x g(lambda)) + A--> Y[k0][x2][k1] --B--> --C-->
+//
+// Reads are always whole contiguous lines (one warp reads 512 B per
+// instruction); writes towards the next pass's contiguous axis go through a
+// shared-memory tile so that every store instruction covers LPC*16
+// contiguous bytes ("tile store").
+#pragma once
+#include "pf_args.h"
+#include "pf_fft.cuh"
+#include "pf_rng.cuh"
+
+namespace pf {
+
+constexpr int PF_THREADS = 128;
+
+template <int N>
+struct KCfg
+{
+  using C = LineCfg<N>;
+  static constexpr int E = C::E;
+  static constexpr int TPL = C::TPL;
+  static constexpr int LPC = PF_THREADS / TPL; // lines (FFTs) per CTA
+  static constexpr int SP = LPC + 1;           // stage pitch (odd)
+  static constexpr int ZP = N + 1;             // r2c stage pitch (odd)
+  static constexpr size_t exch_bytes = sizeof(cplx) * LPC * C::PITCH;
+  static __host__ __device__ constexpr size_t smem_tile(int keep)
+  {
+    size_t st = sizeof(cplx) * (size_t)keep * SP;
+    return st > exch_bytes ? st : exch_bytes;
+  }
+  static __host__ __device__ constexpr size_t smem_r2c()
+  {
+    size_t st = sizeof(cplx) * (size_t)LPC * ZP;
+    return st > exch_bytes ? st : exch_bytes;
+  }
+};
+
+// ---------------------------------------------------------------------------
+// value transforms, mutators.hh:36-118
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double
+apply_transform(double v, int kind, double lambda)
+{
+  switch (kind) {
+    case 1:
+      return exp(v);
+    case 2:
+      return fabs(v);
+    case 3:
+      return v < 0. ? -1. : 1.;
+    case 4:
+      return pow(v * lambda + 1, -lambda);
+    default:
+      return v;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// covariance on the torus, matrix.hh:624-648 + covariance.hh (same arithmetic
+// as the reference functors)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double
+cov_function(const CovParams& c, const double* x)
+{
+  const int dim = c.dim;
+  if (c.cov == COV_SEPARABLE_EXP) {
+    double sum = 0.;
+    for (int i = 0; i < dim; i++)
+      sum += fabs(x[i]);
+    return c.variance * exp(-sum);
+  }
+  if (c.cov == COV_WHITE_NOISE) {
+    for (int i = 0; i < dim; i++)
+      if (fabs(x[i]) > 1e-10)
+        return 0.;
+    return c.variance;
+  }
+  double sum = 0.;
+  for (int i = 0; i < dim; i++)
+    sum += x[i] * x[i];
+  const double h = sqrt(sum);
+  switch (c.cov) {
+    case COV_EXPONENTIAL:
+      return c.variance * exp(-h);
+    case COV_GAUSSIAN:
+      return c.variance * exp(-h * h);
+    case COV_SPHERICAL:
+      if (h > 1.)
+        return 0.;
+      if (dim == 3)
+        return c.variance * (1. - 1.5 * h + 0.5 * (h * h * h));
+      if (dim == 2)
+        return c.variance *
+               (1. - 2. / 3.14159265358979323846 *
+                       (h * sqrt(1. - h * h) + asin(h)));
+      return c.variance * (1. - h);
+    case COV_MATERN32:
+      return c.variance * (1. + sqrt(3.) * h) * exp(-sqrt(3.) * h);
+    case COV_MATERN52:
+      return c.variance * (1. + sqrt(5.) * h + 5. / 3. * h * h) *
+             exp(-sqrt(5.) * h);
+    case COV_DAMPED_OSC:
+      if (dim == 3)
+        return c.variance * exp(-h) * cos(h / sqrt(3.));
+      return c.variance * exp(-h) * cos(h);
+    case COV_GAMMA_EXP:
+      return c.variance * exp(-pow(h, c.p0));
+    case COV_CAUCHY: {
+      const double b = 1. + h * h;
+      return c.variance / (b * b * b);
+    }
+    case COV_GEN_CAUCHY:
+      return c.variance * pow(1. + pow(h, c.p0), -c.p1);
+    case COV_CUBIC: {
+      if (h > 1.)
+        return 0.;
+      const double h2 = h * h, h3 = h2 * h, h5 = h3 * h2, h7 = h5 * h2;
+      return c.variance *
+             (1. - 7. * h2 + 8.75 * h3 - 3.5 * h5 + 0.75 * h7);
+    }
+  }
+  return 0.;
+}
+
+// torus cell (i0,i1,i2) -> covariance value
+__device__ __forceinline__ double
+cov_torus(const CovParams& c, unsigned i0, unsigned i1, unsigned i2)
+{
+  double coord[3], tc[3];
+  const unsigned idx[3] = { i0, i1, i2 };
+  for (int i = 0; i < c.dim; i++) {
+    coord[i] = idx[i] * c.h[i];
+    if (coord[i] > c.half[i])
+      coord[i] -= c.period[i];
+  }
+  if (c.aniso == 0) {
+    for (int i = 0; i < c.dim; i++)
+      tc[i] = c.g[0] * coord[i];
+  } else if (c.aniso == 1) {
+    for (int i = 0; i < c.dim; i++)
+      tc[i] = c.g[i] * coord[i];
+  } else {
+    for (int i = 0; i < c.dim; i++) {
+      tc[i] = 0.;
+      for (int j = 0; j < c.dim; j++)
+        tc[i] += c.g[i * c.dim + j] * coord[j];
+    }
+  }
+  return cov_function(c, tc);
+}
+
+// ---------------------------------------------------------------------------
+// loaders
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ const double*
+table_row(const PassArgs& p, int a, int b)
+{
+  const int am = (p.tab_mirror_a && a > p.tab_mirror_a / 2) ? p.tab_mirror_a - a
+                                                            : a;
+  return p.tab + ((long long)am * p.rma + (long long)b * p.rmb) * p.tab_pitch;
+}
+
+// white noise scaled by sigma.  Follows Matrix::generateField's loop
+// (matrix.hh:396-421) and FieldBackend::set (r2cfieldbackend.hh:305-325,
+// dftfieldbackend.hh:276-280); the table holds sqrt(lambda)/sqrt(2)
+// (hermitian) or sqrt(lambda) (DFT backend rule).
+template <int N, int NOISE>
+__device__ __forceinline__ void
+load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
+           bool valid)
+{
+  using C = LineCfg<N>;
+  constexpr int H = C::E / 2;
+  constexpr double SQRT2 = 1.41421356237309504880168872420969808;
+  if (!valid) {
+#pragma unroll
+    for (int q = 0; q < C::E; q++)
+      v[q] = make_double2(0., 0.);
+    return;
+  }
+  const double* row = table_row(p, a, b);
+  const bool a_self = (2 * a) % p.na_self == 0;
+  const bool b_self = (2 * b) % p.nb_self == 0;
+  const bool line_self = p.hermitian && a_self && b_self;
+  const bool plane = p.hermitian && p.corrected &&
+                     (p.plane_axis == 0 ? a_self : b_self);
+  const double boost = plane ? SQRT2 : 1.0;
+  const unsigned long long cbase =
+    (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
+  const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
+#pragma unroll
+  for (int q = 0; q < H; q++) {
+    const int e = t + C::TPL * q; // < N/2
+    const int e2 = e + N / 2;
+    const double s1 = __ldg(row + e) * boost;
+    const double s2 = __ldg(row + (p.tab_mirror_e ? N / 2 - e : e2)) * boost;
+    double2 n1, n2;
+    if constexpr (NOISE == NOISE_INJECTED) {
+      n1 = __ldg(p.noise + ibase + (long long)e * p.ime);
+      n2 = __ldg(p.noise + ibase + (long long)e2 * p.ime);
+    } else {
+      const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
+      uint4 w = philox4x32_10(ctr, p.realization, p.seed);
+      if constexpr (NOISE == NOISE_PHILOX_FAST) {
+        n1 = box_muller_fast(w.x, w.y);
+        n2 = box_muller_fast(w.z, w.w);
+      } else {
+        n1 = box_muller_f64(w.x, w.y);
+        n2 = box_muller_f64(w.z, w.w);
+      }
+    }
+    cplx x1 = make_double2(s1 * n1.x, s1 * n1.y);
+    cplx x2 = make_double2(s2 * n2.x, s2 * n2.y);
+    if (e == 0 && line_self) {
+      // self-conjugate entries (e = 0 and e2 = N/2): real, full weight
+      const double f = plane ? 1.0 : SQRT2;
+      x1 = make_double2(x1.x * f, 0.);
+      x2 = make_double2(x2.x * f, 0.);
+    }
+    v[q] = x1;
+    v[q + H] = x2;
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void
+load_contig(cplx (&v)[LineCfg<N>::E], const cplx* __restrict__ line, int t,
+            int n_valid, bool valid)
+{
+  using C = LineCfg<N>;
+#pragma unroll
+  for (int q = 0; q < C::E; q++) {
+    const int e = t + C::TPL * q;
+    v[q] = (valid && e < n_valid) ? __ldg(line + e) : make_double2(0., 0.);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// storers
+// ---------------------------------------------------------------------------
+// tile store: out[base + e*ose + l], l = line in tile (contiguous), e < keep
+template <int N>
+__device__ __forceinline__ void
+tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
+           cplx* __restrict__ out, long long base, long long ose,
+           int lines_valid, double scale)
+{
+  using K = KCfg<N>;
+  __syncthreads(); // exchange area is about to be reused as the stage
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    if (e < keep)
+      stage[e * K::SP + lic] = make_double2(v[q].x * scale, v[q].y * scale);
+  }
+  __syncthreads();
+  const int total = keep * K::LPC;
+  for (int idx = threadIdx.x; idx < total; idx += PF_THREADS) {
+    const int l = idx % K::LPC, e = idx / K::LPC;
+    if (l < lines_valid)
+      out[base + (long long)e * ose + l] = stage[e * K::SP + l];
+  }
+}
+
+// ===========================================================================
+// kernels
+// ===========================================================================
+
+// pass A: noise -> inverse FFT -> tile
+template <int N, int NOISE>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  const int ntA = (p.A + K::LPC - 1) / K::LPC;
+  const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
+  const int a = at * K::LPC + lic;
+  cplx v[K::E];
+  load_noise<N, NOISE>(v, p, a, b, t, a < p.A);
+  line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
+  const int lv = min(K::LPC, p.A - at * K::LPC);
+  tile_store<N>(v, sm, lic, t, p.keep, reinterpret_cast<cplx*>(p.out),
+                (long long)b * p.osb + (long long)at * K::LPC, p.ose, lv,
+                p.scale);
+}
+
+// 1D: noise -> inverse FFT -> real part / imaginary part lines
+template <int N, int NOISE>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_gen_reim(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  const int ntA = (p.A + K::LPC - 1) / K::LPC;
+  const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
+  const int a = at * K::LPC + lic;
+  const bool valid = a < p.A;
+  cplx v[K::E];
+  load_noise<N, NOISE>(v, p, a, b, t, valid);
+  line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
+  if (!valid)
+    return;
+  const long long line = (long long)b * p.A + a;
+  double* o1 = reinterpret_cast<double*>(p.out);
+  double* o2 = reinterpret_cast<double*>(p.out2);
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    if (e < p.keep) {
+      if (o1)
+        o1[line * p.out_pitch + e] =
+          apply_transform(v[q].x * p.scale, p.transform, p.tparam);
+      if (o2)
+        o2[line * p.out_pitch + e] = v[q].y * p.scale;
+    }
+  }
+}
+
+// contiguous complex lines -> FFT -> tile (pass B, F1, E1)
+template <int N, int DIR>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_c2t(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  const int ntA = (p.A + K::LPC - 1) / K::LPC;
+  const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
+  const int a = at * K::LPC + lic;
+  cplx v[K::E];
+  const cplx* line = reinterpret_cast<const cplx*>(p.in) +
+                     (long long)a * p.isa + (long long)b * p.isb;
+  load_contig<N>(v, line, t, p.n_valid, a < p.A);
+  line_fft<N, DIR>(v, sm + lic * K::C::PITCH, t, tw2);
+  const int lv = min(K::LPC, p.A - at * K::LPC);
+  tile_store<N>(v, sm, lic, t, p.keep, reinterpret_cast<cplx*>(p.out),
+                (long long)b * p.osb + (long long)at * K::LPC, p.ose, lv,
+                p.scale);
+}
+
+// pass C: two half-spectrum lines (m0 = N/2+1 complex each) -> one complex
+// inverse FFT -> two real lines, restricted to e < keep, value transform
+// fused.  c2r semantics of FFTW on non-Hermitian input: Im at k0 in {0,N/2}
+// is ignored (r2cfieldbackend.hh:250-274).
+template <int N>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_c2r(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  const long long f = (long long)blockIdx.x * K::LPC + lic;
+  const long long L0 = 2 * f, L1 = 2 * f + 1;
+  const long long nl = (long long)p.A * p.B;
+  const bool v0 = L0 < nl, v1 = L1 < nl;
+  const cplx* in = reinterpret_cast<const cplx*>(p.in);
+  const cplx* la = in + L0 * p.isa;
+  const cplx* lb = in + L1 * p.isa;
+  cplx v[K::E];
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    const int kk = e <= N / 2 ? e : N - e;
+    const cplx xa = v0 ? __ldg(la + kk) : make_double2(0., 0.);
+    const cplx xb = v1 ? __ldg(lb + kk) : make_double2(0., 0.);
+    if (e == 0 || 2 * e == N)
+      v[q] = make_double2(xa.x, xb.x);
+    else if (e < N / 2)
+      v[q] = make_double2(xa.x - xb.y, xa.y + xb.x);
+    else
+      v[q] = make_double2(xa.x + xb.y, xb.x - xa.y);
+  }
+  line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
+  double* out = reinterpret_cast<double*>(p.out);
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    if (e < p.keep) {
+      if (v0)
+        out[L0 * p.out_pitch + e] =
+          apply_transform(v[q].x * p.scale, p.transform, p.tparam);
+      if (v1)
+        out[L1 * p.out_pitch + e] =
+          apply_transform(v[q].y * p.scale, p.transform, p.tparam);
+    }
+  }
+}
+
+// F0 / E0: two real lines (loaded or covariance-evaluated) -> one complex
+// forward FFT -> split into the two half spectra -> tile store.
+// Lines a (tile axis, pairs a, a+1), b; element e = x0.
+template <int N, bool COV>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_r2c(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  constexpr int LT = 2 * K::LPC; // real lines per tile
+  const int ntA = (p.A + LT - 1) / LT;
+  const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
+  const int a0 = at * LT + 2 * lic, a1 = a0 + 1;
+  const bool v0 = a0 < p.A, v1 = a1 < p.A;
+  cplx v[K::E];
+  if constexpr (COV) {
+    unsigned ia[3] = { 0, 0, 0 }, ib[3] = { 0, 0, 0 };
+    if (p.cov_axis_a >= 0) {
+      ia[p.cov_axis_a] = a0;
+      ib[p.cov_axis_a] = a1;
+    }
+    if (p.cov_axis_b >= 0) {
+      ia[p.cov_axis_b] = b;
+      ib[p.cov_axis_b] = b;
+    }
+#pragma unroll 4
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      v[q].x = v0 ? cov_torus(p.cov, e, ia[1], ia[2]) : 0.;
+      v[q].y = v1 ? cov_torus(p.cov, e, ib[1], ib[2]) : 0.;
+    }
+  } else {
+    const double* in = reinterpret_cast<const double*>(p.in);
+    const double* l0 = in + (long long)a0 * p.isa + (long long)b * p.isb;
+    const double* l1 = in + (long long)a1 * p.isa + (long long)b * p.isb;
+#pragma unroll
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      v[q].x = (v0 && e < p.n_valid) ? __ldg(l0 + e) : 0.;
+      v[q].y = (v1 && e < p.n_valid) ? __ldg(l1 + e) : 0.;
+    }
+  }
+  line_fft<N, -1>(v, sm + lic * K::C::PITCH, t, tw2);
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < K::E; q++)
+    sm[lic * K::ZP + t + K::TPL * q] = v[q];
+  __syncthreads();
+  cplx* out = reinterpret_cast<cplx*>(p.out);
+  const long long base = (long long)b * p.osb + (long long)at * LT;
+  const int lv = min(LT, p.A - at * LT);
+  const int total = p.keep * LT;
+  for (int idx = threadIdx.x; idx < total; idx += PF_THREADS) {
+    const int l = idx % LT, k = idx / LT;
+    if (l < lv) {
+      const cplx zk = sm[(l >> 1) * K::ZP + k];
+      const cplx zm = sm[(l >> 1) * K::ZP + ((N - k) & (N - 1))];
+      cplx r;
+      if ((l & 1) == 0)
+        r = make_double2(0.5 * (zk.x + zm.x), 0.5 * (zk.y - zm.y));
+      else
+        r = make_double2(0.5 * (zk.y + zm.y), 0.5 * (zm.x - zk.x));
+      out[base + (long long)k * p.ose + l] =
+        make_double2(r.x * p.scale, r.y * p.scale);
+    }
+  }
+}
+
+__device__ __forceinline__ unsigned long long
+ordered_bits(double v)
+{
+  const unsigned long long u = (unsigned long long)__double_as_longlong(v);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+
+// E2: contiguous complex lines -> forward FFT -> eigenvalues: real part,
+// scale 1/N_ext, census and clamp (matrix.hh:283-306), contiguous store of
+// the first `keep` entries.  COV1D: the line is evaluated from the covariance
+// (1D DFT matrix backend, dftmatrixbackend.hh:209-238).
+template <int N, bool COV1D>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_lambda(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  const long long line = (long long)blockIdx.x * K::LPC + lic;
+  const long long nl = (long long)p.A * p.B;
+  const bool valid = line < nl;
+  cplx v[K::E];
+  if constexpr (COV1D) {
+#pragma unroll 4
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      v[q] = make_double2(valid ? cov_torus(p.cov, e, 0, 0) : 0., 0.);
+    }
+  } else {
+    load_contig<N>(v, reinterpret_cast<const cplx*>(p.in) + line * p.isa, t,
+                   p.n_valid, valid);
+  }
+  line_fft<N, -1>(v, sm + lic * K::C::PITCH, t, tw2);
+  unsigned nsmall = 0, nzero = 0, nneg = 0;
+  double smallest = 1.7976931348623157e308;
+  double* out = reinterpret_cast<double*>(p.out);
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    if (valid && e < p.keep) {
+      double val = v[q].x * p.scale;
+      if (val < smallest)
+        smallest = val;
+      if (val < 1e-6) {
+        if (val < p.threshold) {
+          if (val > -p.threshold)
+            nzero++;
+          else
+            nneg++;
+        } else
+          nsmall++;
+      }
+      if (val < 0.)
+        val = 0.;
+      out[line * p.out_pitch + e] = val;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    nsmall += __shfl_xor_sync(0xffffffffu, nsmall, o);
+    nzero += __shfl_xor_sync(0xffffffffu, nzero, o);
+    nneg += __shfl_xor_sync(0xffffffffu, nneg, o);
+    smallest = fmin(smallest, __shfl_xor_sync(0xffffffffu, smallest, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (nsmall)
+      atomicAdd(p.census + 0, (unsigned long long)nsmall);
+    if (nzero)
+      atomicAdd(p.census + 1, (unsigned long long)nzero);
+    if (nneg)
+      atomicAdd(p.census + 2, (unsigned long long)nneg);
+    atomicMin(p.smallest_bits, ordered_bits(smallest));
+  }
+}
+
+// F2 + A fused: contiguous complex line -> forward FFT -> * g(lambda)*scale
+// -> inverse FFT -> tile store (fieldBackend.mult between forwardTransform
+// and backwardTransform, matrix.hh:1495-1513).  REAL1D: 1D variant, real
+// input line, real output line (DFT field backend, component 0).
+template <int N, bool REAL1D>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_spec(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  const int ntA = (p.A + K::LPC - 1) / K::LPC;
+  const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
+  const int a = at * K::LPC + lic;
+  const bool valid = a < p.A;
+  cplx v[K::E];
+  if constexpr (REAL1D) {
+    const double* line = reinterpret_cast<const double*>(p.in) +
+                         (long long)a * p.isa + (long long)b * p.isb;
+#pragma unroll
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      v[q] = make_double2((valid && e < p.n_valid) ? __ldg(line + e) : 0., 0.);
+    }
+  } else {
+    const cplx* line = reinterpret_cast<const cplx*>(p.in) +
+                       (long long)a * p.isa + (long long)b * p.isb;
+    load_contig<N>(v, line, t, p.n_valid, valid);
+  }
+  line_fft<N, -1>(v, sm + lic * K::C::PITCH, t, tw2);
+  if (valid) {
+    const double* row = table_row(p, a, b);
+#pragma unroll
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      const int em = (p.tab_mirror_e && e > N / 2) ? N - e : e;
+      const double g = __ldg(row + em) * p.scale;
+      v[q] = make_double2(v[q].x * g, v[q].y * g);
+    }
+  }
+  line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
+  if constexpr (REAL1D) {
+    if (valid) {
+      double* o1 = reinterpret_cast<double*>(p.out);
+      const long long line = (long long)b * p.A + a;
+#pragma unroll
+      for (int q = 0; q < K::E; q++) {
+        const int e = t + K::TPL * q;
+        if (e < p.keep)
+          o1[line * p.out_pitch + e] = v[q].x;
+      }
+    }
+  } else {
+    const int lv = min(K::LPC, p.A - at * K::LPC);
+    tile_store<N>(v, sm, lic, t, p.keep, reinterpret_cast<cplx*>(p.out),
+                  (long long)b * p.osb + (long long)at * K::LPC, p.ose, lv,
+                  1.0);
+  }
+}
+
+} // namespace pf

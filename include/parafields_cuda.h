@@ -1,0 +1,214 @@
+/* parafields_cuda.h -- C ABI of libparafields_cuda.so
+ *
+ * B200-native (sm_100a) replacement for the sampling hot path of
+ * parafields-core: the covariance operator `parafields::Matrix`
+ * (ext/parafields-core/include/parafields/matrix.hh:59-1663) together with the
+ * matrix / field / RNG backends it drives
+ * (.../backends/{dct,r2c,dft}matrixbackend.hh, {r2c,dft}fieldbackend.hh,
+ * cpprngbackend.hh, fftwwrapper.hh).
+ *
+ * Conventions
+ *  - every function returns 0 on success, a pf_status otherwise; nothing
+ *    throws across the boundary; pf_last_error() returns the message of the
+ *    last failure on the calling thread.  Messages reuse the reference's
+ *    exception texts where one exists (e.g. "negative eigenvalues in
+ *    covariance matrix", matrix.hh:327).
+ *  - `double*` data arguments may point to host OR device memory (detected
+ *    with cudaPointerGetAttributes); fields are dense, dimension 0 fastest:
+ *    index = i0 + c0*(i1 + c1*i2)  (fieldtraits.hh:397-405).
+ *  - a plan is not thread safe; calls are synchronous on return unless the
+ *    data pointers are device pointers, in which case work is only enqueued
+ *    on the plan's stream (pf_plan_set_stream / pf_plan_synchronize).
+ *  - there is no CPU fallback: without a CUDA device every compute entry
+ *    point fails with PF_ERR_CUDA.
+ */
+#ifndef PARAFIELDS_CUDA_H
+#define PARAFIELDS_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pf_plan pf_plan;
+
+typedef enum pf_status
+{
+  PF_OK = 0,
+  PF_ERR_INVALID = 1,              /* bad argument / unsupported size      */
+  PF_ERR_NEGATIVE_EIGENVALUES = 2, /* matrix.hh:322-328                    */
+  PF_ERR_CUDA = 3,                 /* CUDA runtime failure / no device     */
+  PF_ERR_NOMEM = 4
+} pf_status;
+
+/* stochastic.covariance, names as in matrix.hh:241-266 */
+typedef enum pf_covariance
+{
+  PF_COV_EXPONENTIAL = 0,
+  PF_COV_GAUSSIAN = 1,
+  PF_COV_SPHERICAL = 2,
+  PF_COV_SEPARABLE_EXPONENTIAL = 3,
+  PF_COV_MATERN32 = 4,
+  PF_COV_MATERN52 = 5,
+  PF_COV_DAMPED_OSCILLATION = 6,
+  PF_COV_GAMMA_EXPONENTIAL = 7,
+  PF_COV_CAUCHY = 8,
+  PF_COV_GENERALIZED_CAUCHY = 9,
+  PF_COV_CUBIC = 10,
+  PF_COV_WHITE_NOISE = 11
+} pf_covariance;
+
+/* stochastic.anisotropy, matrix.hh:496-508 */
+typedef enum pf_anisotropy
+{
+  PF_ANISO_NONE = 0,
+  PF_ANISO_AXIPARALLEL = 1,
+  PF_ANISO_GEOMETRIC = 2
+} pf_anisotropy;
+
+/* randomField.transform, mutators.hh:137-155 */
+typedef enum pf_transform_kind
+{
+  PF_TRANSFORM_NONE = 0,
+  PF_TRANSFORM_LOG_NORMAL = 1,
+  PF_TRANSFORM_FOLDED_NORMAL = 2,
+  PF_TRANSFORM_SIGN = 3,
+  PF_TRANSFORM_BOX_COX = 4
+} pf_transform_kind;
+
+typedef enum pf_op
+{
+  PF_OP_MATRIX = 0,      /* Matrix::operator*,   matrix.hh:151,1459-1517  */
+  PF_OP_ROOT = 1,        /* multiplyRoot,        matrix.hh:176,1530-1589  */
+  PF_OP_INVERSE_EXT = 2  /* multiplyInverseExtended, matrix.hh:1603-1662  */
+} pf_op;
+
+typedef enum pf_lambda_layout
+{
+  PF_LAMBDA_NATURAL = 0, /* field-backend index set, natural order:
+                            (m0,n1,n2) half spectrum, k0 fastest; n0 in 1D */
+  PF_LAMBDA_REFERENCE = 1 /* as stored by the reference's matrix backend
+                            after finalize(): DCT compact / R2C half spectrum
+                            (last two dims swapped in 3D) / DFT full        */
+} pf_lambda_layout;
+
+/* Configuration = the ini keys the hot path reads
+ * (fieldtraits.hh:166-206, matrix.hh:283-284,496-508, covariance.hh,
+ * mutators.hh:137-155).  Fill with pf_desc_default() first. */
+typedef struct pf_desc
+{
+  int dim;                  /* 1..3 = number of grid.extensions entries      */
+  unsigned cells[3];        /* grid.cells                                     */
+  double extensions[3];     /* grid.extensions                                */
+  unsigned embedding_factor; /* embedding.factor (default 2)                  */
+  int covariance;           /* pf_covariance                                  */
+  double variance;          /* stochastic.variance                            */
+  double cov_param[2];      /* expGamma | cauchyAlpha, cauchyBeta             */
+  int anisotropy;           /* pf_anisotropy                                  */
+  double corr_length[9];    /* stochastic.corrLength: 1 | dim | dim*dim
+                               numbers, row major (NOT inverted)              */
+  double threshold;         /* embedding.threshold (1e-14)                    */
+  int approximate;          /* embedding.approximate                          */
+  int periodic;             /* randomField.periodic (forces factor 1)         */
+  int transform;            /* pf_transform_kind                              */
+  double boxcox_lambda;     /* transform.boxCoxLambda                         */
+  unsigned cg_iterations;   /* randomField.cgIterations (100)                 */
+  int parity_mode;          /* 0 reference sampler, 1 corrected  */
+  int rng_mode;             /* 0 Philox + fp32 Box-Muller, 1 fp64 Box-Muller  */
+  int census_quirk;         /* 1: R2C census walks interleaved re/im of the
+                               first half like the reference (Appendix C.3)   */
+  unsigned max_factor;      /* embedding-factor retry bound, 0 = no retry     */
+  int device;               /* CUDA device ordinal, -1 = current              */
+} pf_desc;
+
+/* eigenvalue census, matrix.hh:283-320 */
+typedef struct pf_eig_stats
+{
+  unsigned long long small_count;    /* thr <= v < 1e-6   */
+  unsigned long long zero_count;     /* |v| < thr         */
+  unsigned long long negative_count; /* v <= -thr         */
+  double smallest;
+  unsigned factor_used;              /* after retries     */
+} pf_eig_stats;
+
+const char* pf_version(void);
+const char* pf_last_error(void);
+int pf_device_count(void);
+/* name (<=256 bytes), SM count, memory bytes of a device */
+int pf_device_info(int device, char* name, int* sm_count, size_t* mem_bytes);
+
+void pf_desc_default(pf_desc* desc);
+
+/* Matrix(traits) + update(), matrix.hh:106-142: sizes, tables, streams. */
+int pf_plan_create(const pf_desc* desc, pf_plan** plan);
+int pf_plan_destroy(pf_plan* plan);
+/* cudaStream_t as void*; NULL = default stream */
+int pf_plan_set_stream(pf_plan* plan, void* cuda_stream);
+int pf_plan_synchronize(pf_plan* plan);
+/* number of kernels this plan has launched so far */
+unsigned long long pf_plan_launch_count(const pf_plan* plan);
+
+/* sizes: Traits::{domainSize, extendedDomainSize} (fieldtraits.hh:284-296),
+ * FieldBackend::localFieldSize() (r2cfieldbackend.hh:151) */
+size_t pf_domain_size(const pf_plan* plan);
+size_t pf_extended_size(const pf_plan* plan);
+size_t pf_noise_entries(const pf_plan* plan);
+
+/* Matrix::fillTransformedMatrix, matrix.hh:232-331 (lazy in every other
+ * entry point, like matrixBackend.valid()).  Returns
+ * PF_ERR_NEGATIVE_EIGENVALUES exactly when the reference throws. */
+int pf_compute_eigenvalues(pf_plan* plan, pf_eig_stats* stats);
+size_t pf_eigenvalue_count(const pf_plan* plan, int layout);
+int pf_get_eigenvalues(pf_plan* plan, double* out, size_t count, int layout);
+
+/* Matrix::generateField, matrix.hh:343-438, with device Philox noise keyed by
+ * (seed, realization).  apply_transform fuses ValueTransform::apply
+ * (randomfield.hh:600) into the last pass.  In 1D the DFT backend's spare
+ * field protocol (matrix.hh:349,428-437) is kept: every second call returns
+ * the imaginary part of the previous transform. */
+int pf_generate(pf_plan* plan, uint64_t seed, uint64_t realization,
+                double* out, int apply_transform);
+/* `count` realizations first..first+count-1 into out[count][domain] */
+int pf_generate_batch(pf_plan* plan, uint64_t seed, uint64_t first,
+                      size_t count, double* out, int apply_transform);
+/* same arithmetic with caller-supplied white noise: 2*pf_noise_entries()
+ * doubles (r1,r2 interleaved) in the reference's stream order
+ * (SURVEY Appendix A.5).  spare may be NULL (1D: imaginary part). */
+int pf_generate_from_noise(pf_plan* plan, const double* noise, double* out,
+                           double* spare);
+/* Matrix::generateUncorrelatedField, matrix.hh:450-462 (device Philox) */
+int pf_generate_uncorrelated(pf_plan* plan, uint64_t seed, double* out);
+/* Matrix::setVarianceAsField, matrix.hh:473-479 */
+int pf_set_variance_as_field(pf_plan* plan, double* out);
+
+/* multiplyExtended / multiplyRootExtended / multiplyInverseExtended */
+int pf_apply(pf_plan* plan, int op, const double* in, double* out);
+/* Matrix::multiplyInverse + innerCG, matrix.hh:198-215,1331-1448 */
+int pf_solve(pf_plan* plan, const double* in, double* out,
+             unsigned* iterations);
+
+/* ValueTransform::apply over n values (mutators.hh:161) */
+int pf_transform(pf_plan* plan, const double* in, double* out, size_t n);
+
+/* StochasticPart vector space operations (stochastic.hh:320-467,762-787) on
+ * device or host arrays of n doubles */
+int pf_vec_axpy(pf_plan* plan, size_t n, double alpha, const double* x,
+                double* y);                       /* y += alpha x */
+int pf_vec_scale(pf_plan* plan, size_t n, double alpha, double* x);
+int pf_vec_dot(pf_plan* plan, size_t n, const double* x, const double* y,
+               double* result);
+int pf_vec_norm1(pf_plan* plan, size_t n, const double* x, double* result);
+int pf_vec_norminf(pf_plan* plan, size_t n, const double* x, double* result);
+
+/* device memory helpers so that a host-only caller (C++, cgo, ctypes) can
+ * keep fields resident in HBM */
+int pf_device_alloc(pf_plan* plan, size_t bytes, void** ptr);
+int pf_device_free(pf_plan* plan, void* ptr);
+int pf_memcpy(pf_plan* plan, void* dst, const void* src, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PARAFIELDS_CUDA_H */
