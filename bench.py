@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py -- realizations/s of the circulant-embedding sampler on B200.
+
+Contract (see the task statement): `python bench.py --gpus N --steps K
+--warmup W` prints ONE JSON line from rank 0.  A "step" is one realization of
+the workload per GPU (K3 of SURVEY.md section 8: 3D 512^3 cells, spherical
+covariance, corrLength 0.1, embedding factor 2 -> 1024^3 fp64 torus).
+
+  value        whole-job realizations/s, fields stay in HBM, timed with CUDA
+               events on the launching stream, max over ranks
+  e2e          same metric through the public API with a HOST (pinned) output
+               buffer: the device->host copy of every field is inside the
+               timed region (the only per-step input is the (seed,
+               realization) pair passed by value)
+  roofline     dominant kernel (pass A: Philox noise * sqrt(lambda) + inverse
+               FFT along the last axis), algorithmic bytes / measured launch
+               duration against MEASURED_PEAKS.json
+  cpu_baseline the CPU oracle (single thread = one MPI rank of the reference)
+               on a bounded sample of the same workload
+
+Multi-GPU (N>1, launched by torch.distributed.run): realizations are
+independent given (seed, realization), so ranks generate disjoint realization
+indices with no data-path collective ("replicas", weak scaling).
+
+`--impl reference` times the CPU restatement of the reference path
+(oracle/, all host threads) -- the reference itself cannot be built in this
+image (needs FFTW3-MPI, MPI, dune-common).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # SURVEY.md 8(d) synthetic inputs
+    "K3": dict(cells=[512, 512, 512], covariance="spherical", corr_length=0.1, label="3D 512^3 spherical l=0.1, factor 2 (1024^3 fp64 torus)"),
+    "K2": dict(cells=[256, 256, 256], covariance="gaussian", corr_length=[0.05, 0.03, 0.02], anisotropy="axiparallel", transform="logNormal", approximate=True, label="3D 256^3 gaussian axiparallel + logNormal (512^3 torus)"),
+    "K1": dict(cells=[512, 512], covariance="exponential", corr_length=0.05, label="2D 512^2 exponential l=0.05 (1024^2 torus)"),
+    "K5": dict(cells=[256, 256, 256], covariance="exponential", corr_length=0.05, label="3D 256^3 exponential (512^3 torus)"),
+    "S3": dict(cells=[128, 128, 128], covariance="spherical", corr_length=0.1, label="3D 128^3 spherical (256^3 torus)"),
+}
+
+
+def algorithmic_bytes(cells, factor=2, compact=True):
+    """bytes per realization of the pruned pass pipeline and
+    of its dominant kernel (pass A)."""
+    c = list(cells)
+    n = [factor * x for x in c]
+    m0 = n[0] // 2 + 1
+    if len(c) == 3:
+        lam = 8 * ((n[0] // 2 + 1) * (n[1] // 2 + 1) * (n[2] // 2 + 1) if compact else m0 * n[1] * n[2])
+        a_w = 16 * m0 * n[1] * c[2]
+        b_w = 16 * m0 * c[1] * c[2]
+        c_w = 8 * c[0] * c[1] * c[2]
+        total = lam + 2 * a_w + 2 * b_w + c_w
+        return dict(total=total, pass_a=lam + a_w, pass_b=a_w + b_w, pass_c=b_w + c_w)
+    if len(c) == 2:
+        lam = 8 * ((n[0] // 2 + 1) * (n[1] // 2 + 1) if compact else m0 * n[1])
+        a_w = 16 * m0 * c[1]
+        c_w = 8 * c[0] * c[1]
+        return dict(total=lam + 2 * a_w + c_w, pass_a=lam + a_w, pass_b=0, pass_c=a_w + c_w)
+    return dict(total=8 * n[0] + 16 * c[0], pass_a=8 * n[0] + 16 * c[0], pass_b=0, pass_c=0)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE,
+                stderr=subprocess.DEVNULL,
+                text=True,
+            )
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax.append(float(f[1]))
+                power.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return dict(
+            sm_mhz=float(np.median(sm)) if sm else None,
+            sm_max_mhz=max(smax) if smax else None,
+            power_w_max=max(power) if power else None,
+            samples=len(sm),
+            reasons=sorted(reasons),
+        )
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)), "measured"
+        except Exception:
+            pass
+    return dict(hbm_gbs=6650.0), "fallback"
+
+
+def cpu_sample_config(wl):
+    """Bounded CPU sample of a workload: same covariance, 1/4 of the cells per
+    dimension in 3D (1/64 of the work), 1/2 in 2D."""
+    cfg = {k: v for k, v in WORKLOADS[wl].items() if k not in ("label", "transform")}
+    cells = cfg["cells"]
+    if len(cells) == 3 and cells[0] >= 512:
+        div = 2
+    elif len(cells) == 3 and cells[0] >= 256:
+        div = 2
+    else:
+        div = 1
+    cfg["cells"] = [c // div for c in cells]
+    scale = float(np.prod(cells)) / float(np.prod(cfg["cells"]))
+    return cfg, scale
+
+
+def time_oracle(wl, threads, reps):
+    """seconds per realization of the CPU oracle on the bounded sample."""
+    from oracle import oracle_lib as ol
+
+    cfg, scale = cpu_sample_config(wl)
+    o = ol.Oracle(threads=threads, **cfg)
+    t0 = time.perf_counter()
+    o.eigenvalues()
+    t_eig = time.perf_counter() - t0
+    times = []
+    # `threads` emulates an MPI run of the reference with that many ranks:
+    # rank r draws its slab of the noise stream with seed + r
+    ranks = threads
+    while ranks > 1 and o.noise_entries % ranks:
+        ranks -= 1
+    for r in range(reps):
+        t0 = time.perf_counter()
+        noise = o.reference_noise_ranks(20240611 + r, ranks)  # RNG stream(s)
+        o.generate_from_noise(noise)  # sqrt(lambda) loop + c2r + restrict
+        times.append(time.perf_counter() - t0)
+    return min(times), scale, cfg, t_eig
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement with all host threads."""
+    if rank != 0:
+        return
+    from oracle import oracle_lib as ol
+
+    threads = max(1, os.cpu_count() or 1)
+    threads = min(threads, ol.lib().orc_max_threads()) if hasattr(ol.lib(), "orc_max_threads") else threads
+    steps = max(1, args.steps)
+    # warm-up + timed steps on the bounded sample
+    t_warm, scale, cfg, t_eig = time_oracle(args.workload, threads, max(1, min(args.warmup, 1)))
+    t0 = time.perf_counter()
+    t_step, _, _, _ = time_oracle(args.workload, threads, min(steps, 3))
+    wall = time.perf_counter() - t0
+    value = 1.0 / (t_step * scale)
+    sample = "one realization of %s cells (1/%d of the workload's cells), linear scaling to the full size; eigenvalue setup %.1fs excluded" % (
+        "x".join(map(str, cfg["cells"])),
+        int(scale),
+        t_eig,
+    )
+    line = dict(
+        impl="reference",
+        metric="realizations/sec",
+        value=value,
+        unit="realizations/s",
+        n_gpus=args.gpus,
+        steps=args.steps,
+        warmup=args.warmup,
+        ms_per_step=1e3 * t_step * scale,
+        higher_is_better=True,
+        scaling="weak",
+        vs_baseline=None,
+        dtype="f64",
+        data="synthetic",
+        config=dict(workload=WORKLOADS[args.workload]["label"], name=args.workload),
+        cpu_baseline=dict(value=value, unit="realizations/s", cores=threads, kind="port", sample=sample),
+        e2e=dict(value=value, unit="realizations/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+        note="reference = CPU restatement of parafields-core (oracle/pf_oracle.cpp, OpenMP over FFT lines); the real reference needs FFTW3-MPI/MPI/dune-common, absent here",
+    )
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="K3", choices=sorted(WORKLOADS))
+    ap.add_argument("--rng", default="fast", choices=["fast", "fp64"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    distributed = world > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    pfb = importlib.import_module("dune-parafields_b200")
+    wl = {k: v for k, v in WORKLOADS[args.workload].items() if k != "label"}
+    plan = pfb.Plan(device=local_rank, rng_mode=args.rng, **wl)
+    stream = torch.cuda.Stream()
+    plan.set_stream(stream)
+
+    t0 = time.perf_counter()
+    stats = plan.compute_eigenvalues()
+    plan.synchronize()
+    t_eig = time.perf_counter() - t0
+
+    D = plan.domain_size
+    apply_tr = wl.get("transform", "none") != "none"
+    field = torch.empty(D, dtype=torch.float64, device="cuda")
+    seed = 20240611
+    K, W = args.steps, args.warmup
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up -----------------------------------------------------------
+    for s in range(W):
+        plan.generate(seed, rank + world * s, out=field, apply_transform=apply_tr)
+    plan.synchronize()
+
+    # ---- timed region: K realizations per rank, fields resident in HBM -----
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    plan.set_profiling(True)
+    l0 = plan.launch_count
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for s in range(K):
+        plan.generate(seed, rank + world * (W + s), out=field, apply_transform=apply_tr)
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = plan.launch_count - l0
+    times = plan.pass_times()
+    plan.set_profiling(False)
+    clocks = sampler.stop() if rank == 0 else None
+    if distributed:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * K / (ms * 1e-3)
+
+    # ---- e2e: host (pinned) output, D2H copy inside the timed region -------
+    e2e = None
+    if not args.no_e2e:
+        Ke = max(2, min(K, 8))
+        host = torch.empty((Ke, D), dtype=torch.float64).pin_memory()
+        plan.generate_batch(seed, 0, 2, out=host[:2], apply_transform=apply_tr)  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        plan.generate_batch(seed, rank * Ke, Ke, out=host, apply_transform=apply_tr)
+        torch.cuda.synchronize()
+        te = time.perf_counter() - t0
+        if distributed:
+            t = torch.tensor([te], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            te = float(t.item())
+        e2e = dict(
+            value=world * Ke / te,
+            unit="realizations/s",
+            h2d_bytes_per_step=16,
+            d2h_bytes_per_step=8 * D,
+            steps=Ke,
+            api="pf_generate_batch with a pinned host output buffer",
+        )
+        del host
+
+    if rank == 0:
+        peaks, peak_kind = measured_peaks()
+        ab = algorithmic_bytes(wl["cells"], compact=wl.get("anisotropy", "none") != "geometric")
+        # dominant kernel = the pass with the largest share of the step
+        names = {0: "pass_a", 2: "pass_b", 4: "pass_c", 1: "pass_a"}
+        shares = {names[k]: v for k, v in times.items() if k in names}
+        dom = max(shares, key=lambda k: shares[k][0]) if shares else "pass_a"
+        dom_ms = shares[dom][0] / max(shares[dom][1], 1) if shares else float("nan")
+        achieved = ab[dom] / (dom_ms * 1e-3) / 1e9
+        peak = float(peaks["hbm_gbs"])
+        roofline = dict(
+            bound="hbm",
+            kernel=dom,
+            achieved=achieved,
+            peak=peak,
+            unit="GB/s",
+            frac=achieved / peak,
+            traffic=None,
+            peak_source=peak_kind + " copy bandwidth (MEASURED_PEAKS.json hbm_gbs)",
+            algorithmic_bytes_per_launch=ab[dom],
+            ms_per_launch=dom_ms,
+            step=dict(
+                algorithmic_bytes=ab["total"],
+                achieved=ab["total"] / (ms / K * 1e-3) / 1e9,
+                frac=ab["total"] / (ms / K * 1e-3) / 1e9 / peak,
+            ),
+            passes_ms={k: v[0] / max(v[1], 1) for k, v in shares.items()},
+        )
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            t_step, scale, cfg, t_eig_cpu = time_oracle(args.workload, 1, 1)
+            cpu = dict(
+                value=1.0 / (t_step * scale),
+                unit="realizations/s",
+                cores=1,
+                kind="port",
+                sample="one realization of %s cells (1/%d of the workload's cells, %.1f s), linear scaling; single thread = one MPI rank of the reference"
+                % ("x".join(map(str, cfg["cells"])), int(scale), t_step),
+            )
+        line = dict(
+            metric="realizations/sec",
+            value=value,
+            unit="realizations/s",
+            n_gpus=world,
+            steps=K,
+            warmup=W,
+            ms_per_step=ms / K,
+            higher_is_better=True,
+            scaling="weak",
+            vs_baseline=None,
+            dtype="f64",
+            data="synthetic",
+            config=dict(
+                workload=WORKLOADS[args.workload]["label"],
+                name=args.workload,
+                parallelism="replicas x%d (independent realizations, no collective)" % world,
+                l2="per-step working set (>9 GB) exceeds the 126 MB L2",
+                rng=args.rng,
+                eigenvalue_setup_s=t_eig,
+                eigenvalue_census=stats,
+            ),
+            clocks=clocks,
+            e2e=e2e,
+            gpu_launches=launches,
+            roofline=roofline,
+            cpu_baseline=cpu,
+        )
+        print(json.dumps(line))
+    plan.close()
+    if distributed:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -57,6 +57,8 @@ ABI_SYMBOLS = [
     "pf_plan_set_stream",
     "pf_plan_synchronize",
     "pf_plan_launch_count",
+    "pf_plan_set_profiling",
+    "pf_plan_get_pass_times",
     "pf_domain_size",
     "pf_extended_size",
     "pf_noise_entries",
@@ -161,6 +163,8 @@ def lib():
     L.pf_plan_synchronize.argtypes = [vp]
     L.pf_plan_launch_count.argtypes = [vp]
     L.pf_plan_launch_count.restype = C.c_ulonglong
+    L.pf_plan_set_profiling.argtypes = [vp, C.c_int]
+    L.pf_plan_get_pass_times.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
     for f in (L.pf_domain_size, L.pf_extended_size, L.pf_noise_entries):
         f.argtypes = [vp]
         f.restype = sz
@@ -298,6 +302,16 @@ class Plan:
 
     def synchronize(self):
         _check(lib().pf_plan_synchronize(self._h))
+
+    def set_profiling(self, on=True):
+        _check(lib().pf_plan_set_profiling(self._h, int(on)))
+
+    def pass_times(self):
+        """{pass kind: (total ms, launches)} measured with CUDA events."""
+        ms = (C.c_double * 16)()
+        cnt = (C.c_ulonglong * 16)()
+        _check(lib().pf_plan_get_pass_times(self._h, ms, cnt))
+        return {i: (ms[i], int(cnt[i])) for i in range(16) if cnt[i]}
 
     @property
     def launch_count(self):

@@ -375,6 +375,11 @@ struct pf_plan
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_done[2] = { nullptr, nullptr }, ev_copied[2] = { nullptr, nullptr };
   unsigned long long launches = 0;
+  // optional per-pass timing (CUDA events on the plan's stream)
+  bool profiling = false;
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_events;
+  double prof_ms[16] = { 0 };
+  unsigned long long prof_count[16] = { 0 };
   pf::CovParams cov{};
   int device = 0;
 };
@@ -558,12 +563,39 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     return fail(PF_ERR_INVALID, "no kernel for line length " + std::to_string(N));
   const cplx* tw = nullptr;
   PF_TRY(twiddles(pl, N, &tw));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (pl->profiling) {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, pl->stream);
+  }
   const int e = fn(kind, &a, tw, pl->stream);
+  if (pl->profiling) {
+    cudaEventRecord(e1, pl->stream);
+    pl->prof_events.push_back({ kind, { e0, e1 } });
+  }
   if (e != 0)
     return fail(PF_ERR_CUDA, std::string("kernel launch failed: ") +
                                cudaGetErrorString((cudaError_t)e));
   pl->launches++;
   return 0;
+}
+
+void
+prof_collect(pf_plan* pl)
+{
+  for (auto& pe : pl->prof_events) {
+    cudaEventSynchronize(pe.second.second);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, pe.second.first, pe.second.second) ==
+        cudaSuccess) {
+      pl->prof_ms[pe.first & 15] += ms;
+      pl->prof_count[pe.first & 15]++;
+    }
+    cudaEventDestroy(pe.second.first);
+    cudaEventDestroy(pe.second.second);
+  }
+  pl->prof_events.clear();
 }
 
 PassArgs
@@ -1181,6 +1213,7 @@ pf_plan_destroy(pf_plan* pl)
     return 0;
   cudaSetDevice(pl->device);
   cudaDeviceSynchronize();
+  prof_collect(pl);
   free_sized(pl);
   for (auto& kv : pl->tw)
     cudaFree(kv.second);
@@ -1223,6 +1256,33 @@ unsigned long long
 pf_plan_launch_count(const pf_plan* pl)
 {
   return pl ? pl->launches : 0;
+}
+
+int
+pf_plan_set_profiling(pf_plan* pl, int on)
+{
+  PF_TRY(check_plan(pl));
+  prof_collect(pl);
+  pl->profiling = on != 0;
+  for (int i = 0; i < 16; i++) {
+    pl->prof_ms[i] = 0.;
+    pl->prof_count[i] = 0;
+  }
+  return 0;
+}
+
+int
+pf_plan_get_pass_times(pf_plan* pl, double* ms, unsigned long long* counts)
+{
+  PF_TRY(check_plan(pl));
+  prof_collect(pl);
+  for (int i = 0; i < 16; i++) {
+    if (ms)
+      ms[i] = pl->prof_ms[i];
+    if (counts)
+      counts[i] = pl->prof_count[i];
+  }
+  return 0;
 }
 
 size_t

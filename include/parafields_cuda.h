@@ -149,6 +149,14 @@ int pf_plan_set_stream(pf_plan* plan, void* cuda_stream);
 int pf_plan_synchronize(pf_plan* plan);
 /* number of kernels this plan has launched so far */
 unsigned long long pf_plan_launch_count(const pf_plan* plan);
+/* per-pass device timing with CUDA events on the plan's stream (off by
+ * default).  pf_plan_get_pass_times fills 16 slots indexed by pass kind
+ * (0 noise+inverse axis pass "A", 2 inverse middle pass "B", 3 forward middle
+ * pass, 4 c2r pass "C", 5/6 r2c pass, 7/8 eigenvalue pass, 9 fused spectral
+ * pass, 1/10 the 1D variants): accumulated milliseconds and launch counts. */
+int pf_plan_set_profiling(pf_plan* plan, int on);
+int pf_plan_get_pass_times(pf_plan* plan, double* ms16,
+                           unsigned long long* counts16);
 
 /* sizes: Traits::{domainSize, extendedDomainSize} (fieldtraits.hh:284-296),
  * FieldBackend::localFieldSize() (r2cfieldbackend.hh:151) */

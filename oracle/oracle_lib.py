@@ -80,6 +80,8 @@ def lib():
         L.orc_lambda_natural.argtypes = [C.POINTER(OrcCfg), dp, dp]
         L.orc_generate_from_noise.argtypes = [C.POINTER(OrcCfg), dp, dp, dp, dp]
         L.orc_reference_noise.argtypes = [C.c_uint, C.c_size_t, dp]
+        L.orc_reference_noise_ranks.argtypes = [C.c_uint, C.c_size_t, C.c_int, dp]
+        L.orc_max_threads.restype = C.c_int
         L.orc_generate_uncorrelated.argtypes = [C.c_uint, C.c_size_t, dp]
         L.orc_multiply.argtypes = [C.POINTER(OrcCfg), dp, C.c_int, dp, dp]
         L.orc_multiply_inverse.argtypes = [C.POINTER(OrcCfg), dp, dp, dp, C.POINTER(C.c_uint)]
@@ -217,6 +219,12 @@ class Oracle:
     def reference_noise(self, seed):
         noise = np.empty(2 * self.noise_entries, dtype=np.float64)
         _check(lib().orc_reference_noise(C.c_uint(seed), self.noise_entries, _dp(noise)))
+        return noise
+
+    def reference_noise_ranks(self, seed, ranks):
+        """noise stream of a `ranks`-rank MPI run of the reference"""
+        noise = np.empty(2 * self.noise_entries, dtype=np.float64)
+        _check(lib().orc_reference_noise_ranks(C.c_uint(seed), self.noise_entries, ranks, _dp(noise)))
         return noise
 
     def generate_from_noise(self, noise, want_spare=False):

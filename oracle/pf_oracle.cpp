@@ -694,7 +694,9 @@ generate_from_noise(const OrcCfg& cfg, const double* lambda,
   const size_t S = m0 * s.n[1] * s.n[2];
   std::vector<cd> X(S);
   const bool tr = cfg.transposed && d == 3;
-  for (size_t idx = 0; idx < S; idx++) {
+#pragma omp parallel for num_threads(cfg.threads > 0 ? cfg.threads : 1)
+  for (long long idx_ = 0; idx_ < (long long)S; idx_++) {
+    const size_t idx = (size_t)idx_;
     size_t k[3] = { 0, 0, 0 };
     if (tr) {
       size_t b[3] = { m0, s.n[2], s.n[1] }, t[3];
@@ -723,11 +725,14 @@ generate_from_noise(const OrcCfg& cfg, const double* lambda,
   std::vector<double> real;
   c2r(s, X, real, cfg.threads);
   // extendedFieldToField, r2cfieldbackend.hh:423-441
-  for (size_t i2 = 0; i2 < s.c[2]; i2++)
+#pragma omp parallel for num_threads(cfg.threads > 0 ? cfg.threads : 1)
+  for (long long i2_ = 0; i2_ < (long long)s.c[2]; i2_++) {
+    const size_t i2 = (size_t)i2_;
     for (size_t i1 = 0; i1 < s.c[1]; i1++)
       for (size_t i0 = 0; i0 < s.c[0]; i0++)
         out[i0 + s.c[0] * (i1 + s.c[1] * i2)] =
           real[i0 + s.n[0] * (i1 + s.n[1] * i2)];
+  }
 }
 
 static size_t
@@ -987,6 +992,32 @@ orc_reference_noise(unsigned seed, size_t entries, double* noise)
   generator.seed(seed);
   for (size_t i = 0; i < 2 * entries; i++)
     noise[i] = normalDist(generator);
+  ORC_CATCH
+}
+
+// The same stream as produced by `ranks` MPI ranks of the reference: rank r
+// seeds with seed + r (matrix.hh:353) and fills its slab, which is a
+// contiguous chunk of the stream because the distributed dimension is the
+// slowest one (fieldtraits.hh:271-282).  Used by the all-core CPU baseline.
+int
+orc_reference_noise_ranks(unsigned seed, size_t entries, int ranks,
+                          double* noise)
+{
+  ORC_TRY
+  if (ranks < 1 || entries % (size_t)ranks != 0)
+    throw std::runtime_error{
+      "number of cells in last dimension has to be multiple of numProc"
+    };
+  const size_t chunk = entries / (size_t)ranks;
+#pragma omp parallel for num_threads(ranks) schedule(static, 1)
+  for (int r = 0; r < ranks; r++) {
+    std::default_random_engine generator;
+    std::normal_distribution<double> normalDist(0., 1.);
+    generator.seed(seed + (unsigned)r);
+    double* dst = noise + 2 * chunk * (size_t)r;
+    for (size_t i = 0; i < 2 * chunk; i++)
+      dst[i] = normalDist(generator);
+  }
   ORC_CATCH
 }
 
