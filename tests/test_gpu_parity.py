@@ -107,7 +107,10 @@ def test_embedding_factor_retry(m):
         o = ol.Oracle([16, 16], covariance="gaussian", corr_length=0.3, factor=4, approximate=True)
         assert rel(p.eigenvalues(m.LAMBDA_NATURAL), o.lambda_natural().ravel()) < TOL
         noise = o.reference_noise(9)
-        assert rel(p.generate_from_noise(noise), o.generate_from_noise(noise)) < TOL
+        # the Gaussian spectrum decays to ~1e-17: eigenvalues that agree to
+        # 1e-16 absolute give sqrt(lambda) that agree to ~1e-8 only, so the
+        # field tolerance here is sqrt(eps)-limited by construction
+        assert rel(p.generate_from_noise(noise), o.generate_from_noise(noise)) < 1e-7
 
 
 @pytest.mark.parametrize("kind", ["logNormal", "foldedNormal", "sign", "boxCox"])
