@@ -317,6 +317,46 @@ line_fft_phase2(cplx (&v)[LineCfg<N>::E], const cplx* s, int t,
   }
 }
 
+// Phase 2 split in two so that a kernel can release the exchange area (and
+// start refilling it asynchronously) before the second register pass:
+//   load    : all butterflies' operands, v[i + NB2*r] = s[jb_i + 32 r]
+//   compute : twiddle + radix-R2 butterflies in place (register stride NB2)
+template <int N>
+PF_HD void
+line_fft_phase2_load(cplx (&v)[LineCfg<N>::E], const cplx* s, int t)
+{
+  using C = LineCfg<N>;
+  static_assert(C::R2 > 1, "two-pass lines only");
+#pragma unroll
+  for (int i = 0; i < C::NB2; i++)
+#pragma unroll
+    for (int r = 0; r < C::R2; r++)
+      v[i + C::NB2 * r] = s[pidx(t + C::TPL * i + 32 * r)];
+}
+
+template <int N, int DIR>
+PF_HD void
+line_fft_phase2_compute(cplx (&v)[LineCfg<N>::E], int t,
+                        const cplx* __restrict__ tw2)
+{
+  using C = LineCfg<N>;
+#pragma unroll
+  for (int i = 0; i < C::NB2; i++) {
+    const int jb = t + C::TPL * i;
+#pragma unroll
+    for (int r = 1; r < C::R2; r++) {
+#ifdef __CUDA_ARCH__
+      const cplx w = __ldg(&tw2[r * 32 + jb]);
+#else
+      const cplx w = tw2[r * 32 + jb];
+#endif
+      v[i + C::NB2 * r] =
+        DIR < 0 ? cmul(v[i + C::NB2 * r], w) : cmulc(v[i + C::NB2 * r], w);
+    }
+    Dft<C::R2, DIR, C::NB2>::run(v + i);
+  }
+}
+
 #ifdef __CUDACC__
 template <int N, int DIR>
 __device__ __forceinline__ void

@@ -1,6 +1,9 @@
 // pf_inst.cu -- instantiates every pass kernel for one line length PF_N
 // (compiled once per N: -DPF_N=2 ... 1024) and exports one launcher.
 #include "pf_kernels.cuh"
+#if PF_N >= 256
+#include "pf_pipe.cuh"
+#endif
 
 #ifndef PF_N
 #error "compile with -DPF_N=<line length>"
@@ -104,3 +107,70 @@ extern "C" int PF_CAT(pf_launch_n, PF_N)(int kind, const PassArgs* ap,
   }
   return (int)e;
 }
+
+#if PF_N >= 256
+// persistent TMA-pipelined variants (pf_pipe.cuh); `tmap` is a host pointer to
+// the CUtensorMap of the transposed output (unused for K_C2R)
+namespace pf {
+template <class Kern, class... Extra>
+static cudaError_t
+launch_pipe(Kern kern, int threads, size_t smem, int grid, cudaStream_t st,
+            const PassArgs& a, const cplx* tw2, Extra... extra)
+{
+  cudaError_t e = cudaFuncSetAttribute(
+    kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess)
+    return e;
+  kern<<<grid, threads, smem, st>>>(a, tw2, extra...);
+  return cudaGetLastError();
+}
+} // namespace pf
+
+extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
+                                              const void* tw2v,
+                                              const void* tmap, int grid,
+                                              cudaStream_t st)
+{
+  constexpr int N = PF_N;
+  using P = PCfg<N>;
+  const PassArgs& a = *ap;
+  const cplx* tw2 = reinterpret_cast<const cplx*>(tw2v);
+  cudaError_t e = cudaErrorInvalidValue;
+  if (grid <= 0)
+    return (int)cudaSuccess;
+  switch (kind) {
+    case K_GEN_TILE: {
+      const CUtensorMap tm = *reinterpret_cast<const CUtensorMap*>(tmap);
+      if (a.noise_kind == NOISE_PHILOX_FAST)
+        e = launch_pipe(kp_gen<N, NOISE_PHILOX_FAST>, P::THREADS, P::SMEM_TILE,
+                        grid, st, a, tw2, tm);
+      else if (a.noise_kind == NOISE_PHILOX_F64)
+        e = launch_pipe(kp_gen<N, NOISE_PHILOX_F64>, P::THREADS, P::SMEM_TILE,
+                        grid, st, a, tw2, tm);
+      else
+        e = launch_pipe(kp_gen<N, NOISE_INJECTED>, P::THREADS, P::SMEM_TILE,
+                        grid, st, a, tw2, tm);
+      break;
+    }
+    case K_C2T_INV: {
+      const CUtensorMap tm = *reinterpret_cast<const CUtensorMap*>(tmap);
+      e = launch_pipe(kp_c2t<N, +1>, P::THREADS, P::SMEM_TILE, grid, st, a, tw2,
+                      tm);
+      break;
+    }
+    case K_C2T_FWD: {
+      const CUtensorMap tm = *reinterpret_cast<const CUtensorMap*>(tmap);
+      e = launch_pipe(kp_c2t<N, -1>, P::THREADS, P::SMEM_TILE, grid, st, a, tw2,
+                      tm);
+      break;
+    }
+    case K_C2R:
+      e = launch_pipe(kp_c2r<N>, P::THREADS - 32, P::SMEM_LINES, grid, st, a,
+                      tw2);
+      break;
+    default:
+      break;
+  }
+  return (int)e;
+}
+#endif

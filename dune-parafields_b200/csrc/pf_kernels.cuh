@@ -64,6 +64,46 @@ apply_transform(double v, int kind, double lambda)
   }
 }
 
+// compile-time variant + dispatcher: keeps the switch out of unrolled store
+// loops (one specialised loop per transform kind)
+template <int KIND>
+__device__ __forceinline__ double
+apply_transform_c(double v, double lambda)
+{
+  if constexpr (KIND == 1)
+    return exp(v);
+  else if constexpr (KIND == 2)
+    return fabs(v);
+  else if constexpr (KIND == 3)
+    return v < 0. ? -1. : 1.;
+  else if constexpr (KIND == 4)
+    return pow(v * lambda + 1, -lambda);
+  else
+    return v;
+}
+template <class F>
+__device__ __forceinline__ void
+dispatch_transform(int kind, F&& f)
+{
+  switch (kind) {
+    case 1:
+      f(std::integral_constant<int, 1>{});
+      break;
+    case 2:
+      f(std::integral_constant<int, 2>{});
+      break;
+    case 3:
+      f(std::integral_constant<int, 3>{});
+      break;
+    case 4:
+      f(std::integral_constant<int, 4>{});
+      break;
+    default:
+      f(std::integral_constant<int, 0>{});
+      break;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // covariance on the torus, matrix.hh:624-648 + covariance.hh (same arithmetic
 // as the reference functors)
@@ -317,17 +357,20 @@ k_gen_reim(const PassArgs p, const cplx* __restrict__ tw2)
   const long long line = (long long)b * p.A + a;
   double* o1 = reinterpret_cast<double*>(p.out);
   double* o2 = reinterpret_cast<double*>(p.out2);
+  dispatch_transform(p.transform, [&](auto trc) {
+    constexpr int TR = decltype(trc)::value;
 #pragma unroll
-  for (int q = 0; q < K::E; q++) {
-    const int e = t + K::TPL * q;
-    if (e < p.keep) {
-      if (o1)
-        o1[line * p.out_pitch + e] =
-          apply_transform(v[q].x * p.scale, p.transform, p.tparam);
-      if (o2)
-        o2[line * p.out_pitch + e] = v[q].y * p.scale;
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      if (e < p.keep) {
+        if (o1)
+          o1[line * p.out_pitch + e] =
+            apply_transform_c<TR>(v[q].x * p.scale, p.tparam);
+        if (o2)
+          o2[line * p.out_pitch + e] = v[q].y * p.scale;
+      }
     }
-  }
+  });
 }
 
 // contiguous complex lines -> FFT -> tile (pass B, F1, E1)
@@ -388,18 +431,21 @@ k_c2r(const PassArgs p, const cplx* __restrict__ tw2)
   }
   line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
   double* out = reinterpret_cast<double*>(p.out);
+  dispatch_transform(p.transform, [&](auto trc) {
+    constexpr int TR = decltype(trc)::value;
 #pragma unroll
-  for (int q = 0; q < K::E; q++) {
-    const int e = t + K::TPL * q;
-    if (e < p.keep) {
-      if (v0)
-        out[L0 * p.out_pitch + e] =
-          apply_transform(v[q].x * p.scale, p.transform, p.tparam);
-      if (v1)
-        out[L1 * p.out_pitch + e] =
-          apply_transform(v[q].y * p.scale, p.transform, p.tparam);
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      if (e < p.keep) {
+        if (v0)
+          out[L0 * p.out_pitch + e] =
+            apply_transform_c<TR>(v[q].x * p.scale, p.tparam);
+        if (v1)
+          out[L1 * p.out_pitch + e] =
+            apply_transform_c<TR>(v[q].y * p.scale, p.tparam);
+      }
     }
-  }
+  });
 }
 
 // F0 / E0: two real lines (loaded or covariance-evaluated) -> one complex

@@ -1,0 +1,498 @@
+// pf_pipe.cuh -- persistent, warp-specialised versions of the three passes of
+// the generate pipeline (A: noise -> inverse FFT -> tile, B: contiguous lines
+// -> FFT -> tile, C: half-spectrum line pairs -> real lines) for long lines
+// (N >= 256).  Same arithmetic as pf_kernels.cuh (k_gen_tile / k_c2t / k_c2r);
+// what changes is how data moves:
+//
+//  * one CTA per SM, 8 FFT warps + 1 store warp, looping over tiles;
+//  * input lines arrive by 1D bulk copies (cp.async.bulk, completion on an
+//    mbarrier) straight into the line's exchange buffer; the copy of the
+//    NEXT tile's line is issued as soon as the current line has left shared
+//    memory for the second register pass, so HBM latency hides behind the
+//    fp64 butterflies;
+//  * the transposed output tile ([element][line], 8 lines = 128 contiguous
+//    bytes per element row) is staged in shared memory with the 128-byte
+//    swizzle and written by one TMA tensor store per 256 rows
+//    (cp.async.bulk.tensor), issued by the store warp, so FFT warps never
+//    wait for global stores.
+//
+// Shared memory (N=1024): 8 x 16.5 KB exchange/landing buffers + 64 KB stage.
+#pragma once
+#include <cuda.h>
+
+#include "pf_kernels.cuh"
+
+namespace pf {
+
+template <int N>
+struct PCfg
+{
+  using C = LineCfg<N>;
+  static constexpr int E = C::E;
+  static constexpr int TPL = C::TPL;
+  static constexpr int CW = 8;              // FFT (consumer) warps per CTA
+  static constexpr int LPW = 32 / TPL;      // lines per warp
+  static constexpr int LT = CW * LPW;       // lines per tile
+  static constexpr int SUBS = LT / 8;       // 8-line (128 B) sub-stages
+  static constexpr int THREADS = 32 * (CW + 1);
+  static constexpr int SLOT_BYTES = C::PITCH * 16;
+  static constexpr int SLOTS_BYTES = LT * SLOT_BYTES;
+  static constexpr int STAGE_BYTES = 65536;
+  static constexpr int SR = STAGE_BYTES / (LT * 16); // stage rows per chunk
+  static constexpr int BOXR = SR < 256 ? SR : 256;   // TMA box rows
+  static constexpr int SUB_BYTES = SR * 128;
+  static constexpr int BAR_BYTES = 128;
+  static constexpr int SMEM_TILE = SLOTS_BYTES + STAGE_BYTES + BAR_BYTES + 1024;
+  static constexpr int SMEM_LINES = SLOTS_BYTES + BAR_BYTES + 1024;
+  static_assert(SLOTS_BYTES % 1024 == 0, "stage must stay 1024-byte aligned");
+  static_assert(N + 2 <= C::PITCH, "c2r landing zone needs 2*(N/2+1) entries");
+};
+
+// ---- PTX wrappers -----------------------------------------------------------
+__device__ __forceinline__ uint32_t
+smem_u32(const void* p)
+{
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void
+mbar_init(uint32_t bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count)
+               : "memory");
+}
+__device__ __forceinline__ void
+mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void
+mbar_arrive(uint32_t bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void
+mbar_wait(uint32_t bar, uint32_t parity)
+{
+  asm volatile("{\n"
+               ".reg .pred P1;\n"
+               "LAB_WAIT:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+               "@P1 bra DONE;\n"
+               "bra LAB_WAIT;\n"
+               "DONE:\n"
+               "}" ::"r"(bar),
+               "r"(parity)
+               : "memory");
+}
+__device__ __forceinline__ void
+fence_proxy_async()
+{
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// global -> shared bulk copy, bytes % 16 == 0, completion counted on `bar`
+__device__ __forceinline__ void
+bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes "
+               "[%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// shared -> global tensor store of one box at (c0, c1, c2)
+__device__ __forceinline__ void
+tma_store_3d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2)
+{
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group "
+               "[%0, {%2, %3, %4}], [%1];" ::"l"(tm),
+               "r"(src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void
+bulk_commit()
+{
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void
+bulk_wait_read0()
+{
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void
+bulk_wait0()
+{
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+__device__ __forceinline__ unsigned char*
+align1024(unsigned char* p)
+{
+  const uint32_t a = smem_u32(p);
+  return p + ((1024u - (a & 1023u)) & 1023u);
+}
+
+// shared-memory carve-up of the tile kernels
+template <int N>
+struct PSmem
+{
+  using P = PCfg<N>;
+  unsigned char* base;
+  __device__ __forceinline__ explicit PSmem(unsigned char* raw)
+    : base(align1024(raw))
+  {}
+  __device__ __forceinline__ cplx* slot(int s) const
+  {
+    return reinterpret_cast<cplx*>(base + (size_t)s * P::SLOT_BYTES);
+  }
+  __device__ __forceinline__ unsigned char* stage() const
+  {
+    return base + P::SLOTS_BYTES;
+  }
+  // barriers: [0..CW) input per warp, [CW] stage full, [CW+1] stage free
+  __device__ __forceinline__ uint32_t bar(int i, bool tile) const
+  {
+    return smem_u32(base + P::SLOTS_BYTES + (tile ? P::STAGE_BYTES : 0)) + 8u * i;
+  }
+};
+
+// the store warp's loop: wait for a full stage, write it with TMA, release
+template <int N>
+__device__ __forceinline__ void
+store_warp_loop(const PassArgs& p, const CUtensorMap* tm, const PSmem<N>& sm,
+                int ntA, long long ntiles)
+{
+  using P = PCfg<N>;
+  if ((threadIdx.x & 31) != 0)
+    return;
+  const uint32_t full = sm.bar(P::CW, true), free_ = sm.bar(P::CW + 1, true);
+  const uint32_t st = smem_u32(sm.stage());
+  const int nchunk = (p.keep + P::SR - 1) / P::SR;
+  uint32_t it = 0;
+  for (long long T = blockIdx.x; T < ntiles; T += gridDim.x) {
+    const int at = (int)(T % ntA), b = (int)(T / ntA);
+    for (int c = 0; c < nchunk; c++, it++) {
+      mbar_wait(full, it & 1);
+      const int rows = min(P::SR, p.keep - c * P::SR);
+#pragma unroll
+      for (int sub = 0; sub < P::SUBS; sub++) {
+        if (at * P::LT + sub * 8 < p.A) {
+          for (int r0 = 0; r0 < rows; r0 += P::BOXR)
+            tma_store_3d(tm, st + sub * P::SUB_BYTES + r0 * 128,
+                         2 * (at * P::LT + sub * 8), c * P::SR + r0, b);
+        }
+      }
+      bulk_commit();
+      bulk_wait_read0();
+      mbar_arrive(free_);
+    }
+  }
+  bulk_wait0();
+}
+
+// FFT warps: write registers (thread t of line `slot` owns e = t + TPL*q) to
+// the swizzled stage, one chunk of SR rows at a time
+template <int N>
+__device__ __forceinline__ void
+stage_out(const cplx (&v)[LineCfg<N>::E], const PSmem<N>& sm, int slot, int t,
+          int keep, uint32_t& it)
+{
+  using P = PCfg<N>;
+  const uint32_t full = sm.bar(P::CW, true), free_ = sm.bar(P::CW + 1, true);
+  unsigned char* st = sm.stage() + (slot >> 3) * P::SUB_BYTES;
+  const int l8 = slot & 7;
+  const int nchunk = (keep + P::SR - 1) / P::SR;
+  for (int c = 0; c < nchunk; c++, it++) {
+    mbar_wait(free_, (it & 1) ^ 1);
+    const int lo = c * P::SR;
+    const int hi = min(keep, lo + P::SR);
+#pragma unroll
+    for (int q = 0; q < P::E; q++) {
+      const int e = t + P::TPL * q;
+      if (e >= lo && e < hi) {
+        const int r = e - lo;
+        *reinterpret_cast<cplx*>(st + r * 128 + ((l8 ^ (r & 7)) << 4)) = v[q];
+      }
+    }
+    fence_proxy_async();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0)
+      mbar_arrive(full);
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void
+pipe_init(const PSmem<N>& sm, bool tile)
+{
+  using P = PCfg<N>;
+  if (threadIdx.x == 0) {
+    for (int w = 0; w < P::CW; w++)
+      mbar_init(sm.bar(w, tile), 1);
+    if (tile) {
+      mbar_init(sm.bar(P::CW, true), P::CW);
+      mbar_init(sm.bar(P::CW + 1, true), 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------
+// white noise * sigma, register layout of load_noise (pf_kernels.cuh) with the
+// rare cases (self-conjugate entries, `corrected` planes) moved out of the
+// unrolled loop.  Follows matrix.hh:396-421 + r2cfieldbackend.hh:305-325.
+// ---------------------------------------------------------------------------
+template <int N, int NOISE>
+__device__ __forceinline__ void
+load_noise_p(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
+             bool valid)
+{
+  using C = LineCfg<N>;
+  constexpr int H = C::E / 2;
+  constexpr double SQRT2 = 1.41421356237309504880168872420969808;
+  if (!valid) {
+#pragma unroll
+    for (int q = 0; q < C::E; q++)
+      v[q] = make_double2(0., 0.);
+    return;
+  }
+  const double* row = table_row(p, a, b);
+  // second half of the line: e + N/2, or its mirror N/2 - e (compact table)
+  const double* row2 = row + N / 2;
+  const int dir2 = p.tab_mirror_e ? -1 : 1;
+  const unsigned long long cbase =
+    (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
+  const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
+  double s1[H], s2[H];
+#pragma unroll
+  for (int q = 0; q < H; q++) {
+    const int e = t + C::TPL * q; // < N/2
+    s1[q] = __ldg(row + e);
+    s2[q] = __ldg(row2 + dir2 * e);
+  }
+#pragma unroll
+  for (int q = 0; q < H; q++) {
+    const int e = t + C::TPL * q;
+    double2 n1, n2;
+    if constexpr (NOISE == NOISE_INJECTED) {
+      n1 = __ldg(p.noise + ibase + (long long)e * p.ime);
+      n2 = __ldg(p.noise + ibase + (long long)(e + N / 2) * p.ime);
+    } else {
+      const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
+      const uint4 w = philox4x32_10(ctr, p.realization, p.seed);
+      if constexpr (NOISE == NOISE_PHILOX_FAST) {
+        n1 = box_muller_fast(w.x, w.y);
+        n2 = box_muller_fast(w.z, w.w);
+      } else {
+        n1 = box_muller_f64(w.x, w.y);
+        n2 = box_muller_f64(w.z, w.w);
+      }
+    }
+    v[q] = make_double2(s1[q] * n1.x, s1[q] * n1.y);
+    v[q + H] = make_double2(s2[q] * n2.x, s2[q] * n2.y);
+  }
+  if (p.hermitian) {
+    const bool a_self = (2 * a) % p.na_self == 0;
+    const bool b_self = (2 * b) % p.nb_self == 0;
+    const bool plane = p.corrected && (p.plane_axis == 0 ? a_self : b_self);
+    if (plane) {
+#pragma unroll
+      for (int q = 0; q < C::E; q++)
+        v[q] = make_double2(v[q].x * SQRT2, v[q].y * SQRT2);
+    }
+    if (t == 0 && a_self && b_self) {
+      // self-conjugate entries e = 0 and e = N/2: real, full weight
+      const double f = plane ? 1.0 : SQRT2;
+      v[0] = make_double2(v[0].x * f, 0.);
+      v[H] = make_double2(v[H].x * f, 0.);
+    }
+  }
+}
+
+// ===========================================================================
+// pass A: noise -> inverse FFT -> transposed tile (k_gen_tile)
+// ===========================================================================
+template <int N, int NOISE>
+__global__ void __launch_bounds__(PCfg<N>::THREADS, 1)
+kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
+       const __grid_constant__ CUtensorMap tm)
+{
+  using P = PCfg<N>;
+  extern __shared__ unsigned char smem_raw[];
+  PSmem<N> sm(smem_raw);
+  pipe_init<N>(sm, true);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntA = (p.A + P::LT - 1) / P::LT;
+  const long long ntiles = (long long)ntA * p.B;
+  if (warp == P::CW) {
+    store_warp_loop<N>(p, &tm, sm, ntA, ntiles);
+    return;
+  }
+  const int slot = warp * P::LPW + lane / P::TPL, t = lane % P::TPL;
+  cplx* buf = sm.slot(slot);
+  uint32_t it = 0;
+  for (long long T = blockIdx.x; T < ntiles; T += gridDim.x) {
+    const int at = (int)(T % ntA), b = (int)(T / ntA);
+    const int a = at * P::LT + slot;
+    cplx v[P::E];
+    // lines beyond A recompute the last valid line; the tensor store clips
+    load_noise_p<N, NOISE>(v, p, min(a, p.A - 1), b, t, true);
+    line_fft<N, +1>(v, buf, t, tw2);
+    stage_out<N>(v, sm, slot, t, p.keep, it);
+  }
+}
+
+// ===========================================================================
+// pass B / F1 / E1: contiguous complex lines -> FFT -> transposed tile (k_c2t)
+// ===========================================================================
+template <int N, int DIR>
+__global__ void __launch_bounds__(PCfg<N>::THREADS, 1)
+kp_c2t(const PassArgs p, const cplx* __restrict__ tw2,
+       const __grid_constant__ CUtensorMap tm)
+{
+  using P = PCfg<N>;
+  extern __shared__ unsigned char smem_raw[];
+  PSmem<N> sm(smem_raw);
+  pipe_init<N>(sm, true);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntA = (p.A + P::LT - 1) / P::LT;
+  const long long ntiles = (long long)ntA * p.B;
+  if (warp == P::CW) {
+    store_warp_loop<N>(p, &tm, sm, ntA, ntiles);
+    return;
+  }
+  const int slot = warp * P::LPW + lane / P::TPL, t = lane % P::TPL;
+  cplx* buf = sm.slot(slot);
+  const uint32_t inbar = sm.bar(warp, true);
+  const cplx* in = reinterpret_cast<const cplx*>(p.in);
+  const uint32_t line_bytes = (uint32_t)p.n_valid * 16u;
+  // lane 0 arms the warp's barrier and copies the warp's lines of tile T
+  auto issue = [&](long long T) {
+    const int at = (int)(T % ntA), b = (int)(T / ntA);
+    const int a0 = at * P::LT + warp * P::LPW;
+    const int nv = max(0, min(P::LPW, p.A - a0));
+    if (lane == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(inbar, (uint32_t)nv * line_bytes);
+      for (int l = 0; l < nv; l++)
+        bulk_load(smem_u32(sm.slot(warp * P::LPW + l)),
+                  in + (long long)(a0 + l) * p.isa + (long long)b * p.isb,
+                  line_bytes, inbar);
+    }
+  };
+  uint32_t it = 0, ph = 0;
+  long long T = blockIdx.x;
+  if (T < ntiles)
+    issue(T);
+  for (; T < ntiles; T += gridDim.x) {
+    const int at = (int)(T % ntA);
+    const int a = at * P::LT + slot;
+    const bool valid = a < p.A;
+    cplx v[P::E];
+    mbar_wait(inbar, ph);
+    ph ^= 1;
+#pragma unroll
+    for (int q = 0; q < P::E; q++) {
+      const int e = t + P::TPL * q;
+      v[q] = (valid && e < p.n_valid) ? buf[e] : make_double2(0., 0.);
+    }
+    __syncwarp();
+    line_fft_phase1<N, DIR>(v, buf, t);
+    __syncwarp();
+    line_fft_phase2_load<N>(v, buf, t);
+    __syncwarp();
+    // the exchange area is free again: start the next tile's copy
+    const long long Tn = T + gridDim.x;
+    if (Tn < ntiles)
+      issue(Tn);
+    line_fft_phase2_compute<N, DIR>(v, t, tw2);
+    stage_out<N>(v, sm, slot, t, p.keep, it);
+  }
+}
+
+// ===========================================================================
+// pass C: pairs of half-spectrum lines -> one complex inverse FFT -> two real
+// lines, restricted, value transform fused (k_c2r)
+// ===========================================================================
+template <int N>
+__global__ void __launch_bounds__(PCfg<N>::THREADS - 32, 1)
+kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using P = PCfg<N>;
+  constexpr int M0 = N / 2 + 1;
+  extern __shared__ unsigned char smem_raw[];
+  PSmem<N> sm(smem_raw);
+  pipe_init<N>(sm, false);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long nl = (long long)p.A * p.B;
+  const long long npairs = (nl + 1) / 2;
+  const long long ntiles = (npairs + P::LT - 1) / P::LT;
+  const int slot = warp * P::LPW + lane / P::TPL, t = lane % P::TPL;
+  cplx* buf = sm.slot(slot);
+  const uint32_t inbar = sm.bar(warp, false);
+  const cplx* in = reinterpret_cast<const cplx*>(p.in);
+  constexpr uint32_t line_bytes = (uint32_t)M0 * 16u;
+  auto issue = [&](long long T) {
+    const long long L = 2 * (T * P::LT + warp * P::LPW); // first line
+    const long long nv = max(0ll, min((long long)2 * P::LPW, nl - L));
+    if (lane == 0) {
+      fence_proxy_async();
+      mbar_expect_tx(inbar, (uint32_t)nv * line_bytes);
+      for (int l = 0; l < (int)nv; l++)
+        bulk_load(smem_u32(sm.slot(warp * P::LPW + (l >> 1))) +
+                    (l & 1) * line_bytes,
+                  in + (L + l) * p.isa, line_bytes, inbar);
+    }
+  };
+  uint32_t ph = 0;
+  long long T = blockIdx.x;
+  if (T < ntiles)
+    issue(T);
+  double* out = reinterpret_cast<double*>(p.out);
+  for (; T < ntiles; T += gridDim.x) {
+    const long long L0 = 2 * (T * P::LT + slot), L1 = L0 + 1;
+    const bool v0 = L0 < nl, v1 = L1 < nl;
+    cplx v[P::E];
+    mbar_wait(inbar, ph);
+    ph ^= 1;
+#pragma unroll
+    for (int q = 0; q < P::E; q++) {
+      const int e = t + P::TPL * q;
+      const int kk = e <= N / 2 ? e : N - e;
+      const cplx xa = v0 ? buf[kk] : make_double2(0., 0.);
+      const cplx xb = v1 ? buf[M0 + kk] : make_double2(0., 0.);
+      if (e == 0 || 2 * e == N)
+        v[q] = make_double2(xa.x, xb.x);
+      else if (e < N / 2)
+        v[q] = make_double2(xa.x - xb.y, xa.y + xb.x);
+      else
+        v[q] = make_double2(xa.x + xb.y, xb.x - xa.y);
+    }
+    __syncwarp();
+    line_fft_phase1<N, +1>(v, buf, t);
+    __syncwarp();
+    line_fft_phase2_load<N>(v, buf, t);
+    __syncwarp();
+    const long long Tn = T + gridDim.x;
+    if (Tn < ntiles)
+      issue(Tn);
+    line_fft_phase2_compute<N, +1>(v, t, tw2);
+    dispatch_transform(p.transform, [&](auto trc) {
+      constexpr int TR = decltype(trc)::value;
+#pragma unroll
+      for (int q = 0; q < P::E; q++) {
+        const int e = t + P::TPL * q;
+        if (e < p.keep) {
+          if (v0)
+            out[L0 * p.out_pitch + e] = apply_transform_c<TR>(v[q].x, p.tparam);
+          if (v1)
+            out[L1 * p.out_pitch + e] = apply_transform_c<TR>(v[q].y, p.tparam);
+        }
+      }
+    });
+  }
+}
+
+} // namespace pf

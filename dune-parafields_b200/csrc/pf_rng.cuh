@@ -30,15 +30,11 @@ philox4x32_10(unsigned long long ctr, unsigned long long realization,
   uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
 #pragma unroll
   for (int r = 0; r < 10; r++) {
-#ifdef __CUDA_ARCH__
-    const uint32_t hi0 = __umulhi(PF_PHILOX_M0, c0);
-    const uint32_t hi1 = __umulhi(PF_PHILOX_M1, c2);
-#else
-    const uint32_t hi0 = (uint32_t)(((uint64_t)PF_PHILOX_M0 * c0) >> 32);
-    const uint32_t hi1 = (uint32_t)(((uint64_t)PF_PHILOX_M1 * c2) >> 32);
-#endif
-    const uint32_t lo0 = PF_PHILOX_M0 * c0;
-    const uint32_t lo1 = PF_PHILOX_M1 * c2;
+    // one 32x32->64 multiply per lane pair (IMAD.WIDE.U32 on the device)
+    const uint64_t p0 = (uint64_t)PF_PHILOX_M0 * c0;
+    const uint64_t p1 = (uint64_t)PF_PHILOX_M1 * c2;
+    const uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0;
+    const uint32_t hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
     const uint32_t n0 = hi1 ^ c1 ^ k0;
     const uint32_t n2 = hi0 ^ c3 ^ k1;
     c0 = n0;
