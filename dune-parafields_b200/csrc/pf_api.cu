@@ -8,9 +8,11 @@
 #include "../../include/parafields_cuda.h"
 #include "pf_args.h"
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -34,6 +36,13 @@ PF_DECL(128)
 PF_DECL(256)
 PF_DECL(512)
 PF_DECL(1024)
+// persistent TMA-pipelined variants (pf_pipe.cuh), N >= 256
+#define PF_DECL_PIPE(n)                                                        \
+  extern "C" int pf_pipe_launch_n##n(int, const PassArgs*, const void*,        \
+                                     const void*, int, cudaStream_t);
+PF_DECL_PIPE(256)
+PF_DECL_PIPE(512)
+PF_DECL_PIPE(1024)
 
 namespace {
 
@@ -89,6 +98,47 @@ launcher_for(long long n)
       return pf_launch_n1024;
   }
   return nullptr;
+}
+
+typedef int (*pipe_fn)(int, const PassArgs*, const void*, const void*, int,
+                       cudaStream_t);
+pipe_fn
+pipe_launcher_for(long long n)
+{
+  switch (n) {
+    case 256:
+      return pf_pipe_launch_n256;
+    case 512:
+      return pf_pipe_launch_n512;
+    case 1024:
+      return pf_pipe_launch_n1024;
+  }
+  return nullptr;
+}
+
+// cuTensorMapEncodeTiled through the runtime (no link-time libcuda dependency)
+typedef CUresult (*encode_tiled_fn)(
+  CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_tiled_fn
+get_encode_tiled()
+{
+  static encode_tiled_fn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault,
+                                &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<encode_tiled_fn>(p);
+    else
+      cudaGetLastError();
+  }
+  return fn;
 }
 
 bool
@@ -382,6 +432,13 @@ struct pf_plan
   unsigned long long prof_count[16] = { 0 };
   pf::CovParams cov{};
   int device = 0;
+  int sm_count = 148;
+  // bit mask of pass kinds routed to the persistent TMA kernels (N >= 256);
+  // PF_PIPE=0 in the environment selects the plain kernels everywhere
+  // (pass A stays on the plain kernel: it is issue-bound and the plain
+  // kernel keeps 12 warps per SM against 8 FFT warps, profiles/r01b)
+  unsigned pipe_mask = (1u << pf::K_C2T_INV) | (1u << pf::K_C2T_FWD) |
+                       (1u << pf::K_C2R);
 };
 
 namespace {
@@ -555,6 +612,56 @@ twiddles(pf_plan* pl, long long N, const cplx** out)
   return 0;
 }
 
+// transposed-tile output of a pass as a 3D tensor map: dim0 = 2*A doubles
+// (the tile axis), dim1 = element row e < keep, dim2 = b
+int
+make_tile_map(const PassArgs& a, int boxr, CUtensorMap* tm)
+{
+  encode_tiled_fn enc = get_encode_tiled();
+  if (!enc)
+    return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
+  const cuuint64_t gdim[3] = { (cuuint64_t)2 * a.A, (cuuint64_t)a.keep,
+                               (cuuint64_t)a.B };
+  const cuuint64_t row = (cuuint64_t)a.ose * 16;
+  const cuuint64_t plane =
+    a.B > 1 ? (cuuint64_t)a.osb * 16 : row * (cuuint64_t)a.keep;
+  const cuuint64_t gstr[2] = { row, plane };
+  const cuuint32_t box[3] = { 16, (cuuint32_t)boxr, 1 };
+  const cuuint32_t estr[3] = { 1, 1, 1 };
+  const CUresult r =
+    enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, a.out, gdim, gstr, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " +
+                               std::to_string((int)r));
+  return 0;
+}
+
+// rows per TMA box of the persistent tile kernels (PCfg<N>::BOXR)
+int
+pipe_box_rows(long long N)
+{
+  const int tpl = (int)(N / 32), lt = 8 * (32 / tpl);
+  const int sr = 32768 / (lt * 16);
+  return sr < 256 ? sr : 256;
+}
+
+bool
+use_pipe(const pf_plan* pl, long long N, int kind, const PassArgs& a)
+{
+  if (N < 256 || !(pl->pipe_mask & (1u << kind)) || !pipe_launcher_for(N))
+    return false;
+  if (kind == pf::K_C2R)
+    return a.B == 1 && (a.isa * 16) % 16 == 0;
+  // tile kernels: plain scale, 16-byte aligned lines, whole-line bulk copies
+  if (a.scale != 1.0)
+    return false;
+  if (kind != pf::K_GEN_TILE && (a.n_valid <= 0 || a.n_valid > N))
+    return false;
+  return a.keep >= 1;
+}
+
 int
 run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
 {
@@ -563,13 +670,29 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     return fail(PF_ERR_INVALID, "no kernel for line length " + std::to_string(N));
   const cplx* tw = nullptr;
   PF_TRY(twiddles(pl, N, &tw));
+  const bool pipe = use_pipe(pl, N, kind, a);
+  CUtensorMap tm;
+  int grid = 0;
+  if (pipe) {
+    const int tpl = (int)(N / 32), lt = 8 * (32 / tpl);
+    long long ntiles;
+    if (kind == pf::K_C2R) {
+      const long long nl = (long long)a.A * a.B;
+      ntiles = ((nl + 1) / 2 + lt - 1) / lt;
+    } else {
+      ntiles = (long long)((a.A + lt - 1) / lt) * a.B;
+      PF_TRY(make_tile_map(a, pipe_box_rows(N), &tm));
+    }
+    grid = (int)std::min<long long>(ntiles, pl->sm_count);
+  }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (pl->profiling) {
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     cudaEventRecord(e0, pl->stream);
   }
-  const int e = fn(kind, &a, tw, pl->stream);
+  const int e = pipe ? pipe_launcher_for(N)(kind, &a, tw, &tm, grid, pl->stream)
+                     : fn(kind, &a, tw, pl->stream);
   if (pl->profiling) {
     cudaEventRecord(e1, pl->stream);
     pl->prof_events.push_back({ kind, { e0, e1 } });
@@ -861,7 +984,7 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   PassArgs a = blank_args();
   set_table(pl, a, pl->sig_gen);
   a.noise_kind = noise_kind;
-  a.seed = seed;
+  a.keys = pf::philox_keys(seed);
   a.realization = realization;
   a.noise = noise_dev;
   a.hermitian = pl->hermitian ? 1 : 0;
@@ -1189,6 +1312,10 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     delete pl;
     return fail(PF_ERR_CUDA, "cudaSetDevice failed");
   }
+  cudaDeviceGetAttribute(&pl->sm_count, cudaDevAttrMultiProcessorCount,
+                         pl->device);
+  if (const char* env = getenv("PF_PIPE"))
+    pl->pipe_mask = (unsigned)strtoul(env, nullptr, 0);
   pl->factor = desc->embedding_factor ? desc->embedding_factor : 2;
   if (desc->periodic)
     pl->factor = 1; // fieldtraits.hh:196-202

@@ -59,6 +59,12 @@ enum
   NOISE_INJECTED = 2     // caller supplied (r1,r2) pairs, reference order
 };
 
+// Philox round keys k_r = key + r * Weyl (pf_rng.cuh), computed on the host
+struct PhiloxKeys
+{
+  uint32_t k0[10], k1[10];
+};
+
 struct PassArgs
 {
   // ---- line space: lines (a, b), a in [0,A) is the tile axis -------------
@@ -88,7 +94,8 @@ struct PassArgs
 
   // ---- noise ----------------------------------------------------------------
   int noise_kind;
-  unsigned long long seed, realization;
+  PhiloxKeys keys;         // round keys of the user seed
+  unsigned long long realization;
   long long cma, cmb, cme; // philox counter = a*cma + b*cmb + (e mod N/2)*cme
   const double2* noise;    // injected
   long long ima, imb, ime; // injected index = a*ima + b*imb + e*ime

@@ -249,11 +249,12 @@ load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
       n2 = __ldg(p.noise + ibase + (long long)e2 * p.ime);
     } else {
       const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
-      uint4 w = philox4x32_10(ctr, p.realization, p.seed);
       if constexpr (NOISE == NOISE_PHILOX_FAST) {
+        const uint4 w = philox4x32_r<7>(ctr, p.realization, p.keys);
         n1 = box_muller_fast(w.x, w.y);
         n2 = box_muller_fast(w.z, w.w);
       } else {
+        const uint4 w = philox4x32_r<10>(ctr, p.realization, p.keys);
         n1 = box_muller_f64(w.x, w.y);
         n2 = box_muller_f64(w.z, w.w);
       }

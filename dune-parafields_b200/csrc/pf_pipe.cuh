@@ -37,12 +37,14 @@ struct PCfg
   static constexpr int THREADS = 32 * (CW + 1);
   static constexpr int SLOT_BYTES = C::PITCH * 16;
   static constexpr int SLOTS_BYTES = LT * SLOT_BYTES;
-  static constexpr int STAGE_BYTES = 65536;
+  static constexpr int NSTAGE = 2;           // double-buffered output stage
+  static constexpr int STAGE_BYTES = 32768;  // per stage
   static constexpr int SR = STAGE_BYTES / (LT * 16); // stage rows per chunk
   static constexpr int BOXR = SR < 256 ? SR : 256;   // TMA box rows
   static constexpr int SUB_BYTES = SR * 128;
   static constexpr int BAR_BYTES = 128;
-  static constexpr int SMEM_TILE = SLOTS_BYTES + STAGE_BYTES + BAR_BYTES + 1024;
+  static constexpr int SMEM_TILE =
+    SLOTS_BYTES + NSTAGE * STAGE_BYTES + BAR_BYTES + 1024;
   static constexpr int SMEM_LINES = SLOTS_BYTES + BAR_BYTES + 1024;
   static_assert(SLOTS_BYTES % 1024 == 0, "stage must stay 1024-byte aligned");
   static_assert(N + 2 <= C::PITCH, "c2r landing zone needs 2*(N/2+1) entries");
@@ -145,18 +147,28 @@ struct PSmem
   {
     return reinterpret_cast<cplx*>(base + (size_t)s * P::SLOT_BYTES);
   }
-  __device__ __forceinline__ unsigned char* stage() const
+  __device__ __forceinline__ unsigned char* stage(int i) const
   {
-    return base + P::SLOTS_BYTES;
+    return base + P::SLOTS_BYTES + (size_t)i * P::STAGE_BYTES;
   }
-  // barriers: [0..CW) input per warp, [CW] stage full, [CW+1] stage free
+  // barriers: [0..CW) input per warp, [CW + i] stage i full,
+  // [CW + 2 + i] stage i free
   __device__ __forceinline__ uint32_t bar(int i, bool tile) const
   {
-    return smem_u32(base + P::SLOTS_BYTES + (tile ? P::STAGE_BYTES : 0)) + 8u * i;
+    return smem_u32(base + P::SLOTS_BYTES +
+                    (tile ? P::NSTAGE * P::STAGE_BYTES : 0)) +
+           8u * i;
   }
 };
 
+__device__ __forceinline__ void
+bulk_wait_read1()
+{
+  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
+
 // the store warp's loop: wait for a full stage, write it with TMA, release
+// the PREVIOUS stage once its bulk group has been read out of shared memory
 template <int N>
 __device__ __forceinline__ void
 store_warp_loop(const PassArgs& p, const CUtensorMap* tm, const PSmem<N>& sm,
@@ -165,14 +177,14 @@ store_warp_loop(const PassArgs& p, const CUtensorMap* tm, const PSmem<N>& sm,
   using P = PCfg<N>;
   if ((threadIdx.x & 31) != 0)
     return;
-  const uint32_t full = sm.bar(P::CW, true), free_ = sm.bar(P::CW + 1, true);
-  const uint32_t st = smem_u32(sm.stage());
   const int nchunk = (p.keep + P::SR - 1) / P::SR;
   uint32_t it = 0;
   for (long long T = blockIdx.x; T < ntiles; T += gridDim.x) {
     const int at = (int)(T % ntA), b = (int)(T / ntA);
     for (int c = 0; c < nchunk; c++, it++) {
-      mbar_wait(full, it & 1);
+      const int s = it & 1;
+      mbar_wait(sm.bar(P::CW + s, true), (it >> 1) & 1);
+      const uint32_t st = smem_u32(sm.stage(s));
       const int rows = min(P::SR, p.keep - c * P::SR);
 #pragma unroll
       for (int sub = 0; sub < P::SUBS; sub++) {
@@ -183,8 +195,10 @@ store_warp_loop(const PassArgs& p, const CUtensorMap* tm, const PSmem<N>& sm,
         }
       }
       bulk_commit();
-      bulk_wait_read0();
-      mbar_arrive(free_);
+      if (it > 0) {
+        bulk_wait_read1();
+        mbar_arrive(sm.bar(P::CW + 2 + (s ^ 1), true));
+      }
     }
   }
   bulk_wait0();
@@ -198,12 +212,12 @@ stage_out(const cplx (&v)[LineCfg<N>::E], const PSmem<N>& sm, int slot, int t,
           int keep, uint32_t& it)
 {
   using P = PCfg<N>;
-  const uint32_t full = sm.bar(P::CW, true), free_ = sm.bar(P::CW + 1, true);
-  unsigned char* st = sm.stage() + (slot >> 3) * P::SUB_BYTES;
   const int l8 = slot & 7;
   const int nchunk = (keep + P::SR - 1) / P::SR;
   for (int c = 0; c < nchunk; c++, it++) {
-    mbar_wait(free_, (it & 1) ^ 1);
+    const int s = it & 1;
+    mbar_wait(sm.bar(P::CW + 2 + s, true), ((it >> 1) & 1) ^ 1);
+    unsigned char* st = sm.stage(s) + (slot >> 3) * P::SUB_BYTES;
     const int lo = c * P::SR;
     const int hi = min(keep, lo + P::SR);
 #pragma unroll
@@ -217,7 +231,7 @@ stage_out(const cplx (&v)[LineCfg<N>::E], const PSmem<N>& sm, int slot, int t,
     fence_proxy_async();
     __syncwarp();
     if ((threadIdx.x & 31) == 0)
-      mbar_arrive(full);
+      mbar_arrive(sm.bar(P::CW + s, true));
   }
 }
 
@@ -230,8 +244,10 @@ pipe_init(const PSmem<N>& sm, bool tile)
     for (int w = 0; w < P::CW; w++)
       mbar_init(sm.bar(w, tile), 1);
     if (tile) {
-      mbar_init(sm.bar(P::CW, true), P::CW);
-      mbar_init(sm.bar(P::CW + 1, true), 1);
+      for (int i = 0; i < P::NSTAGE; i++) {
+        mbar_init(sm.bar(P::CW + i, true), P::CW);
+        mbar_init(sm.bar(P::CW + 2 + i, true), 1);
+      }
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
@@ -281,11 +297,12 @@ load_noise_p(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
       n2 = __ldg(p.noise + ibase + (long long)(e + N / 2) * p.ime);
     } else {
       const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
-      const uint4 w = philox4x32_10(ctr, p.realization, p.seed);
       if constexpr (NOISE == NOISE_PHILOX_FAST) {
+        const uint4 w = philox4x32_r<7>(ctr, p.realization, p.keys);
         n1 = box_muller_fast(w.x, w.y);
         n2 = box_muller_fast(w.z, w.w);
       } else {
+        const uint4 w = philox4x32_r<10>(ctr, p.realization, p.keys);
         n1 = box_muller_f64(w.x, w.y);
         n2 = box_muller_f64(w.z, w.w);
       }
@@ -403,7 +420,10 @@ kp_c2t(const PassArgs p, const cplx* __restrict__ tw2,
     __syncwarp();
     line_fft_phase2_load<N>(v, buf, t);
     __syncwarp();
-    // the exchange area is free again: start the next tile's copy
+    // the exchange area is free again: start the next tile's copy (generic
+    // accesses of every lane ordered before the async-proxy write)
+    fence_proxy_async();
+    __syncwarp();
     const long long Tn = T + gridDim.x;
     if (Tn < ntiles)
       issue(Tn);
@@ -474,6 +494,7 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
     line_fft_phase1<N, +1>(v, buf, t);
     __syncwarp();
     line_fft_phase2_load<N>(v, buf, t);
+    fence_proxy_async();
     __syncwarp();
     const long long Tn = T + gridDim.x;
     if (Tn < ntiles)
@@ -486,9 +507,11 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
         const int e = t + P::TPL * q;
         if (e < p.keep) {
           if (v0)
-            out[L0 * p.out_pitch + e] = apply_transform_c<TR>(v[q].x, p.tparam);
+            out[L0 * p.out_pitch + e] =
+              apply_transform_c<TR>(v[q].x * p.scale, p.tparam);
           if (v1)
-            out[L1 * p.out_pitch + e] = apply_transform_c<TR>(v[q].y, p.tparam);
+            out[L1 * p.out_pitch + e] =
+              apply_transform_c<TR>(v[q].y * p.scale, p.tparam);
         }
       }
     });

@@ -17,6 +17,10 @@ CASES = [
     dict(cells=[8, 8, 8], covariance="exponential", corr_length=0.05),
     dict(cells=[16, 16], covariance="gaussian", corr_length=0.05, approximate=True),
     dict(cells=[8, 8, 8], covariance="spherical", corr_length=0.05),
+    # long lines (N >= 256): persistent TMA-pipelined pass kernels
+    dict(cells=[128, 128, 8], covariance="exponential", corr_length=0.1),
+    dict(cells=[8, 8, 128], covariance="spherical", corr_length=0.2),
+    dict(cells=[256, 2, 128], covariance="exponential", corr_length=[0.1, 0.3, 0.05], anisotropy="axiparallel"),
     # ragged / anisotropic
     dict(cells=[64, 16], covariance="exponential", corr_length=0.1, extensions=[2.0, 0.5]),
     dict(cells=[16, 8, 32], covariance="gaussian", corr_length=[0.05, 0.03, 0.02], anisotropy="axiparallel", approximate=True),
@@ -74,7 +78,7 @@ def test_generate_from_reference_noise(m, case):
         assert rel(f, f_o) < TOL
 
 
-@pytest.mark.parametrize("case", CASES[:10], ids=ids)
+@pytest.mark.parametrize("case", CASES[:13], ids=ids)
 @pytest.mark.parametrize("op", ["matrix", "root", "inverse_ext"])
 def test_operators_match_oracle(m, case, op):
     o = ol.Oracle(**case)
