@@ -21,7 +21,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libparafields_cuda.so")
+LIB_PATH = os.environ.get("PF_LIB") or os.path.join(CSRC, "libparafields_cuda.so")
 INCLUDE_DIR = os.path.join(os.path.dirname(_HERE), "include")
 
 COVARIANCE = {

@@ -212,11 +212,14 @@ table_row(const PassArgs& p, int a, int b)
 // white noise scaled by sigma.  Follows Matrix::generateField's loop
 // (matrix.hh:396-421) and FieldBackend::set (r2cfieldbackend.hh:305-325,
 // dftfieldbackend.hh:276-280); the table holds sqrt(lambda)/sqrt(2)
-// (hermitian) or sqrt(lambda) (DFT backend rule).
+// (hermitian) or sqrt(lambda) (DFT backend rule).  The sigma row is fetched
+// up front (registers are free before the line is populated) and the rare
+// cases (self-conjugate entries, `corrected` planes) sit outside the
+// unrolled loop.
 template <int N, int NOISE>
 __device__ __forceinline__ void
 load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
-           bool valid)
+             bool valid)
 {
   using C = LineCfg<N>;
   constexpr int H = C::E / 2;
@@ -228,25 +231,26 @@ load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
     return;
   }
   const double* row = table_row(p, a, b);
-  const bool a_self = (2 * a) % p.na_self == 0;
-  const bool b_self = (2 * b) % p.nb_self == 0;
-  const bool line_self = p.hermitian && a_self && b_self;
-  const bool plane = p.hermitian && p.corrected &&
-                     (p.plane_axis == 0 ? a_self : b_self);
-  const double boost = plane ? SQRT2 : 1.0;
+  // second half of the line: e + N/2, or its mirror N/2 - e (compact table)
+  const double* row2 = row + N / 2;
+  const int dir2 = p.tab_mirror_e ? -1 : 1;
   const unsigned long long cbase =
     (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
   const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
+  double s1[H], s2[H];
 #pragma unroll
   for (int q = 0; q < H; q++) {
     const int e = t + C::TPL * q; // < N/2
-    const int e2 = e + N / 2;
-    const double s1 = __ldg(row + e) * boost;
-    const double s2 = __ldg(row + (p.tab_mirror_e ? N / 2 - e : e2)) * boost;
+    s1[q] = __ldg(row + e);
+    s2[q] = __ldg(row2 + dir2 * e);
+  }
+#pragma unroll
+  for (int q = 0; q < H; q++) {
+    const int e = t + C::TPL * q;
     double2 n1, n2;
     if constexpr (NOISE == NOISE_INJECTED) {
       n1 = __ldg(p.noise + ibase + (long long)e * p.ime);
-      n2 = __ldg(p.noise + ibase + (long long)e2 * p.ime);
+      n2 = __ldg(p.noise + ibase + (long long)(e + N / 2) * p.ime);
     } else {
       const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
       if constexpr (NOISE == NOISE_PHILOX_FAST) {
@@ -259,16 +263,24 @@ load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
         n2 = box_muller_f64(w.z, w.w);
       }
     }
-    cplx x1 = make_double2(s1 * n1.x, s1 * n1.y);
-    cplx x2 = make_double2(s2 * n2.x, s2 * n2.y);
-    if (e == 0 && line_self) {
-      // self-conjugate entries (e = 0 and e2 = N/2): real, full weight
-      const double f = plane ? 1.0 : SQRT2;
-      x1 = make_double2(x1.x * f, 0.);
-      x2 = make_double2(x2.x * f, 0.);
+    v[q] = make_double2(s1[q] * n1.x, s1[q] * n1.y);
+    v[q + H] = make_double2(s2[q] * n2.x, s2[q] * n2.y);
+  }
+  if (p.hermitian) {
+    const bool a_self = (2 * a) % p.na_self == 0;
+    const bool b_self = (2 * b) % p.nb_self == 0;
+    const bool plane = p.corrected && (p.plane_axis == 0 ? a_self : b_self);
+    if (plane) {
+#pragma unroll
+      for (int q = 0; q < C::E; q++)
+        v[q] = make_double2(v[q].x * SQRT2, v[q].y * SQRT2);
     }
-    v[q] = x1;
-    v[q + H] = x2;
+    if (t == 0 && a_self && b_self) {
+      // self-conjugate entries e = 0 and e = N/2: real, full weight
+      const double f = plane ? 1.0 : SQRT2;
+      v[0] = make_double2(v[0].x * f, 0.);
+      v[H] = make_double2(v[H].x * f, 0.);
+    }
   }
 }
 
@@ -288,12 +300,29 @@ load_contig(cplx (&v)[LineCfg<N>::E], const cplx* __restrict__ line, int t,
 // ---------------------------------------------------------------------------
 // storers
 // ---------------------------------------------------------------------------
-// tile store: out[base + e*ose + l], l = line in tile (contiguous), e < keep
+// tile store: out[base + e*ose + l], l = line in tile (contiguous), e < keep.
+// The stage holds rows of LPC complex numbers (one per line of the tile);
+// the 16-byte chunks of a row pair are XOR-swizzled so that both the
+// per-line writes (stride one row) and the row-major reads are free of bank
+// conflicts for LPC = 4 (N = 1024) and LPC = 8 (N = 512).
+template <int N>
+__device__ __forceinline__ int
+stage_slot(int e, int l)
+{
+  using K = KCfg<N>;
+  if constexpr (K::LPC == 4)
+    return e * 4 + (l ^ ((e >> 1) & 3));
+  else if constexpr (K::LPC == 8)
+    return e * 8 + (l ^ (e & 7));
+  else
+    return e * K::SP + l;
+}
+
 template <int N>
 __device__ __forceinline__ void
 tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
-           cplx* __restrict__ out, long long base, long long ose,
-           int lines_valid, double scale)
+           cplx* __restrict__ obase, long long ose, int lines_valid,
+           double scale)
 {
   using K = KCfg<N>;
   __syncthreads(); // exchange area is about to be reused as the stage
@@ -301,15 +330,26 @@ tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
   for (int q = 0; q < K::E; q++) {
     const int e = t + K::TPL * q;
     if (e < keep)
-      stage[e * K::SP + lic] = make_double2(v[q].x * scale, v[q].y * scale);
+      stage[stage_slot<N>(e, lic)] =
+        make_double2(v[q].x * scale, v[q].y * scale);
   }
   __syncthreads();
   const int total = keep * K::LPC;
   for (int idx = threadIdx.x; idx < total; idx += PF_THREADS) {
     const int l = idx % K::LPC, e = idx / K::LPC;
     if (l < lines_valid)
-      out[base + (long long)e * ose + l] = stage[e * K::SP + l];
+      obase[(long long)e * ose + l] = stage[stage_slot<N>(e, l)];
   }
+}
+
+// output base pointer of a tile, materialised early so that the kernel
+// parameters it needs are not fetched on the critical path after the FFT
+__device__ __forceinline__ cplx*
+tile_base(const PassArgs& p, int b, int first_line)
+{
+  cplx* o = reinterpret_cast<cplx*>(p.out) + (long long)b * p.osb + first_line;
+  asm volatile("" : "+l"(o));
+  return o;
 }
 
 // ===========================================================================
@@ -317,8 +357,11 @@ tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
 // ===========================================================================
 
 // pass A: noise -> inverse FFT -> tile
+#ifndef PF_GEN_MINB
+#define PF_GEN_MINB 3
+#endif
 template <int N, int NOISE>
-__global__ void __launch_bounds__(PF_THREADS, 3)
+__global__ void __launch_bounds__(PF_THREADS, PF_GEN_MINB)
 k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
 {
   using K = KCfg<N>;
@@ -328,13 +371,14 @@ k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
   const int ntA = (p.A + K::LPC - 1) / K::LPC;
   const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
   const int a = at * K::LPC + lic;
+  cplx* obase = tile_base(p, b, at * K::LPC);
+  long long ose = p.ose;
+  asm volatile("" : "+l"(ose));
   cplx v[K::E];
   load_noise<N, NOISE>(v, p, a, b, t, a < p.A);
   line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
   const int lv = min(K::LPC, p.A - at * K::LPC);
-  tile_store<N>(v, sm, lic, t, p.keep, reinterpret_cast<cplx*>(p.out),
-                (long long)b * p.osb + (long long)at * K::LPC, p.ose, lv,
-                p.scale);
+  tile_store<N>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
 }
 
 // 1D: noise -> inverse FFT -> real part / imaginary part lines
@@ -392,8 +436,7 @@ k_c2t(const PassArgs p, const cplx* __restrict__ tw2)
   load_contig<N>(v, line, t, p.n_valid, a < p.A);
   line_fft<N, DIR>(v, sm + lic * K::C::PITCH, t, tw2);
   const int lv = min(K::LPC, p.A - at * K::LPC);
-  tile_store<N>(v, sm, lic, t, p.keep, reinterpret_cast<cplx*>(p.out),
-                (long long)b * p.osb + (long long)at * K::LPC, p.ose, lv,
+  tile_store<N>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC), p.ose, lv,
                 p.scale);
 }
 
@@ -650,9 +693,8 @@ k_spec(const PassArgs p, const cplx* __restrict__ tw2)
     }
   } else {
     const int lv = min(K::LPC, p.A - at * K::LPC);
-    tile_store<N>(v, sm, lic, t, p.keep, reinterpret_cast<cplx*>(p.out),
-                  (long long)b * p.osb + (long long)at * K::LPC, p.ose, lv,
-                  1.0);
+    tile_store<N>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC), p.ose,
+                  lv, 1.0);
   }
 }
 

@@ -255,79 +255,6 @@ pipe_init(const PSmem<N>& sm, bool tile)
   __syncthreads();
 }
 
-// ---------------------------------------------------------------------------
-// white noise * sigma, register layout of load_noise (pf_kernels.cuh) with the
-// rare cases (self-conjugate entries, `corrected` planes) moved out of the
-// unrolled loop.  Follows matrix.hh:396-421 + r2cfieldbackend.hh:305-325.
-// ---------------------------------------------------------------------------
-template <int N, int NOISE>
-__device__ __forceinline__ void
-load_noise_p(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
-             bool valid)
-{
-  using C = LineCfg<N>;
-  constexpr int H = C::E / 2;
-  constexpr double SQRT2 = 1.41421356237309504880168872420969808;
-  if (!valid) {
-#pragma unroll
-    for (int q = 0; q < C::E; q++)
-      v[q] = make_double2(0., 0.);
-    return;
-  }
-  const double* row = table_row(p, a, b);
-  // second half of the line: e + N/2, or its mirror N/2 - e (compact table)
-  const double* row2 = row + N / 2;
-  const int dir2 = p.tab_mirror_e ? -1 : 1;
-  const unsigned long long cbase =
-    (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
-  const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
-  double s1[H], s2[H];
-#pragma unroll
-  for (int q = 0; q < H; q++) {
-    const int e = t + C::TPL * q; // < N/2
-    s1[q] = __ldg(row + e);
-    s2[q] = __ldg(row2 + dir2 * e);
-  }
-#pragma unroll
-  for (int q = 0; q < H; q++) {
-    const int e = t + C::TPL * q;
-    double2 n1, n2;
-    if constexpr (NOISE == NOISE_INJECTED) {
-      n1 = __ldg(p.noise + ibase + (long long)e * p.ime);
-      n2 = __ldg(p.noise + ibase + (long long)(e + N / 2) * p.ime);
-    } else {
-      const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
-      if constexpr (NOISE == NOISE_PHILOX_FAST) {
-        const uint4 w = philox4x32_r<7>(ctr, p.realization, p.keys);
-        n1 = box_muller_fast(w.x, w.y);
-        n2 = box_muller_fast(w.z, w.w);
-      } else {
-        const uint4 w = philox4x32_r<10>(ctr, p.realization, p.keys);
-        n1 = box_muller_f64(w.x, w.y);
-        n2 = box_muller_f64(w.z, w.w);
-      }
-    }
-    v[q] = make_double2(s1[q] * n1.x, s1[q] * n1.y);
-    v[q + H] = make_double2(s2[q] * n2.x, s2[q] * n2.y);
-  }
-  if (p.hermitian) {
-    const bool a_self = (2 * a) % p.na_self == 0;
-    const bool b_self = (2 * b) % p.nb_self == 0;
-    const bool plane = p.corrected && (p.plane_axis == 0 ? a_self : b_self);
-    if (plane) {
-#pragma unroll
-      for (int q = 0; q < C::E; q++)
-        v[q] = make_double2(v[q].x * SQRT2, v[q].y * SQRT2);
-    }
-    if (t == 0 && a_self && b_self) {
-      // self-conjugate entries e = 0 and e = N/2: real, full weight
-      const double f = plane ? 1.0 : SQRT2;
-      v[0] = make_double2(v[0].x * f, 0.);
-      v[H] = make_double2(v[H].x * f, 0.);
-    }
-  }
-}
-
 // ===========================================================================
 // pass A: noise -> inverse FFT -> transposed tile (k_gen_tile)
 // ===========================================================================
@@ -355,7 +282,7 @@ kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
     const int a = at * P::LT + slot;
     cplx v[P::E];
     // lines beyond A recompute the last valid line; the tensor store clips
-    load_noise_p<N, NOISE>(v, p, min(a, p.A - 1), b, t, true);
+    load_noise<N, NOISE>(v, p, min(a, p.A - 1), b, t, true);
     line_fft<N, +1>(v, buf, t, tw2);
     stage_out<N>(v, sm, slot, t, p.keep, it);
   }

@@ -128,7 +128,10 @@ class Oracle:
         threads=1,
         p0=0.0,
         p1=0.0,
+        periodic=False,
     ):
+        if periodic:
+            factor = 1  # fieldtraits.hh:196-202
         cells = list(cells)
         dim = len(cells)
         self.dim = dim
