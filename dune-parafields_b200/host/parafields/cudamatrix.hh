@@ -1,0 +1,352 @@
+// parafields/cudamatrix.hh -- the B200 covariance operator as a drop-in for
+// parafields::Matrix (reference: include/parafields/matrix.hh:59-1663).
+//
+//   using Field = parafields::RandomField<GridTraits,
+//                                         parafields::CudaMatrix,   // IsoMatrix
+//                                         parafields::CudaMatrix>;  // AnisoMatrix
+//
+// CudaMatrix<Traits> implements the members RandomField uses from Matrix
+// (matrix.hh:106,130,151,176,198,232,343,450,473) on top of the C ABI of
+// libparafields_cuda.so (include/parafields_cuda.h).  It works both with the
+// reference's own randomfield.hh / fieldtraits.hh / stochastic.hh (it is named
+// a friend there through the IsoMatrix / AnisoMatrix template parameters,
+// fieldtraits.hh:102-109, stochastic.hh:37-38) and with the stand-alone
+// headers shipped next to this file.
+//
+// Extra ini keys (all optional, section [cuda]):
+//   cuda.noise      philox (default): device Philox4x32 keyed by the seed
+//                   reference: the reference's CppRNGBackend stream
+//                     (std::default_random_engine + std::normal_distribution,
+//                     cpprngbackend.hh:49-58) drawn on the host and injected,
+//                     so generate(seed) reproduces the reference's field
+//   cuda.rng        fast (fp32 Box-Muller, default) | fp64
+//   cuda.sampler    reference (default) | corrected   
+//   cuda.maxFactor  embedding-factor retry bound (0 = off, the reference throws)
+//   cuda.device     CUDA device ordinal (-1 = current)
+#ifndef PARAFIELDS_CUDAMATRIX_HH
+#define PARAFIELDS_CUDAMATRIX_HH
+
+#include <array>
+#include <cstdint>
+#include <iostream>
+#include <memory>
+#include <random>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include <parafields_cuda.h>
+
+namespace parafields {
+
+template<typename Traits>
+class StochasticPart;
+
+template<typename Traits>
+class CudaMatrix
+{
+public:
+  // named as friends by the traits class; no per-element backends exist here
+  struct MatrixBackendType {};
+  struct FieldBackendType {};
+  struct RNGBackendType {};
+
+  using StochasticPartType = StochasticPart<Traits>;
+
+private:
+  using RF = typename Traits::RF;
+  enum { dim = Traits::dim };
+  static_assert(std::is_same<RF, double>::value,
+                "the CUDA path computes in fp64 (RangeField must be double)");
+  static_assert(dim >= 1 && dim <= 3, "CudaMatrix supports dim 1, 2, 3");
+
+  const std::shared_ptr<Traits> traits;
+  mutable pf_plan* plan = nullptr;
+  mutable bool filled = false;
+  bool referenceNoise = false;
+
+  static void check(int rc)
+  {
+    if (rc != 0)
+      throw std::runtime_error{ pf_last_error() };
+  }
+
+  static int covarianceId(const std::string& name)
+  {
+    static const std::pair<const char*, int> table[] = {
+      { "exponential", PF_COV_EXPONENTIAL },
+      { "gaussian", PF_COV_GAUSSIAN },
+      { "spherical", PF_COV_SPHERICAL },
+      { "separableExponential", PF_COV_SEPARABLE_EXPONENTIAL },
+      { "matern32", PF_COV_MATERN32 },
+      { "matern52", PF_COV_MATERN52 },
+      { "dampedOscillation", PF_COV_DAMPED_OSCILLATION },
+      { "gammaExponential", PF_COV_GAMMA_EXPONENTIAL },
+      { "cauchy", PF_COV_CAUCHY },
+      { "generalizedCauchy", PF_COV_GENERALIZED_CAUCHY },
+      { "cubic", PF_COV_CUBIC },
+      { "whiteNoise", PF_COV_WHITE_NOISE }
+    };
+    for (const auto& e : table)
+      if (name == e.first)
+        return e.second;
+    if (name == "matern")
+      throw std::runtime_error{
+        "general Matern covariance needs the GSL library (use matern32 or "
+        "matern52 on the CUDA path)"
+      };
+    if (name == "custom-iso" || name == "custom-aniso")
+      throw std::runtime_error{
+        "custom covariance classes are host functors and cannot be evaluated "
+        "by the CUDA path"
+      };
+    // same text as matrix.hh:267-268
+    throw std::runtime_error{ "covariance structure " + name + " not known" };
+  }
+
+public:
+  explicit CudaMatrix(const std::shared_ptr<Traits>& traits_)
+    : traits(traits_)
+  {
+    update();
+  }
+
+  CudaMatrix(const CudaMatrix&) = delete;
+  CudaMatrix& operator=(const CudaMatrix&) = delete;
+
+  ~CudaMatrix()
+  {
+    if (plan)
+      pf_plan_destroy(plan);
+  }
+
+  // Matrix::update, matrix.hh:130-142: (re)read sizes after construction or
+  // refinement; the eigenvalues are recomputed lazily
+  void update()
+  {
+    if (plan) {
+      pf_plan_destroy(plan);
+      plan = nullptr;
+    }
+    filled = false;
+    const auto& config = (*traits).config;
+    pf_desc d;
+    pf_desc_default(&d);
+    d.dim = dim;
+    for (unsigned int i = 0; i < dim; i++) {
+      d.cells[i] = (*traits).cells[i];
+      d.extensions[i] = (*traits).extensions[i];
+    }
+    d.embedding_factor = (*traits).embeddingFactor;
+    d.periodic = (*traits).periodic ? 1 : 0;
+    d.approximate = (*traits).approximate ? 1 : 0;
+    d.variance = (*traits).variance;
+    d.covariance = covarianceId((*traits).covariance);
+    d.cg_iterations = (*traits).cgIterations;
+    d.threshold = config.template get<RF>("embedding.threshold", 1e-14);
+
+    // stochastic.anisotropy / corrLength, matrix.hh:496-508 and
+    // covariance.hh:32,61,94 (arity follows the anisotropy)
+    const std::string anisotropy =
+      config.template get<std::string>("stochastic.anisotropy", "none");
+    if (anisotropy == "none") {
+      d.anisotropy = PF_ANISO_NONE;
+      d.corr_length[0] = config.template get<RF>("stochastic.corrLength");
+    } else if (anisotropy == "axiparallel") {
+      d.anisotropy = PF_ANISO_AXIPARALLEL;
+      const auto c =
+        config.template get<std::array<RF, dim>>("stochastic.corrLength");
+      for (unsigned int i = 0; i < dim; i++)
+        d.corr_length[i] = c[i];
+    } else if (anisotropy == "geometric") {
+      d.anisotropy = PF_ANISO_GEOMETRIC;
+      const auto c =
+        config.template get<std::array<RF, dim * dim>>("stochastic.corrLength");
+      for (unsigned int i = 0; i < dim * dim; i++)
+        d.corr_length[i] = c[i];
+    } else
+      throw std::runtime_error{
+        "stochastic.anisotropy must be \"none\", \"axiparallel\" or \"geometric\""
+      };
+
+    if (d.covariance == PF_COV_GAMMA_EXPONENTIAL)
+      d.cov_param[0] = config.template get<RF>("stochastic.expGamma");
+    if (d.covariance == PF_COV_GENERALIZED_CAUCHY) {
+      d.cov_param[0] = config.template get<RF>("stochastic.cauchyAlpha");
+      d.cov_param[1] = config.template get<RF>("stochastic.cauchyBeta");
+    }
+
+    // randomField.transform is applied at evaluation time by the host
+    // (ValueTransform, randomfield.hh:600); the plan only needs it for the
+    // fused variant used by the batch API
+    const std::string transform =
+      config.template get<std::string>("randomField.transform", "none");
+    if (transform == "logNormal")
+      d.transform = PF_TRANSFORM_LOG_NORMAL;
+    else if (transform == "foldedNormal")
+      d.transform = PF_TRANSFORM_FOLDED_NORMAL;
+    else if (transform == "sign")
+      d.transform = PF_TRANSFORM_SIGN;
+    else if (transform == "boxCox") {
+      d.transform = PF_TRANSFORM_BOX_COX;
+      d.boxcox_lambda = config.template get<RF>("transform.boxCoxLambda");
+    }
+
+    const std::string noise =
+      config.template get<std::string>("cuda.noise", "philox");
+    if (noise != "philox" && noise != "reference")
+      throw std::runtime_error{ "cuda.noise must be \"philox\" or \"reference\"" };
+    referenceNoise = (noise == "reference");
+    d.rng_mode =
+      config.template get<std::string>("cuda.rng", "fast") == "fp64" ? 1 : 0;
+    d.parity_mode =
+      config.template get<std::string>("cuda.sampler", "reference") ==
+          "corrected"
+        ? 1
+        : 0;
+    d.max_factor = config.template get<unsigned int>("cuda.maxFactor", 0);
+    d.device = config.template get<int>("cuda.device", -1);
+    // the reference's R2C-matrix census quirk is
+    // kept so that the clamp pattern matches the reference
+    d.census_quirk = (d.anisotropy == PF_ANISO_GEOMETRIC) ? 1 : 0;
+
+    if ((*traits).commSize != 1)
+      throw std::runtime_error{
+        "CudaMatrix: one process drives the GPUs of a plan; MPI ranks > 1 "
+        "are not supported (use the multi-GPU plan instead)"
+      };
+
+    check(pf_plan_create(&d, &plan));
+  }
+
+  // Matrix::operator*, matrix.hh:151-160
+  StochasticPartType operator*(const StochasticPartType& input) const
+  {
+    return apply(PF_OP_MATRIX, input);
+  }
+
+  // Matrix::multiplyRoot, matrix.hh:176-185
+  StochasticPartType multiplyRoot(const StochasticPartType& input) const
+  {
+    return apply(PF_OP_ROOT, input);
+  }
+
+  // Matrix::multiplyInverse, matrix.hh:198-215 (PCG of matrix.hh:1331-1448)
+  StochasticPartType multiplyInverse(const StochasticPartType& input) const
+  {
+    ensureFilled();
+    StochasticPartType output(input);
+    unsigned int iterations = 0;
+    check(pf_solve(plan, input.dataVector.data(), output.dataVector.data(),
+                   &iterations));
+    output.evalValid = false;
+    if ((*traits).verbose && (*traits).rank == 0)
+      std::cout << iterations << " iterations" << std::endl;
+    return output;
+  }
+
+  // Matrix::fillTransformedMatrix, matrix.hh:232-331
+  template<typename Covariance = void>
+  void fillTransformedMatrix() const
+  {
+    if constexpr (!std::is_same<Covariance, void>::value)
+      throw std::runtime_error{
+        "custom covariance classes are host functors and cannot be evaluated "
+        "by the CUDA path"
+      };
+    pf_eig_stats stats;
+    const int rc = pf_compute_eigenvalues(plan, &stats);
+    if ((*traits).verbose && (*traits).rank == 0)
+      std::cout << stats.small_count << " small, " << stats.zero_count
+                << " approx. zero and " << stats.negative_count
+                << " large negative eigenvalues in covariance matrix, smallest "
+                << stats.smallest << std::endl;
+    if (rc == PF_ERR_NEGATIVE_EIGENVALUES && (*traits).rank == 0)
+      std::cerr << "negative eigenvalues in covariance matrix, "
+                << "consider increasing embeddingFactor, or alternatively "
+                << "allow generation of approximate samples" << std::endl;
+    check(rc);
+    filled = true;
+  }
+
+  // Matrix::generateField, matrix.hh:343-438
+  void generateField(unsigned int seed, StochasticPartType& stochasticPart) const
+  {
+    ensureFilled();
+    stochasticPart.dataVector.resize((*traits).localDomainSize);
+    seed += (*traits).rank; // different seed for each processor (:352)
+    if (referenceNoise) {
+      if (dim == 1 && spare.size() == stochasticPart.dataVector.size()) {
+        // DFT field backend: every second call returns the imaginary part
+        // and ignores its seed (matrix.hh:349,433-437)
+        stochasticPart.dataVector = spare;
+        spare.clear();
+      } else {
+        const size_t entries = pf_noise_entries(plan);
+        std::vector<double> noise(2 * entries);
+        std::default_random_engine generator(seed);
+        std::normal_distribution<RF> normalDist(0., 1.);
+        for (auto& v : noise)
+          v = normalDist(generator);
+        if (dim == 1)
+          spare.resize(stochasticPart.dataVector.size());
+        check(pf_generate_from_noise(plan, noise.data(),
+                                     stochasticPart.dataVector.data(),
+                                     dim == 1 ? spare.data() : nullptr));
+      }
+    } else
+      check(
+        pf_generate(plan, seed, 0, stochasticPart.dataVector.data(), 0));
+    stochasticPart.evalValid = false;
+  }
+
+  // Matrix::generateUncorrelatedField, matrix.hh:450-462
+  void generateUncorrelatedField(unsigned int seed,
+                                 StochasticPartType& stochasticPart) const
+  {
+    stochasticPart.dataVector.resize((*traits).localDomainSize);
+    seed += (*traits).rank;
+    if (referenceNoise) {
+      std::default_random_engine generator(seed);
+      std::normal_distribution<RF> normalDist(0., 1.);
+      for (auto& v : stochasticPart.dataVector)
+        v = normalDist(generator);
+    } else
+      check(pf_generate_uncorrelated(plan, seed,
+                                     stochasticPart.dataVector.data()));
+    stochasticPart.evalValid = false;
+  }
+
+  // Matrix::setVarianceAsField, matrix.hh:473-479
+  void setVarianceAsField(StochasticPartType& stochasticPart) const
+  {
+    stochasticPart.dataVector.resize((*traits).localDomainSize);
+    check(pf_set_variance_as_field(plan, stochasticPart.dataVector.data()));
+    stochasticPart.evalValid = false;
+  }
+
+  // access for callers that want to keep data on the device
+  pf_plan* cudaPlan() const { return plan; }
+
+private:
+  mutable std::vector<RF> spare;
+
+  void ensureFilled() const
+  {
+    if (!filled)
+      fillTransformedMatrix();
+  }
+
+  StochasticPartType apply(int op, const StochasticPartType& input) const
+  {
+    ensureFilled();
+    StochasticPartType output(input);
+    check(pf_apply(plan, op, input.dataVector.data(), output.dataVector.data()));
+    output.evalValid = false;
+    return output;
+  }
+};
+
+} // namespace parafields
+
+#endif // PARAFIELDS_CUDAMATRIX_HH

@@ -1,0 +1,182 @@
+// oracle/dropin_test.cpp -- drop-in proof.  TEST INFRASTRUCTURE.
+//
+// The UNMODIFIED reference parafields::RandomField (from /root/reference) is
+// instantiated twice in one process:
+//   RandomField<GridTraits>                           reference CPU matrices
+//                                                     (FFTW via oracle/shim)
+//   RandomField<GridTraits, CudaMatrix, CudaMatrix>   this repository's plugin
+// and both are driven through the reference's own public API with the same
+// configuration and seed.  With cuda.noise = reference the plugin consumes the
+// reference's RNG stream, so every result must agree to 1e-10 (fp64).
+// Built by oracle/Makefile into oracle/_ref/dropin_test (needs the reference
+// checkout at build time, a B200 at run time; run by tests/test_dropin.py).
+#include <cmath>
+#include <cstdio>
+#include <iostream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include <dune/common/fvector.hh>
+#include <dune/common/parametertree.hh>
+#include <dune/common/parametertreeparser.hh>
+
+#include <parafields/cudamatrix.hh>
+#include <parafields/randomfield.hh>
+
+template<typename DF, typename RF, unsigned int dimension>
+class GridTraits
+{
+public:
+  enum
+  {
+    dim = dimension
+  };
+  using RangeField = RF;
+  using Scalar = Dune::FieldVector<RF, 1>;
+  using DomainField = DF;
+  using Domain = Dune::FieldVector<DF, dim>;
+};
+
+static int failures = 0;
+
+// compares the raw cell values (StochasticPart::dataVector; this test file is
+// compiled with -fno-access-control).  bulkEvaluate is not used here because
+// the reference's spare-field branch (matrix.hh:433-437) leaves evalValid set,
+// so it would return the previous field.
+template<class A, class B>
+double
+relDiff(const A& a, const B& b)
+{
+  const auto& va = a.stochasticPart.dataVector;
+  const auto& vb = b.stochasticPart.dataVector;
+  double num = 0., den = 0.;
+  for (size_t i = 0; i < va.size() && i < vb.size(); i++) {
+    num = std::max(num, std::abs(va[i] - vb[i]));
+    den = std::max(den, std::abs(va[i]));
+  }
+  return va.size() == vb.size() && den > 0. ? num / den : 1e300;
+}
+
+static void
+report(const std::string& what, double err, double tol)
+{
+  const bool ok = err < tol;
+  if (!ok)
+    failures++;
+  std::printf("  %-34s rel err %.3e  %s\n", what.c_str(), err, ok ? "ok" : "FAIL");
+}
+
+template<unsigned int dim>
+void
+run(const std::string& name, const std::string& ini)
+{
+  using GT = GridTraits<double, double, dim>;
+  using RefField = parafields::RandomField<GT>;
+  using CudaField =
+    parafields::RandomField<GT, parafields::CudaMatrix, parafields::CudaMatrix>;
+  std::printf("%s\n", name.c_str());
+  Dune::ParameterTree config;
+  std::istringstream in(ini);
+  Dune::ParameterTreeParser::readINITree(in, config);
+  Dune::ParameterTree cconfig = config;
+  cconfig["cuda.noise"] = "reference";
+
+  RefField ref(config);
+  CudaField gpu(cconfig);
+  ref.generate(20240611u);
+  gpu.generate(20240611u);
+  report("generate(seed)", relDiff(ref, gpu), 1e-10);
+  if (dim == 1) { // spare field of the DFT backend
+    ref.generate(1u);
+    gpu.generate(1u);
+    report("generate (spare field)", relDiff(ref, gpu), 1e-10);
+  }
+  {
+    RefField a(ref);
+    CudaField b(gpu);
+    a.timesMatrix();
+    b.timesMatrix();
+    report("timesMatrix", relDiff(a, b), 1e-10);
+  }
+  {
+    RefField a(ref);
+    CudaField b(gpu);
+    a.timesMatrixRoot();
+    b.timesMatrixRoot();
+    report("timesMatrixRoot", relDiff(a, b), 1e-10);
+  }
+  {
+    RefField a(ref);
+    CudaField b(gpu);
+    a.timesInverseMatrix();
+    b.timesInverseMatrix();
+    report("timesInverseMatrix (pinned CG)", relDiff(a, b), 1e-8);
+  }
+  if (dim > 1) { // fieldtest.cc:103-130: M^-1 M x ~ x (CG count is pinned)
+    CudaField b(gpu);
+    b.timesMatrix();
+    b.timesInverseMatrix();
+    b -= gpu;
+    report("|M^-1 M x - x| / |x| (plugin)",
+           std::sqrt(b * b) / std::sqrt(gpu * gpu), 1e-2);
+  }
+  { // vector space operations of the reference run on plugin fields unchanged
+    CudaField b(gpu);
+    b *= 2.;
+    b.axpy(gpu, -1.);
+    b -= gpu;
+    report("(2x - x) - x == 0", std::sqrt(b * b), 1e-12);
+  }
+  { // evaluation-time value transform through the reference's bulkEvaluate
+    std::vector<typename RefField::Traits::RangeType> va, vb;
+    typename RefField::Traits::Indices sa, sb;
+    RefField a(ref);
+    CudaField b(gpu);
+    a.bulkEvaluate(va, sa);
+    b.bulkEvaluate(vb, sb);
+    double num = 0., den = 0.;
+    for (size_t i = 0; i < va.size(); i++) {
+      num = std::max(num, std::abs(va[i][0] - vb[i][0]));
+      den = std::max(den, std::abs(va[i][0]));
+    }
+    report("bulkEvaluate (transform)", num / den, 1e-10);
+  }
+  { // device RNG: different from the reference stream but a valid field
+    Dune::ParameterTree pconfig = config;
+    CudaField p(pconfig);
+    p.generate(7u);
+    const double n2 = p * p / p.dofs();
+    report("philox field: |mean square - 1|", std::abs(n2 - 1.), 0.6);
+  }
+}
+
+int
+main()
+{
+  const std::string tail = "[stochastic]\nvariance = 1.\n";
+  run<1>("1D 32, exponential (test/randomfield1d.ini)",
+         "[grid]\nextensions = 1\ncells = 32\n" + tail +
+           "covariance = exponential\ncorrLength = 0.05\n");
+  run<2>("2D 16x16, exponential (test/randomfield2d.ini)",
+         "[grid]\nextensions = 1 1\ncells = 16 16\n" + tail +
+           "covariance = exponential\ncorrLength = 0.05\n[randomField]\ncgIterations = 4\n");
+  run<3>("3D 8x8x8, spherical (test/randomfield3d.ini)",
+         "[grid]\nextensions = 1 1 1\ncells = 8 8 8\n" + tail +
+           "covariance = spherical\ncorrLength = 0.05\n[randomField]\ncgIterations = 4\n");
+  run<3>("3D 16x8x32, gaussian axiparallel, logNormal (K2 scaled)",
+         "[grid]\nextensions = 1 1 1\ncells = 16 8 32\n" + tail +
+           "covariance = gaussian\nanisotropy = axiparallel\ncorrLength = 0.05 0.03 0.02\n"
+           "[embedding]\napproximate = 1\n[randomField]\ntransform = logNormal\ncgIterations = 4\n");
+  run<2>("2D 32x64, cubic geometric (K4 scaled)",
+         "[grid]\nextensions = 1 1\ncells = 32 64\n" + tail +
+           "covariance = cubic\nanisotropy = geometric\ncorrLength = 0.08 0.03 0.03 0.05\n"
+           "[embedding]\napproximate = 1\n[randomField]\ncgIterations = 4\n");
+  run<2>("2D 128x128, matern32 with caches (K5 scaled)",
+         "[grid]\nextensions = 1 1\ncells = 128 128\n" + tail +
+           "covariance = matern32\ncorrLength = 0.05\n"
+           "[randomField]\ncgIterations = 4\ncacheInvMatvec = 1\ncacheInvRootMatvec = 1\n");
+  std::printf("%s (%d failure%s)\n", failures ? "DROP-IN FAILED" : "DROP-IN OK",
+              failures, failures == 1 ? "" : "s");
+  return failures ? 1 : 0;
+}
