@@ -62,6 +62,9 @@ ABI_SYMBOLS = [
     "pf_domain_size",
     "pf_extended_size",
     "pf_noise_entries",
+    "pf_local_domain_size",
+    "pf_slab_handle",
+    "pf_slab_connect",
     "pf_compute_eigenvalues",
     "pf_eigenvalue_count",
     "pf_get_eigenvalues",
@@ -106,6 +109,8 @@ class PfDesc(C.Structure):
         ("census_quirk", C.c_int),
         ("max_factor", C.c_uint),
         ("device", C.c_int),
+        ("n_ranks", C.c_int),
+        ("rank", C.c_int),
     ]
 
 
@@ -165,7 +170,9 @@ def lib():
     L.pf_plan_launch_count.restype = C.c_ulonglong
     L.pf_plan_set_profiling.argtypes = [vp, C.c_int]
     L.pf_plan_get_pass_times.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
-    for f in (L.pf_domain_size, L.pf_extended_size, L.pf_noise_entries):
+    L.pf_slab_handle.argtypes = [vp, vp]
+    L.pf_slab_connect.argtypes = [vp, vp, C.c_int]
+    for f in (L.pf_domain_size, L.pf_extended_size, L.pf_noise_entries, L.pf_local_domain_size):
         f.argtypes = [vp]
         f.restype = sz
     L.pf_compute_eigenvalues.argtypes = [vp, C.POINTER(PfEigStats)]
@@ -232,6 +239,8 @@ def make_desc(
     max_factor=0,
     device=-1,
     cov_param=(0.0, 0.0),
+    n_ranks=1,
+    rank=0,
 ):
     d = PfDesc()
     lib().pf_desc_default(C.byref(d))
@@ -264,7 +273,32 @@ def make_desc(
     d.census_quirk = int(census_quirk)
     d.max_factor = max_factor
     d.device = device
+    d.n_ranks = int(n_ranks)
+    d.rank = int(rank)
     return d
+
+
+def slab_layout(cells, factor, n_ranks, rank):
+    """Host-side statement of the slab decomposition the plan uses (pf_api.cu
+    plan_resize; replaces fftw_mpi_local_size of fieldtraits.hh:271-282):
+    which lines of the first inverse pass this rank computes and which layers
+    of the last dimension it owns afterwards."""
+    cells = list(cells)
+    dim = len(cells)
+    if dim < 2:
+        raise ValueError("slab mode needs dim >= 2")
+    if cells[-1] % n_ranks:
+        raise ValueError("number of cells in last dimension has to be multiple of numProc")
+    n = [factor * c for c in cells]
+    m0 = n[0] // 2 + 1
+    A = n[1] if dim == 3 else m0  # pass A lines: k1 (3D) or k0 (2D)
+    N = n[2] if dim == 3 else n[1]  # pass A line length
+    lpc = min(128, 4096 // N)  # lines per tile of the pass kernels
+    chunk = -(-A // n_ranks)
+    chunk = -(-chunk // lpc) * lpc
+    b0, b1 = min(A, chunk * rank), min(A, chunk * (rank + 1))
+    layers = cells[-1] // n_ranks
+    return dict(a_begin=b0, a_count=b1 - b0, layers=layers, layer_begin=rank * layers, lines=A, line_length=N)
 
 
 class Plan:
@@ -330,8 +364,37 @@ class Plan:
         return int(lib().pf_noise_entries(self._h))
 
     @property
+    def local_domain_size(self):
+        return int(lib().pf_local_domain_size(self._h))
+
+    @property
     def shape(self):
-        return tuple(reversed(self.cells))
+        """shape of what this plan's generate() returns: the whole field, or
+        this rank's slab (last dimension split) in slab mode"""
+        sh = list(reversed(self.cells))
+        if self.desc.n_ranks > 1:
+            sh[0] //= self.desc.n_ranks
+        return tuple(sh)
+
+    # -- slab mode (one process per GPU) ---------------------------------------
+    def slab_handle(self):
+        buf = C.create_string_buffer(64)
+        _check(lib().pf_slab_handle(self._h, buf))
+        return buf.raw
+
+    def slab_connect(self, handles):
+        """handles: list of the 64-byte handles of all ranks, in rank order"""
+        blob = b"".join(handles)
+        _check(lib().pf_slab_connect(self._h, blob, len(handles)))
+
+    def connect(self, group=None):
+        """exchange the IPC handles through torch.distributed and map the peers"""
+        import torch.distributed as dist
+
+        handles = [None] * dist.get_world_size(group)
+        dist.all_gather_object(handles, self.slab_handle(), group=group)
+        self.slab_connect(handles)
+        dist.barrier(group)
 
     # -- eigenvalues ---------------------------------------------------------
     def compute_eigenvalues(self):

@@ -351,7 +351,8 @@ k_reduce2(int nb, const double* __restrict__ partial, int mode,
 
 // iid N(0,1) per cell, device Philox (Matrix::generateUncorrelatedField)
 __global__ void
-k_uncorrelated(size_t n, unsigned long long seed, double* __restrict__ out);
+k_uncorrelated(size_t n, unsigned long long seed, unsigned long long q0,
+               double* __restrict__ out);
 
 } // namespace
 
@@ -360,14 +361,15 @@ k_uncorrelated(size_t n, unsigned long long seed, double* __restrict__ out);
 namespace {
 
 __global__ void
-k_uncorrelated(size_t n, unsigned long long seed, double* __restrict__ out)
+k_uncorrelated(size_t n, unsigned long long seed, unsigned long long q0,
+               double* __restrict__ out)
 {
   // one Philox call -> two (r1,r2) pairs -> four cells
   const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t i = 4 * q;
   if (i >= n)
     return;
-  const uint4 w = pf::philox4x32_10(q, 0xFFFFFFFFFFFFFFFFull, seed);
+  const uint4 w = pf::philox4x32_10(q0 + q, 0xFFFFFFFFFFFFFFFFull, seed);
   const double2 a = pf::box_muller_f64(w.x, w.y);
   const double2 b = pf::box_muller_f64(w.z, w.w);
   out[i] = a.x;
@@ -377,6 +379,40 @@ k_uncorrelated(size_t n, unsigned long long seed, double* __restrict__ out)
     out[i + 2] = b.x;
   if (i + 3 < n)
     out[i + 3] = b.y;
+}
+
+// ---- slab mode: flags in peer memory ---------------------------------------
+// thread i publishes `epoch` in slot `me` of rank i's flag array
+__global__ void
+k_slab_signal(unsigned long long* const* flags, int n, int me,
+              unsigned long long epoch)
+{
+  const int i = threadIdx.x;
+  if (i < n) {
+    __threadfence_system();
+    volatile unsigned long long* f = flags[i] + me;
+    *f = epoch;
+    __threadfence_system();
+  }
+}
+// thread i waits until rank i has published at least `epoch` here; bounded
+// spin (about 4 s) so that a lost peer cannot hang the device
+__global__ void
+k_slab_wait(const unsigned long long* mine, int n, unsigned long long epoch,
+            int* timeout_flag)
+{
+  const int i = threadIdx.x;
+  if (i < n) {
+    const volatile unsigned long long* f = mine + i;
+    const long long t0 = clock64();
+    while (*f < epoch) {
+      if (clock64() - t0 > 8000000000ll) {
+        *timeout_flag = 1;
+        break;
+      }
+    }
+    __threadfence_system();
+  }
 }
 
 inline unsigned
@@ -433,6 +469,19 @@ struct pf_plan
   pf::CovParams cov{};
   int device = 0;
   int sm_count = 148;
+  // ---- slab mode (one process per GPU) -------------------------------------
+  int nranks = 1, rank = 0;
+  long long cl = 1;          // local layers of the last dimension
+  size_t Dl = 1;             // cells of the local slab
+  int a_begin = 0, a_count = 0; // pass A lines owned by this rank
+  size_t xbuf_elems = 0;     // complex elements of one exchange buffer
+  unsigned char* slab_block = nullptr; // [2 exchange buffers][flags]
+  void* peer_block[8] = { nullptr };
+  unsigned long long** d_flagsA = nullptr; // device arrays of peer pointers
+  unsigned long long** d_flagsB = nullptr;
+  int* d_timeout = nullptr;
+  bool connected = false;
+  unsigned long long epoch = 0;
   // bit mask of pass kinds routed to the persistent TMA kernels (N >= 256);
   // PF_PIPE=0 in the environment selects the plain kernels everywhere
   // (pass A stays on the plain kernel: it is issue-bound and the plain
@@ -580,6 +629,34 @@ plan_resize(pf_plan* pl)
       m[0] = 1. / copy[0];
     }
   }
+  // slab decomposition (fieldtraits.hh:217-224,271-282: the last dimension
+  // is split evenly over the ranks)
+  pl->cl = pl->c[pl->dim - 1];
+  pl->Dl = pl->D;
+  pl->a_begin = 0;
+  pl->a_count = 0;
+  if (pl->nranks > 1) {
+    const int P = pl->nranks;
+    if (pl->dim < 2)
+      return fail(PF_ERR_INVALID, "slab mode needs dim >= 2");
+    if (pl->c[pl->dim - 1] % P != 0)
+      return fail(PF_ERR_INVALID, "number of cells in last dimension has to be "
+                                  "multiple of numProc"); // fieldtraits.hh:219
+    pl->cl = pl->c[pl->dim - 1] / P;
+    pl->Dl = pl->D / P;
+    // pass A lines (3D: k1, 2D: k0) in chunks aligned to the tile width
+    const long long A = pl->dim == 3 ? pl->n[1] : pl->m0;
+    const long long N = pl->dim == 3 ? pl->n[2] : pl->n[1];
+    const long long lpc = std::min<long long>(128, 4096 / N);
+    long long chunk = (A + P - 1) / P;
+    chunk = (chunk + lpc - 1) / lpc * lpc;
+    const long long b0 = std::min<long long>(A, chunk * pl->rank);
+    const long long b1 = std::min<long long>(A, chunk * (pl->rank + 1));
+    pl->a_begin = (int)b0;
+    pl->a_count = (int)(b1 - b0);
+    pl->xbuf_elems = pl->dim == 3 ? (size_t)pl->m0 * pl->cl * pl->n[1]
+                                  : (size_t)pl->cl * pl->m0p;
+  }
   return 0;
 }
 
@@ -654,6 +731,8 @@ use_pipe(const pf_plan* pl, long long N, int kind, const PassArgs& a)
     return false;
   if (kind == pf::K_C2R)
     return a.B == 1 && (a.isa * 16) % 16 == 0;
+  if (kind == pf::K_GEN_TILE && (a.n_peers > 1 || a.a_begin != 0))
+    return false;
   // tile kernels: plain scale, 16-byte aligned lines, whole-line bulk copies
   if (a.scale != 1.0)
     return false;
@@ -936,18 +1015,21 @@ set_table(const pf_plan* pl, PassArgs& a, const double* tab)
   }
 }
 
-// inverse passes B and C (3D) / C (2D) from Y / Z into a device field
+// inverse passes B and C (3D) / C (2D) from Y / Z into a device field;
+// `layers` = extent of the last physical dimension held here (all of it, or
+// this rank's slab)
 int
-inverse_tail(pf_plan* pl, double* out_dev, int transform)
+inverse_tail(pf_plan* pl, const cplx* Yin, long long layers, double* out_dev,
+             int transform)
 {
   const long long* n = pl->n;
   const long long* c = pl->c;
   if (pl->dim == 3) {
     PassArgs b = blank_args(); // pass B: k1 lines, (a,b) = (k0, x2)
     b.A = (int)pl->m0;
-    b.B = (int)c[2];
-    b.in = pl->Y;
-    b.isa = c[2] * n[1];
+    b.B = (int)layers;
+    b.in = Yin;
+    b.isa = layers * n[1];
     b.isb = n[1];
     b.n_valid = (int)n[1];
     b.out = pl->Z; // Z[x2][x1][k0]
@@ -957,9 +1039,9 @@ inverse_tail(pf_plan* pl, double* out_dev, int transform)
     PF_TRY(run_pass(pl, n[1], pf::K_C2T_INV, b));
   }
   PassArgs cc = blank_args(); // pass C
-  cc.A = (int)(pl->dim == 3 ? c[1] * c[2] : c[1]);
+  cc.A = (int)(pl->dim == 3 ? c[1] * layers : layers);
   cc.B = 1;
-  cc.in = pl->Z;
+  cc.in = pl->dim == 3 ? pl->Z : Yin;
   cc.isa = pl->m0p;
   cc.out = out_dev;
   cc.out_pitch = c[0];
@@ -970,12 +1052,20 @@ inverse_tail(pf_plan* pl, double* out_dev, int transform)
   return 0;
 }
 
+int
+generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
+                  unsigned long long realization, const double2* noise_dev,
+                  double* out_dev, int transform);
+
 // Matrix::generateField (matrix.hh:343-438) into device memory
 int
 generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
              unsigned long long realization, const double2* noise_dev,
              double* out_dev, double* spare_dev, int transform)
 {
+  if (pl->nranks > 1)
+    return generate_slab_dev(pl, noise_kind, seed, realization, noise_dev,
+                             out_dev, transform);
   PF_TRY(ensure_table(pl, &pl->sig_gen, pl->hermitian ? 0 : 1));
   PF_TRY(ensure_work(pl));
   const long long* n = pl->n;
@@ -1006,7 +1096,7 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.ose = n[1];
     a.keep = (int)c[2];
     PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
-    PF_TRY(inverse_tail(pl, out_dev, transform));
+    PF_TRY(inverse_tail(pl, pl->Y, c[2], out_dev, transform));
   } else if (pl->dim == 2) {
     a.A = (int)m0; // a = k0, e = k1
     a.B = 1;
@@ -1024,7 +1114,7 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.ose = pl->m0p;
     a.keep = (int)c[1];
     PF_TRY(run_pass(pl, n[1], pf::K_GEN_TILE, a));
-    PF_TRY(inverse_tail(pl, out_dev, transform));
+    PF_TRY(inverse_tail(pl, pl->Z, c[1], out_dev, transform));
   } else {
     a.A = 1;
     a.B = 1;
@@ -1038,6 +1128,114 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.tparam = pl->d.boxcox_lambda;
     PF_TRY(run_pass(pl, n[0], pf::K_GEN_REIM, a));
   }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// slab mode: generateField over the GPUs of one node.  Rank r runs pass A for
+// its share of the (a) lines and stores every transposed tile row directly
+// into the memory of the rank that owns that layer of the last dimension
+// (peer stores over NVLink); flags in peer memory order the passes.  After
+// the exchange the layout is the reference's field distribution
+// (fieldtraits.hh:281-282), so passes B and C are local.
+// ---------------------------------------------------------------------------
+cplx*
+slab_buffer(const pf_plan* pl, void* block, int which)
+{
+  return reinterpret_cast<cplx*>(static_cast<unsigned char*>(block)) +
+         (size_t)which * pl->xbuf_elems;
+}
+unsigned long long*
+slab_flags(const pf_plan* pl, void* block, int which)
+{
+  return reinterpret_cast<unsigned long long*>(
+           static_cast<unsigned char*>(block) +
+           2 * pl->xbuf_elems * sizeof(cplx)) +
+         8 * which;
+}
+
+int
+generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
+                  unsigned long long realization, const double2* noise_dev,
+                  double* out_dev, int transform)
+{
+  if (!pl->connected)
+    return fail(PF_ERR_INVALID,
+                "slab mode: call pf_slab_connect on every rank first");
+  PF_TRY(ensure_table(pl, &pl->sig_gen, 0));
+  if (pl->dim == 3)
+    PF_TRY(dev_alloc(&pl->Z, (size_t)pl->cl * pl->c[1] * pl->m0p));
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  const int P = pl->nranks;
+  const unsigned long long e = ++pl->epoch;
+  const int s = (int)(e & 1);
+  // peers must have consumed what we wrote into this buffer two calls ago
+  if (e > 2) {
+    k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
+                                          e - 2, pl->d_timeout);
+    pl->launches++;
+  }
+  PassArgs a = blank_args();
+  set_table(pl, a, pl->sig_gen);
+  a.noise_kind = noise_kind;
+  a.keys = pf::philox_keys(seed);
+  a.realization = realization;
+  a.noise = noise_dev;
+  a.hermitian = 1;
+  a.corrected = pl->d.parity_mode == 1;
+  a.a_begin = pl->a_begin;
+  a.A = pl->a_count;
+  a.n_peers = P;
+  a.rows_per_peer = (int)pl->cl;
+  for (int q = 0; q < P; q++)
+    a.peer_out[q] = slab_buffer(pl, pl->peer_block[q], s);
+  a.out = a.peer_out[pl->rank];
+  if (pl->dim == 3) {
+    a.B = (int)m0; // a = k1 (split over ranks), b = k0, e = k2
+    a.cma = m0 * (n[2] / 2);
+    a.cmb = 1;
+    a.cme = m0;
+    a.ima = m0 * n[2];
+    a.imb = 1;
+    a.ime = m0;
+    a.na_self = (int)n[1];
+    a.nb_self = (int)n[0];
+    a.plane_axis = 1;
+    a.osb = pl->cl * n[1]; // Y_q[k0][x2 local][k1]
+    a.ose = n[1];
+    a.keep = (int)c[2];
+    if (a.A > 0)
+      PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
+  } else {
+    a.B = 1; // a = k0 (split over ranks), e = k1
+    a.cma = 1;
+    a.cmb = 0;
+    a.cme = m0;
+    a.ima = 1;
+    a.imb = 0;
+    a.ime = m0;
+    a.na_self = (int)n[0];
+    a.nb_self = 1;
+    a.plane_axis = 0;
+    a.osb = 0; // Z_q[x1 local][k0]
+    a.ose = pl->m0p;
+    a.keep = (int)c[1];
+    if (a.A > 0)
+      PF_TRY(run_pass(pl, n[1], pf::K_GEN_TILE, a));
+  }
+  // publish "pass A of call e done" to every rank, then wait for all ranks
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e);
+  k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e,
+                                        pl->d_timeout);
+  pl->launches += 2;
+  PF_TRY(inverse_tail(pl, slab_buffer(pl, pl->slab_block, s), pl->cl, out_dev,
+                      transform));
+  // publish "buffer s consumed"
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsB, P, pl->rank, e);
+  pl->launches++;
+  PF_CUDA(cudaGetLastError());
   return 0;
 }
 
@@ -1100,7 +1298,7 @@ apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
     s.ose = n[1];
     s.keep = (int)c[2];
     PF_TRY(run_pass(pl, n[2], pf::K_SPEC_TILE, s));
-    PF_TRY(inverse_tail(pl, out_dev, 0));
+    PF_TRY(inverse_tail(pl, pl->Y, c[2], out_dev, 0));
   } else if (pl->dim == 2) {
     PF_TRY(dev_alloc(&pl->V, (size_t)m0 * c[1]));
     PassArgs f0 = blank_args(); // F0: x0 lines, a = x1
@@ -1127,7 +1325,7 @@ apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
     s.ose = pl->m0p;
     s.keep = (int)c[1];
     PF_TRY(run_pass(pl, n[1], pf::K_SPEC_TILE, s));
-    PF_TRY(inverse_tail(pl, out_dev, 0));
+    PF_TRY(inverse_tail(pl, pl->Z, c[1], out_dev, 0));
   } else {
     PassArgs s = blank_args();
     set_table(pl, s, tab);
@@ -1316,6 +1514,16 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
                          pl->device);
   if (const char* env = getenv("PF_PIPE"))
     pl->pipe_mask = (unsigned)strtoul(env, nullptr, 0);
+  pl->nranks = desc->n_ranks > 1 ? desc->n_ranks : 1;
+  pl->rank = pl->nranks > 1 ? desc->rank : 0;
+  if (pl->nranks > 8 || pl->rank < 0 || pl->rank >= pl->nranks) {
+    delete pl;
+    return fail(PF_ERR_INVALID, "slab mode supports 1..8 ranks, 0 <= rank < n_ranks");
+  }
+  if (pl->nranks > 1 && desc->max_factor) {
+    delete pl;
+    return fail(PF_ERR_INVALID, "the embedding-factor retry is not available in slab mode");
+  }
   pl->factor = desc->embedding_factor ? desc->embedding_factor : 2;
   if (desc->periodic)
     pl->factor = 1; // fieldtraits.hh:196-202
@@ -1323,6 +1531,25 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
   if (rc != 0) {
     delete pl;
     return rc;
+  }
+  if (pl->nranks > 1) {
+    // exchange block: two buffers + flag arrays, one cudaMalloc so that one
+    // IPC handle describes it
+    const size_t bytes = 2 * pl->xbuf_elems * sizeof(cplx) + 256;
+    void* blk = nullptr;
+    if (cudaMalloc(&blk, bytes) != cudaSuccess ||
+        cudaMemset(blk, 0, bytes) != cudaSuccess ||
+        cudaMalloc((void**)&pl->d_flagsA, 8 * sizeof(void*)) != cudaSuccess ||
+        cudaMalloc((void**)&pl->d_flagsB, 8 * sizeof(void*)) != cudaSuccess ||
+        cudaMalloc((void**)&pl->d_timeout, sizeof(int)) != cudaSuccess ||
+        cudaMemset(pl->d_timeout, 0, sizeof(int)) != cudaSuccess) {
+      cudaGetLastError();
+      delete pl;
+      return fail(PF_ERR_NOMEM, "slab mode: allocating the exchange block failed");
+    }
+    pl->slab_block = static_cast<unsigned char*>(blk);
+    pl->peer_block[pl->rank] = blk;
+    cudaDeviceSynchronize();
   }
   cudaStreamCreateWithFlags(&pl->copy_stream, cudaStreamNonBlocking);
   for (int i = 0; i < 2; i++) {
@@ -1351,6 +1578,17 @@ pf_plan_destroy(pf_plan* pl)
     dev_free(&pl->cg[i]);
   dev_free(&pl->red_partial);
   dev_free(&pl->census);
+  for (int q = 0; q < pl->nranks; q++)
+    if (q != pl->rank && pl->peer_block[q])
+      cudaIpcCloseMemHandle(pl->peer_block[q]);
+  if (pl->slab_block)
+    cudaFree(pl->slab_block);
+  if (pl->d_flagsA)
+    cudaFree(pl->d_flagsA);
+  if (pl->d_flagsB)
+    cudaFree(pl->d_flagsB);
+  if (pl->d_timeout)
+    cudaFree(pl->d_timeout);
   if (pl->copy_stream)
     cudaStreamDestroy(pl->copy_stream);
   for (int i = 0; i < 2; i++) {
@@ -1376,6 +1614,12 @@ pf_plan_synchronize(pf_plan* pl)
 {
   PF_TRY(check_plan(pl));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
+  if (pl->d_timeout) {
+    int t = 0;
+    PF_CUDA(cudaMemcpy(&t, pl->d_timeout, sizeof(int), cudaMemcpyDeviceToHost));
+    if (t)
+      return fail(PF_ERR_CUDA, "slab mode: timed out waiting for a peer rank");
+  }
   return 0;
 }
 
@@ -1417,6 +1661,54 @@ pf_domain_size(const pf_plan* pl)
 {
   return pl ? pl->D : 0;
 }
+size_t
+pf_local_domain_size(const pf_plan* pl)
+{
+  return pl ? pl->Dl : 0;
+}
+
+int
+pf_slab_handle(pf_plan* pl, void* handle_out)
+{
+  PF_TRY(check_plan(pl));
+  static_assert(sizeof(cudaIpcMemHandle_t) == PF_SLAB_HANDLE_BYTES,
+                "IPC handle size");
+  if (pl->nranks <= 1 || !handle_out)
+    return fail(PF_ERR_INVALID, "pf_slab_handle: plan is not in slab mode");
+  cudaIpcMemHandle_t h;
+  PF_CUDA(cudaIpcGetMemHandle(&h, pl->slab_block));
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+
+int
+pf_slab_connect(pf_plan* pl, const void* handles, int count)
+{
+  PF_TRY(check_plan(pl));
+  if (pl->nranks <= 1 || count != pl->nranks || !handles)
+    return fail(PF_ERR_INVALID, "pf_slab_connect: need one handle per rank");
+  const unsigned char* hb = static_cast<const unsigned char*>(handles);
+  for (int q = 0; q < pl->nranks; q++) {
+    if (q == pl->rank || pl->peer_block[q])
+      continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, hb + (size_t)q * PF_SLAB_HANDLE_BYTES, sizeof(h));
+    void* ptr = nullptr;
+    PF_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    pl->peer_block[q] = ptr;
+  }
+  unsigned long long* fa[8] = { nullptr };
+  unsigned long long* fb[8] = { nullptr };
+  for (int q = 0; q < pl->nranks; q++) {
+    fa[q] = slab_flags(pl, pl->peer_block[q], 0);
+    fb[q] = slab_flags(pl, pl->peer_block[q], 1);
+  }
+  PF_CUDA(cudaMemcpy(pl->d_flagsA, fa, sizeof(fa), cudaMemcpyHostToDevice));
+  PF_CUDA(cudaMemcpy(pl->d_flagsB, fb, sizeof(fb), cudaMemcpyHostToDevice));
+  pl->connected = true;
+  return 0;
+}
+
 size_t
 pf_extended_size(const pf_plan* pl)
 {
@@ -1517,18 +1809,18 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
   const bool dev = is_device_ptr(out);
   if (pl->dim == 1) {
     // DFT backend: one transform yields two fields (matrix.hh:428-437)
-    PF_TRY(dev_alloc(&pl->spare, pl->D));
-    PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+    PF_TRY(dev_alloc(&pl->spare, pl->Dl));
+    PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
     for (size_t r = 0; r < count; r++) {
-      double* o = out + r * pl->D;
+      double* o = out + r * pl->Dl;
       double* dst = dev ? o : pl->dev_io[0];
       if (pl->spare_valid) {
         if (tr) {
-          k_transform<<<grid_for(pl->D), 256, 0, pl->stream>>>(
-            pl->D, pl->spare, dst, tr, pl->d.boxcox_lambda);
+          k_transform<<<grid_for(pl->Dl), 256, 0, pl->stream>>>(
+            pl->Dl, pl->spare, dst, tr, pl->d.boxcox_lambda);
           pl->launches++;
         } else
-          PF_CUDA(cudaMemcpyAsync(dst, pl->spare, pl->D * sizeof(double),
+          PF_CUDA(cudaMemcpyAsync(dst, pl->spare, pl->Dl * sizeof(double),
                                   cudaMemcpyDeviceToDevice, pl->stream));
         pl->spare_valid = false;
       } else {
@@ -1536,7 +1828,7 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
         pl->spare_valid = true;
       }
       if (!dev) {
-        PF_CUDA(cudaMemcpyAsync(o, dst, pl->D * sizeof(double),
+        PF_CUDA(cudaMemcpyAsync(o, dst, pl->Dl * sizeof(double),
                                 cudaMemcpyDeviceToHost, pl->stream));
         PF_CUDA(cudaStreamSynchronize(pl->stream));
       }
@@ -1545,16 +1837,16 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
   }
   if (dev) {
     for (size_t r = 0; r < count; r++)
-      PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->D,
+      PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->Dl,
                           nullptr, tr));
     return 0;
   }
   // host output: double-buffered so that the D2H copy of realization r
   // overlaps the kernels of realization r+1 (needs pinned host memory to
   // overlap; pageable memory still works, serialised by the runtime)
-  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
   if (count > 1)
-    PF_TRY(dev_alloc(&pl->dev_io[1], pl->D));
+    PF_TRY(dev_alloc(&pl->dev_io[1], pl->Dl));
   for (size_t r = 0; r < count; r++) {
     const int s = (int)(r & 1);
     if (r >= 2)
@@ -1562,8 +1854,8 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
     PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, pl->dev_io[s], nullptr, tr));
     PF_CUDA(cudaEventRecord(pl->ev_done[s], pl->stream));
     PF_CUDA(cudaStreamWaitEvent(pl->copy_stream, pl->ev_done[s], 0));
-    PF_CUDA(cudaMemcpyAsync(out + r * pl->D, pl->dev_io[s],
-                            pl->D * sizeof(double), cudaMemcpyDeviceToHost,
+    PF_CUDA(cudaMemcpyAsync(out + r * pl->Dl, pl->dev_io[s],
+                            pl->Dl * sizeof(double), cudaMemcpyDeviceToHost,
                             pl->copy_stream));
     PF_CUDA(cudaEventRecord(pl->ev_copied[s], pl->copy_stream));
   }
@@ -1591,20 +1883,20 @@ pf_generate_from_noise(pf_plan* pl, const double* noise, double* out,
   PF_TRY(stage_in(pl, noise, 2 * ne, sn));
   const bool dev = is_device_ptr(out);
   const bool sdev = is_device_ptr(spare);
-  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
   double* dst = dev ? out : pl->dev_io[0];
   double* sp = nullptr;
   if (pl->dim == 1) {
-    PF_TRY(dev_alloc(&pl->spare, pl->D));
+    PF_TRY(dev_alloc(&pl->spare, pl->Dl));
     sp = (spare && sdev) ? spare : pl->spare;
   }
   PF_TRY(generate_dev(pl, pf::NOISE_INJECTED, 0, 0,
                       reinterpret_cast<const double2*>(sn.dev), dst, sp, 0));
   if (!dev)
-    PF_CUDA(cudaMemcpyAsync(out, dst, pl->D * sizeof(double),
+    PF_CUDA(cudaMemcpyAsync(out, dst, pl->Dl * sizeof(double),
                             cudaMemcpyDeviceToHost, pl->stream));
   if (spare && !sdev && pl->dim == 1)
-    PF_CUDA(cudaMemcpyAsync(spare, sp, pl->D * sizeof(double),
+    PF_CUDA(cudaMemcpyAsync(spare, sp, pl->Dl * sizeof(double),
                             cudaMemcpyDeviceToHost, pl->stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
   return 0;
@@ -1615,14 +1907,16 @@ pf_generate_uncorrelated(pf_plan* pl, uint64_t seed, double* out)
 {
   PF_TRY(check_plan(pl));
   const bool dev = is_device_ptr(out);
-  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
   double* dst = dev ? out : pl->dev_io[0];
-  const size_t q = (pl->D + 3) / 4;
-  k_uncorrelated<<<(unsigned)((q + 255) / 256), 256, 0, pl->stream>>>(pl->D, seed, dst);
+  const size_t q = (pl->Dl + 3) / 4;
+  // slab mode: the Philox counter is the global cell-quad index
+  k_uncorrelated<<<(unsigned)((q + 255) / 256), 256, 0, pl->stream>>>(
+    pl->Dl, seed, (unsigned long long)pl->rank * q, dst);
   PF_CUDA(cudaGetLastError());
   pl->launches++;
   if (!dev) {
-    PF_CUDA(cudaMemcpyAsync(out, dst, pl->D * sizeof(double),
+    PF_CUDA(cudaMemcpyAsync(out, dst, pl->Dl * sizeof(double),
                             cudaMemcpyDeviceToHost, pl->stream));
     PF_CUDA(cudaStreamSynchronize(pl->stream));
   }
@@ -1634,11 +1928,11 @@ pf_set_variance_as_field(pf_plan* pl, double* out)
 {
   PF_TRY(check_plan(pl));
   if (is_device_ptr(out)) {
-    k_fill<<<grid_for(pl->D), 256, 0, pl->stream>>>(pl->D, pl->d.variance, out);
+    k_fill<<<grid_for(pl->Dl), 256, 0, pl->stream>>>(pl->Dl, pl->d.variance, out);
     PF_CUDA(cudaGetLastError());
     pl->launches++;
   } else {
-    for (size_t i = 0; i < pl->D; i++)
+    for (size_t i = 0; i < pl->Dl; i++)
       out[i] = pl->d.variance;
   }
   return 0;
@@ -1650,6 +1944,9 @@ pf_apply(pf_plan* pl, int op, const double* in, double* out)
   PF_TRY(check_plan(pl));
   if (op < 0 || op > 2 || !in || !out)
     return fail(PF_ERR_INVALID, "bad argument");
+  if (pl->nranks > 1)
+    return fail(PF_ERR_INVALID, "pf_apply is not available in slab mode yet "
+                                "(single-GPU plans only)");
   Staged si;
   PF_TRY(stage_in(pl, in, pl->D, si));
   const bool dev = is_device_ptr(out);
@@ -1671,6 +1968,9 @@ pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
   PF_TRY(check_plan(pl));
   if (!in || !out)
     return fail(PF_ERR_INVALID, "null argument");
+  if (pl->nranks > 1)
+    return fail(PF_ERR_INVALID, "pf_solve is not available in slab mode yet "
+                                "(single-GPU plans only)");
   const size_t D = pl->D;
   Staged si;
   PF_TRY(stage_in(pl, in, D, si));

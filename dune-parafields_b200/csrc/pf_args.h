@@ -69,6 +69,10 @@ struct PassArgs
 {
   // ---- line space: lines (a, b), a in [0,A) is the tile axis -------------
   int A, B;
+  // slab mode (pass A only): this rank owns the global lines
+  // a_begin .. a_begin + A - 1; noise counters, table rows and output columns
+  // use the global index
+  int a_begin;
 
   // ---- input --------------------------------------------------------------
   const void* in;       // complex or real lines
@@ -80,6 +84,12 @@ struct PassArgs
   long long osb, ose;
   int keep;
   double scale;
+
+  // slab mode (pass A only): row e of the tile belongs to rank e /
+  // rows_per_peer and is stored into that rank's buffer (peer memory mapped
+  // through CUDA IPC) at local row e % rows_per_peer; n_peers <= 1: off
+  int n_peers, rows_per_peer;
+  void* peer_out[8];
 
   // ---- contiguous line stores (re/im, lambda): line*pitch + e ------------
   void* out2;           // second line set (imag part / spare field)

@@ -356,6 +356,36 @@ tile_base(const PassArgs& p, int b, int first_line)
 // kernels
 // ===========================================================================
 
+// tile store of pass A in slab mode: rows are scattered to the ranks that own
+// them (the FFTW-MPI transpose of the reference, fused into the producing
+// pass as stores to peer memory over NVLink)
+template <int N>
+__device__ __forceinline__ void
+tile_store_peers(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t,
+                 const PassArgs& p, long long base_off, int lines_valid)
+{
+  using K = KCfg<N>;
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    if (e < p.keep)
+      stage[stage_slot<N>(e, lic)] =
+        make_double2(v[q].x * p.scale, v[q].y * p.scale);
+  }
+  __syncthreads();
+  const int total = p.keep * K::LPC;
+  for (int idx = threadIdx.x; idx < total; idx += PF_THREADS) {
+    const int l = idx % K::LPC, e = idx / K::LPC;
+    if (l < lines_valid) {
+      const int owner = e / p.rows_per_peer;
+      const int el = e - owner * p.rows_per_peer;
+      cplx* o = reinterpret_cast<cplx*>(p.peer_out[owner]);
+      o[base_off + (long long)el * p.ose + l] = stage[stage_slot<N>(e, l)];
+    }
+  }
+}
+
 // pass A: noise -> inverse FFT -> tile
 #ifndef PF_GEN_MINB
 #define PF_GEN_MINB 3
@@ -370,15 +400,19 @@ k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
   const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
   const int ntA = (p.A + K::LPC - 1) / K::LPC;
   const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
-  const int a = at * K::LPC + lic;
-  cplx* obase = tile_base(p, b, at * K::LPC);
+  const int al = at * K::LPC + lic; // local line, global line = a_begin + al
+  cplx* obase = tile_base(p, b, p.a_begin + at * K::LPC);
   long long ose = p.ose;
   asm volatile("" : "+l"(ose));
   cplx v[K::E];
-  load_noise<N, NOISE>(v, p, a, b, t, a < p.A);
+  load_noise<N, NOISE>(v, p, p.a_begin + al, b, t, al < p.A);
   line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
   const int lv = min(K::LPC, p.A - at * K::LPC);
-  tile_store<N>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
+  if (p.n_peers > 1)
+    tile_store_peers<N>(v, sm, lic, t, p,
+                        (long long)b * p.osb + p.a_begin + at * K::LPC, lv);
+  else
+    tile_store<N>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
 }
 
 // 1D: noise -> inverse FFT -> real part / imaginary part lines

@@ -121,6 +121,12 @@ typedef struct pf_desc
                                first half like the reference (Appendix C.3)   */
   unsigned max_factor;      /* embedding-factor retry bound, 0 = no retry     */
   int device;               /* CUDA device ordinal, -1 = current              */
+  /* slab decomposition over the GPUs of one node, one process per GPU
+     (replaces the FFTW-MPI slab layout of fieldtraits.hh:271-282): the field
+     is split over its last dimension, rank r owning cells[dim-1]/n_ranks
+     layers; 0 or 1 = single GPU */
+  int n_ranks;
+  int rank;
 } pf_desc;
 
 /* eigenvalue census, matrix.hh:283-320 */
@@ -163,6 +169,23 @@ int pf_plan_get_pass_times(pf_plan* plan, double* ms16,
 size_t pf_domain_size(const pf_plan* plan);
 size_t pf_extended_size(const pf_plan* plan);
 size_t pf_noise_entries(const pf_plan* plan);
+/* cells of this rank's slab (= pf_domain_size without slab decomposition),
+ * Traits::localDomainSize */
+size_t pf_local_domain_size(const pf_plan* plan);
+
+/* Slab mode wiring (one process per GPU).  Every rank exports PF_SLAB_HANDLE_BYTES
+ * bytes describing its exchange buffer (a CUDA IPC memory handle), the host
+ * program gathers the handles of all ranks in rank order (e.g. with
+ * torch.distributed / MPI allgather) and passes them to pf_slab_connect,
+ * which maps the peers' buffers.  After that pf_generate* scatters the
+ * transposed tiles of the first inverse pass straight into the owning
+ * rank's memory over NVLink (the FFTW-MPI transpose of
+ * r2cfieldbackend.hh:250-274 fused into the producing kernel) and
+ * synchronises the ranks with flags in peer memory; `out` receives the local
+ * slab.  All ranks must issue the same sequence of pf_generate* calls. */
+#define PF_SLAB_HANDLE_BYTES 64
+int pf_slab_handle(pf_plan* plan, void* handle_out);
+int pf_slab_connect(pf_plan* plan, const void* handles, int count);
 
 /* Matrix::fillTransformedMatrix, matrix.hh:232-331 (lazy in every other
  * entry point, like matrixBackend.valid()).  Returns
