@@ -229,6 +229,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="K3", choices=sorted(WORKLOADS))
     ap.add_argument("--rng", default="fast", choices=["fast", "fp64"])
+    ap.add_argument("--mode", default="auto", choices=["auto", "slab", "replicas"], help="N>1: slab = one realization sharded over the GPUs (BASELINE config, default), replicas = independent realizations per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -255,16 +256,26 @@ def main():
 
     pfb = importlib.import_module("dune-parafields_b200")
     wl = {k: v for k, v in WORKLOADS[args.workload].items() if k != "label"}
-    plan = pfb.Plan(device=local_rank, rng_mode=args.rng, **wl)
+    slab = distributed and args.mode in ("auto", "slab")
+    if slab:
+        plan = pfb.Plan(device=local_rank, rng_mode=args.rng, n_ranks=world, rank=rank, **wl)
+    else:
+        plan = pfb.Plan(device=local_rank, rng_mode=args.rng, **wl)
     stream = torch.cuda.Stream()
     plan.set_stream(stream)
+    if slab:
+        plan.connect()
 
     t0 = time.perf_counter()
     stats = plan.compute_eigenvalues()
     plan.synchronize()
     t_eig = time.perf_counter() - t0
 
-    D = plan.domain_size
+    D = plan.local_domain_size
+    # realization index of step s on this rank: slab mode = every rank works
+    # on the same realization; replicas = disjoint indices
+    ridx = (lambda s: s) if slab else (lambda s: rank + world * s)
+    per_step = 1 if slab else world  # realizations finished per step, whole job
     apply_tr = wl.get("transform", "none") != "none"
     field = torch.empty(D, dtype=torch.float64, device="cuda")
     seed = 20240611
@@ -277,7 +288,7 @@ def main():
 
     # ---- warm-up -----------------------------------------------------------
     for s in range(W):
-        plan.generate(seed, rank + world * s, out=field, apply_transform=apply_tr)
+        plan.generate(seed, ridx(s), out=field, apply_transform=apply_tr)
     plan.synchronize()
 
     # ---- timed region: K realizations per rank, fields resident in HBM -----
@@ -288,9 +299,17 @@ def main():
     l0 = plan.launch_count
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if slab:
+        # one batch call: the plan pipelines pass A of realization r+1 with
+        # the exchange and tail of realization r
+        fields = torch.empty((K, D), dtype=torch.float64, device="cuda")
+        barrier()
     ev0.record(stream)
-    for s in range(K):
-        plan.generate(seed, rank + world * (W + s), out=field, apply_transform=apply_tr)
+    if slab:
+        plan.generate_batch(seed, W, K, out=fields, apply_transform=apply_tr)
+    else:
+        for s in range(K):
+            plan.generate(seed, ridx(W + s), out=field, apply_transform=apply_tr)
     ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -302,7 +321,7 @@ def main():
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    value = world * K / (ms * 1e-3)
+    value = per_step * K / (ms * 1e-3)
 
     # ---- e2e: host (pinned) output, D2H copy inside the timed region -------
     e2e = None
@@ -312,7 +331,7 @@ def main():
         plan.generate_batch(seed, 0, 2, out=host[:2], apply_transform=apply_tr)  # warm-up
         barrier()
         t0 = time.perf_counter()
-        plan.generate_batch(seed, rank * Ke, Ke, out=host, apply_transform=apply_tr)
+        plan.generate_batch(seed, 0 if slab else rank * Ke, Ke, out=host, apply_transform=apply_tr)
         torch.cuda.synchronize()
         te = time.perf_counter() - t0
         if distributed:
@@ -320,7 +339,7 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             te = float(t.item())
         e2e = dict(
-            value=world * Ke / te,
+            value=per_step * Ke / te,
             unit="realizations/s",
             h2d_bytes_per_step=16,
             d2h_bytes_per_step=8 * D,
@@ -337,8 +356,17 @@ def main():
         shares = {names[k]: v for k, v in times.items() if k in names}
         dom = max(shares, key=lambda k: shares[k][0]) if shares else "pass_a"
         dom_ms = shares[dom][0] / max(shares[dom][1], 1) if shares else float("nan")
-        achieved = ab[dom] / (dom_ms * 1e-3) / 1e9
+        share = world if slab else 1  # slab mode: every rank moves 1/P of the bytes
+        achieved = ab[dom] / share / (dom_ms * 1e-3) / 1e9
         peak = float(peaks["hbm_gbs"])
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if world == 1:
+                traffic = tr.get(args.workload, {}).get(dom)
+        except Exception:
+            pass
+        step_s = ms / K * 1e-3
         roofline = dict(
             bound="hbm",
             kernel=dom,
@@ -346,17 +374,34 @@ def main():
             peak=peak,
             unit="GB/s",
             frac=achieved / peak,
-            traffic=None,
+            traffic=traffic,
+            traffic_source="profiles/traffic.json (ncu --set full capture of the same workload)" if traffic else None,
             peak_source=peak_kind + " copy bandwidth (MEASURED_PEAKS.json hbm_gbs)",
-            algorithmic_bytes_per_launch=ab[dom],
+            algorithmic_bytes_per_launch=ab[dom] // share,
             ms_per_launch=dom_ms,
             step=dict(
                 algorithmic_bytes=ab["total"],
-                achieved=ab["total"] / (ms / K * 1e-3) / 1e9,
-                frac=ab["total"] / (ms / K * 1e-3) / 1e9 / peak,
+                achieved=ab["total"] / step_s / 1e9,
+                frac=ab["total"] / step_s / 1e9 / (peak * world),
+                note="whole job: bytes of one realization / step time, against N x the measured HBM peak",
             ),
             passes_ms={k: v[0] / max(v[1], 1) for k, v in shares.items()},
         )
+        if slab:
+            lay = pfb.slab_layout(wl["cells"], 2, world, 0)
+            c = wl["cells"]
+            m0 = c[0] + 1
+            row = 16 * lay["a_count"] * (m0 if len(c) == 3 else 1)  # bytes per layer written by rank 0
+            sent = row * c[-1] * (world - 1) // world  # layers owned by other ranks
+            roofline["nvlink"] = dict(
+                sent_bytes_per_gpu_per_realization=sent,
+                achieved=sent / step_s / 1e9,
+                peak=770.0,
+                unit="GB/s",
+                frac=sent / step_s / 1e9 / 770.0,
+                peak_source="measured peer copy per direction per GPU (B200_PROFILING.md)",
+                note="pass A stores to peer memory overlap with its compute; passes B and C are local",
+            )
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             t_step, scale, cfg, t_eig_cpu = time_oracle(args.workload, 1, 1)
@@ -377,14 +422,18 @@ def main():
             warmup=W,
             ms_per_step=ms / K,
             higher_is_better=True,
-            scaling="weak",
+            scaling="strong" if slab else "weak",
             vs_baseline=None,
             dtype="f64",
             data="synthetic",
             config=dict(
                 workload=WORKLOADS[args.workload]["label"],
                 name=args.workload,
-                parallelism="replicas x%d (independent realizations, no collective)" % world,
+                parallelism=(
+                    "slab x%d: one realization sharded over the GPUs, pass A scatters tile rows to the layer owners by peer stores over NVLink (no NCCL on the data path)" % world
+                    if slab
+                    else "replicas x%d (independent realizations, no collective)" % world
+                ),
                 l2="per-step working set (>9 GB) exceeds the 126 MB L2",
                 rng=args.rng,
                 eigenvalue_setup_s=t_eig,

@@ -293,7 +293,7 @@ def slab_layout(cells, factor, n_ranks, rank):
     m0 = n[0] // 2 + 1
     A = n[1] if dim == 3 else m0  # pass A lines: k1 (3D) or k0 (2D)
     N = n[2] if dim == 3 else n[1]  # pass A line length
-    lpc = min(128, 4096 // N)  # lines per tile of the pass kernels
+    lpc = max(8, min(128, 4096 // N))  # lines per tile of the pass kernels
     chunk = -(-A // n_ranks)
     chunk = -(-chunk // lpc) * lpc
     b0, b1 = min(A, chunk * rank), min(A, chunk * (rank + 1))

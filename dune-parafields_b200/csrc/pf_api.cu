@@ -482,6 +482,14 @@ struct pf_plan
   int* d_timeout = nullptr;
   bool connected = false;
   unsigned long long epoch = 0;
+  // exchange by DMA (default): pass A writes the rows of other ranks into
+  // local staging buffers with the geometry of the peers' buffers, the copy
+  // engines move them over NVLink (contiguous row segments) while the next
+  // realization's pass A runs.  PF_SLAB_EXCHANGE=peer selects direct stores
+  // to peer memory from the kernel instead.
+  bool slab_dma = true;
+  cplx* send_stage[2] = { nullptr, nullptr }; // [(P-1) buffers] per parity
+  cudaEvent_t ev_a[2] = { nullptr, nullptr }, ev_x[2] = { nullptr, nullptr };
   // bit mask of pass kinds routed to the persistent TMA kernels (N >= 256);
   // PF_PIPE=0 in the environment selects the plain kernels everywhere
   // (pass A stays on the plain kernel: it is issue-bound and the plain
@@ -647,7 +655,7 @@ plan_resize(pf_plan* pl)
     // pass A lines (3D: k1, 2D: k0) in chunks aligned to the tile width
     const long long A = pl->dim == 3 ? pl->n[1] : pl->m0;
     const long long N = pl->dim == 3 ? pl->n[2] : pl->n[1];
-    const long long lpc = std::min<long long>(128, 4096 / N);
+    const long long lpc = std::max<long long>(8, std::min<long long>(128, 4096 / N));
     long long chunk = (A + P - 1) / P;
     chunk = (chunk + lpc - 1) / lpc * lpc;
     const long long b0 = std::min<long long>(A, chunk * pl->rank);
@@ -692,21 +700,22 @@ twiddles(pf_plan* pl, long long N, const cplx** out)
 // transposed-tile output of a pass as a 3D tensor map: dim0 = 2*A doubles
 // (the tile axis), dim1 = element row e < keep, dim2 = b
 int
-make_tile_map(const PassArgs& a, int boxr, CUtensorMap* tm)
+make_tile_map_at(void* base, long long cols, long long rows, long long planes,
+                 long long ose, long long osb, int boxr, CUtensorMap* tm)
 {
   encode_tiled_fn enc = get_encode_tiled();
   if (!enc)
     return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
-  const cuuint64_t gdim[3] = { (cuuint64_t)2 * a.A, (cuuint64_t)a.keep,
-                               (cuuint64_t)a.B };
-  const cuuint64_t row = (cuuint64_t)a.ose * 16;
+  const cuuint64_t gdim[3] = { (cuuint64_t)2 * cols, (cuuint64_t)rows,
+                               (cuuint64_t)planes };
+  const cuuint64_t row = (cuuint64_t)ose * 16;
   const cuuint64_t plane =
-    a.B > 1 ? (cuuint64_t)a.osb * 16 : row * (cuuint64_t)a.keep;
+    planes > 1 ? (cuuint64_t)osb * 16 : row * (cuuint64_t)rows;
   const cuuint64_t gstr[2] = { row, plane };
   const cuuint32_t box[3] = { 16, (cuuint32_t)boxr, 1 };
   const cuuint32_t estr[3] = { 1, 1, 1 };
   const CUresult r =
-    enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, a.out, gdim, gstr, box, estr,
+    enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, gdim, gstr, box, estr,
         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
@@ -714,6 +723,17 @@ make_tile_map(const PassArgs& a, int boxr, CUtensorMap* tm)
                                std::to_string((int)r));
   return 0;
 }
+
+int
+make_tile_map(const PassArgs& a, int boxr, CUtensorMap* tm)
+{
+  return make_tile_map_at(a.out, a.A, a.keep, a.B, a.ose, a.osb, boxr, tm);
+}
+
+struct TileMapsHost
+{
+  CUtensorMap m[8];
+};
 
 // rows per TMA box of the persistent tile kernels (PCfg<N>::BOXR)
 int
@@ -731,8 +751,12 @@ use_pipe(const pf_plan* pl, long long N, int kind, const PassArgs& a)
     return false;
   if (kind == pf::K_C2R)
     return a.B == 1 && (a.isa * 16) % 16 == 0;
-  if (kind == pf::K_GEN_TILE && (a.n_peers > 1 || a.a_begin != 0))
-    return false;
+  if (kind == pf::K_GEN_TILE && a.n_peers > 1) {
+    // slab mode: rows per rank must be a whole number of tensor-store boxes
+    const int rpp = a.rows_per_peer;
+    if (rpp < 8 || (rpp & (rpp - 1)) != 0 || a.a_begin % 8 != 0)
+      return false;
+  }
   // tile kernels: plain scale, 16-byte aligned lines, whole-line bulk copies
   if (a.scale != 1.0)
     return false;
@@ -749,8 +773,22 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     return fail(PF_ERR_INVALID, "no kernel for line length " + std::to_string(N));
   const cplx* tw = nullptr;
   PF_TRY(twiddles(pl, N, &tw));
-  const bool pipe = use_pipe(pl, N, kind, a);
+  // slab mode pass A always goes through the persistent kernel when it can:
+  // its tensor stores write 128-byte rows to peer memory
+  const bool slab_gen =
+    kind == pf::K_GEN_TILE && a.n_peers > 1 && !pl->slab_dma;
+  bool pipe = use_pipe(pl, N, kind, a);
+  if (slab_gen && !pipe && N >= 256 && pipe_launcher_for(N) &&
+      !getenv("PF_SLAB_PLAIN")) {
+    const unsigned saved = pl->pipe_mask;
+    pl->pipe_mask |= 1u << pf::K_GEN_TILE;
+    pipe = use_pipe(pl, N, kind, a);
+    pl->pipe_mask = saved;
+  }
+  PassArgs a2 = a;
   CUtensorMap tm;
+  TileMapsHost tms;
+  const void* tmptr = &tm;
   int grid = 0;
   if (pipe) {
     const int tpl = (int)(N / 32), lt = 8 * (32 / tpl);
@@ -758,6 +796,21 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     if (kind == pf::K_C2R) {
       const long long nl = (long long)a.A * a.B;
       ntiles = ((nl + 1) / 2 + lt - 1) / lt;
+    } else if (kind == pf::K_GEN_TILE) {
+      ntiles = (long long)((a.A + lt - 1) / lt) * a.B;
+      int boxr = pipe_box_rows(N);
+      if (a.n_peers > 1) {
+        boxr = std::min(boxr, a.rows_per_peer);
+        // global column extent: the peers' buffers hold all lines
+        const long long cols = a.ose; // row pitch = number of columns
+        for (int q = 0; q < a.n_peers; q++)
+          PF_TRY(make_tile_map_at(a.peer_out[q], cols, a.rows_per_peer, a.B,
+                                  a.ose, a.osb, boxr, &tms.m[q]));
+      } else {
+        PF_TRY(make_tile_map(a, boxr, &tms.m[0]));
+      }
+      a2.box_rows = boxr;
+      tmptr = &tms;
     } else {
       ntiles = (long long)((a.A + lt - 1) / lt) * a.B;
       PF_TRY(make_tile_map(a, pipe_box_rows(N), &tm));
@@ -770,7 +823,7 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     cudaEventCreate(&e1);
     cudaEventRecord(e0, pl->stream);
   }
-  const int e = pipe ? pipe_launcher_for(N)(kind, &a, tw, &tm, grid, pl->stream)
+  const int e = pipe ? pipe_launcher_for(N)(kind, &a2, tw, tmptr, grid, pl->stream)
                      : fn(kind, &a, tw, pl->stream);
   if (pl->profiling) {
     cudaEventRecord(e1, pl->stream);
@@ -1154,10 +1207,12 @@ slab_flags(const pf_plan* pl, void* block, int which)
          8 * which;
 }
 
+// first half of a slab-mode realization: pass A + start of the exchange.
+// Returns the epoch of this realization in *epoch_out.
 int
-generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
-                  unsigned long long realization, const double2* noise_dev,
-                  double* out_dev, int transform)
+slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
+             unsigned long long realization, const double2* noise_dev,
+             unsigned long long* epoch_out)
 {
   if (!pl->connected)
     return fail(PF_ERR_INVALID,
@@ -1171,8 +1226,14 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   const int P = pl->nranks;
   const unsigned long long e = ++pl->epoch;
   const int s = (int)(e & 1);
-  // peers must have consumed what we wrote into this buffer two calls ago
-  if (e > 2) {
+  *epoch_out = e;
+  if (pl->slab_dma) {
+    for (int i = 0; i < 2; i++)
+      PF_TRY(dev_alloc(&pl->send_stage[i], (size_t)(P - 1) * pl->xbuf_elems));
+    // the copies out of this staging buffer (two calls ago) must be done
+    PF_CUDA(cudaStreamWaitEvent(pl->stream, pl->ev_x[s], 0));
+  } else if (e > 2) {
+    // peers must have consumed what we stored into their buffer s
     k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
                                           e - 2, pl->d_timeout);
     pl->launches++;
@@ -1189,9 +1250,14 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   a.A = pl->a_count;
   a.n_peers = P;
   a.rows_per_peer = (int)pl->cl;
-  for (int q = 0; q < P; q++)
-    a.peer_out[q] = slab_buffer(pl, pl->peer_block[q], s);
+  for (int q = 0, k = 0; q < P; q++) {
+    if (q == pl->rank || !pl->slab_dma)
+      a.peer_out[q] = slab_buffer(pl, pl->peer_block[q], s);
+    else
+      a.peer_out[q] = pl->send_stage[s] + (size_t)(k++) * pl->xbuf_elems;
+  }
   a.out = a.peer_out[pl->rank];
+  long long rows, pitch; // geometry of one exchange buffer, in complex units
   if (pl->dim == 3) {
     a.B = (int)m0; // a = k1 (split over ranks), b = k0, e = k2
     a.cma = m0 * (n[2] / 2);
@@ -1206,6 +1272,8 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.osb = pl->cl * n[1]; // Y_q[k0][x2 local][k1]
     a.ose = n[1];
     a.keep = (int)c[2];
+    rows = m0 * pl->cl;
+    pitch = n[1];
     if (a.A > 0)
       PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
   } else {
@@ -1222,14 +1290,53 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.osb = 0; // Z_q[x1 local][k0]
     a.ose = pl->m0p;
     a.keep = (int)c[1];
+    rows = pl->cl;
+    pitch = pl->m0p;
     if (a.A > 0)
       PF_TRY(run_pass(pl, n[1], pf::K_GEN_TILE, a));
   }
-  // publish "pass A of call e done" to every rank, then wait for all ranks
-  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e);
+  if (pl->slab_dma) {
+    PF_CUDA(cudaEventRecord(pl->ev_a[s], pl->stream));
+    PF_CUDA(cudaStreamWaitEvent(pl->copy_stream, pl->ev_a[s], 0));
+    if (e > 2) {
+      k_slab_wait<<<1, 32, 0, pl->copy_stream>>>(
+        slab_flags(pl, pl->slab_block, 1), P, e - 2, pl->d_timeout);
+      pl->launches++;
+    }
+    if (pl->a_count > 0)
+      for (int q = 0, k = 0; q < P; q++) {
+        if (q == pl->rank)
+          continue;
+        const cplx* src =
+          pl->send_stage[s] + (size_t)(k++) * pl->xbuf_elems + pl->a_begin;
+        cplx* dst = slab_buffer(pl, pl->peer_block[q], s) + pl->a_begin;
+        PF_CUDA(cudaMemcpy2DAsync(dst, (size_t)pitch * sizeof(cplx), src,
+                                  (size_t)pitch * sizeof(cplx),
+                                  (size_t)pl->a_count * sizeof(cplx),
+                                  (size_t)rows, cudaMemcpyDeviceToDevice,
+                                  pl->copy_stream));
+      }
+    k_slab_signal<<<1, 32, 0, pl->copy_stream>>>(pl->d_flagsA, P, pl->rank, e);
+    pl->launches++;
+    PF_CUDA(cudaEventRecord(pl->ev_x[s], pl->copy_stream));
+  } else {
+    k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e);
+    pl->launches++;
+  }
+  PF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// second half: wait for every rank's rows, passes B and C on the local slab
+int
+slab_issue_tail(pf_plan* pl, unsigned long long e, double* out_dev,
+                int transform)
+{
+  const int P = pl->nranks;
+  const int s = (int)(e & 1);
   k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e,
                                         pl->d_timeout);
-  pl->launches += 2;
+  pl->launches++;
   PF_TRY(inverse_tail(pl, slab_buffer(pl, pl->slab_block, s), pl->cl, out_dev,
                       transform));
   // publish "buffer s consumed"
@@ -1237,6 +1344,16 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   pl->launches++;
   PF_CUDA(cudaGetLastError());
   return 0;
+}
+
+int
+generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
+                  unsigned long long realization, const double2* noise_dev,
+                  double* out_dev, int transform)
+{
+  unsigned long long e = 0;
+  PF_TRY(slab_issue_a(pl, noise_kind, seed, realization, noise_dev, &e));
+  return slab_issue_tail(pl, e, out_dev, transform);
 }
 
 // multiplyExtended / multiplyRootExtended / multiplyInverseExtended
@@ -1549,6 +1666,12 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     }
     pl->slab_block = static_cast<unsigned char*>(blk);
     pl->peer_block[pl->rank] = blk;
+    if (const char* env = getenv("PF_SLAB_EXCHANGE"))
+      pl->slab_dma = strcmp(env, "peer") != 0;
+    for (int i = 0; i < 2; i++) {
+      cudaEventCreateWithFlags(&pl->ev_a[i], cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&pl->ev_x[i], cudaEventDisableTiming);
+    }
     cudaDeviceSynchronize();
   }
   cudaStreamCreateWithFlags(&pl->copy_stream, cudaStreamNonBlocking);
@@ -1583,6 +1706,13 @@ pf_plan_destroy(pf_plan* pl)
       cudaIpcCloseMemHandle(pl->peer_block[q]);
   if (pl->slab_block)
     cudaFree(pl->slab_block);
+  for (int i = 0; i < 2; i++) {
+    dev_free(&pl->send_stage[i]);
+    if (pl->ev_a[i])
+      cudaEventDestroy(pl->ev_a[i]);
+    if (pl->ev_x[i])
+      cudaEventDestroy(pl->ev_x[i]);
+  }
   if (pl->d_flagsA)
     cudaFree(pl->d_flagsA);
   if (pl->d_flagsB)
@@ -1833,6 +1963,21 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
         PF_CUDA(cudaStreamSynchronize(pl->stream));
       }
     }
+    return 0;
+  }
+  if (dev && pl->nranks > 1) {
+    // slab mode, software pipelined: pass A (and the start of the exchange)
+    // of realization r+1 is issued before the tail of realization r, so the
+    // NVLink transfer overlaps compute
+    unsigned long long e_prev = 0, e = 0;
+    for (size_t r = 0; r < count; r++) {
+      PF_TRY(slab_issue_a(pl, nk, seed, first + r, nullptr, &e));
+      if (r > 0)
+        PF_TRY(slab_issue_tail(pl, e_prev, out + (r - 1) * pl->Dl, tr));
+      e_prev = e;
+    }
+    if (count > 0)
+      PF_TRY(slab_issue_tail(pl, e_prev, out + (count - 1) * pl->Dl, tr));
     return 0;
   }
   if (dev) {

@@ -90,6 +90,7 @@ struct PassArgs
   // through CUDA IPC) at local row e % rows_per_peer; n_peers <= 1: off
   int n_peers, rows_per_peer;
   void* peer_out[8];
+  int box_rows; // persistent pass A: element rows per tensor store
 
   // ---- contiguous line stores (re/im, lambda): line*pitch + e ------------
   void* out2;           // second line set (imag part / spare field)

@@ -140,16 +140,17 @@ extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
     return (int)cudaSuccess;
   switch (kind) {
     case K_GEN_TILE: {
-      const CUtensorMap tm = *reinterpret_cast<const CUtensorMap*>(tmap);
+      // `tmap` points to a TileMaps (one map per destination rank)
+      const TileMaps tms = *reinterpret_cast<const TileMaps*>(tmap);
       if (a.noise_kind == NOISE_PHILOX_FAST)
         e = launch_pipe(kp_gen<N, NOISE_PHILOX_FAST>, P::THREADS, P::SMEM_TILE,
-                        grid, st, a, tw2, tm);
+                        grid, st, a, tw2, tms);
       else if (a.noise_kind == NOISE_PHILOX_F64)
         e = launch_pipe(kp_gen<N, NOISE_PHILOX_F64>, P::THREADS, P::SMEM_TILE,
-                        grid, st, a, tw2, tm);
+                        grid, st, a, tw2, tms);
       else
         e = launch_pipe(kp_gen<N, NOISE_INJECTED>, P::THREADS, P::SMEM_TILE,
-                        grid, st, a, tw2, tm);
+                        grid, st, a, tw2, tms);
       break;
     }
     case K_C2T_INV: {

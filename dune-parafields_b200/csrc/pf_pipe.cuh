@@ -258,10 +258,60 @@ pipe_init(const PSmem<N>& sm, bool tile)
 // ===========================================================================
 // pass A: noise -> inverse FFT -> transposed tile (k_gen_tile)
 // ===========================================================================
+// one tensor map per destination rank (slab mode); m[0] alone otherwise
+struct TileMaps
+{
+  CUtensorMap m[8];
+};
+
+// store warp of pass A: like store_warp_loop, but every box of `box_rows`
+// element rows goes to the rank that owns those rows (tensor stores to peer
+// memory over NVLink in slab mode)
+template <int N>
+__device__ __forceinline__ void
+store_warp_loop_gen(const PassArgs& p, const TileMaps* tms, const PSmem<N>& sm,
+                    int ntA, long long ntiles)
+{
+  using P = PCfg<N>;
+  if ((threadIdx.x & 31) != 0)
+    return;
+  const int nchunk = (p.keep + P::SR - 1) / P::SR;
+  const int boxr = p.box_rows;
+  const int rpp = p.n_peers > 1 ? p.rows_per_peer : 0x7fffffff;
+  uint32_t it = 0;
+  for (long long T = blockIdx.x; T < ntiles; T += gridDim.x) {
+    const int at = (int)(T % ntA), b = (int)(T / ntA);
+    for (int c = 0; c < nchunk; c++, it++) {
+      const int s = it & 1;
+      mbar_wait(sm.bar(P::CW + s, true), (it >> 1) & 1);
+      const uint32_t st = smem_u32(sm.stage(s));
+      const int rows = min(P::SR, p.keep - c * P::SR);
+#pragma unroll
+      for (int sub = 0; sub < P::SUBS; sub++) {
+        if (at * P::LT + sub * 8 < p.A) {
+          for (int r0 = 0; r0 < rows; r0 += boxr) {
+            const int g = c * P::SR + r0;
+            const int owner = g / rpp;
+            tma_store_3d(&tms->m[owner], st + sub * P::SUB_BYTES + r0 * 128,
+                         2 * (p.a_begin + at * P::LT + sub * 8),
+                         g - owner * rpp, b);
+          }
+        }
+      }
+      bulk_commit();
+      if (it > 0) {
+        bulk_wait_read1();
+        mbar_arrive(sm.bar(P::CW + 2 + (s ^ 1), true));
+      }
+    }
+  }
+  bulk_wait0();
+}
+
 template <int N, int NOISE>
 __global__ void __launch_bounds__(PCfg<N>::THREADS, 1)
 kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
-       const __grid_constant__ CUtensorMap tm)
+       const __grid_constant__ TileMaps tms)
 {
   using P = PCfg<N>;
   extern __shared__ unsigned char smem_raw[];
@@ -271,7 +321,7 @@ kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
   const int ntA = (p.A + P::LT - 1) / P::LT;
   const long long ntiles = (long long)ntA * p.B;
   if (warp == P::CW) {
-    store_warp_loop<N>(p, &tm, sm, ntA, ntiles);
+    store_warp_loop_gen<N>(p, &tms, sm, ntA, ntiles);
     return;
   }
   const int slot = warp * P::LPW + lane / P::TPL, t = lane % P::TPL;
@@ -282,7 +332,8 @@ kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
     const int a = at * P::LT + slot;
     cplx v[P::E];
     // lines beyond A recompute the last valid line; the tensor store clips
-    load_noise<N, NOISE>(v, p, min(a, p.A - 1), b, t, true);
+    // them (A ends either at the global extent or on an 8-line boundary)
+    load_noise<N, NOISE>(v, p, p.a_begin + min(a, p.A - 1), b, t, true);
     line_fft<N, +1>(v, buf, t, tw2);
     stage_out<N>(v, sm, slot, t, p.keep, it);
   }

@@ -49,6 +49,16 @@ def main():
                 ref = full[rank * layers : (rank + 1) * layers]
                 err = float(np.max(np.abs(mine - ref)) / np.max(np.abs(full)))
                 worst = max(worst, err)
+            # pipelined batch on a device buffer
+            nb = 4
+            dev = torch.empty((nb, slab.local_domain_size), dtype=torch.float64, device="cuda")
+            slab.generate_batch(11, 100, nb, out=dev)
+            slab.synchronize()
+            for r in range(nb):
+                full = single.generate(seed=11, realization=100 + r)
+                ref = full[rank * layers : (rank + 1) * layers].ravel()
+                err = float(np.max(np.abs(dev[r].cpu().numpy() - ref)) / np.max(np.abs(full)))
+                worst = max(worst, err)
             # injected (reference-order) noise takes the same route
             rng = np.random.default_rng(5)
             noise = rng.standard_normal(2 * single.noise_entries)
