@@ -734,6 +734,36 @@ struct TileMapsHost
 {
   CUtensorMap m[8];
 };
+struct C2TMapsHost
+{
+  CUtensorMap out, in;
+};
+
+// blocked exchange buffer [plane][tile][row][8 complex] as a 4D tensor of
+// doubles; box = {16, box_rows, box_tiles, 1}
+int
+make_blocked_map(void* base, long long rows, long long tiles, long long planes,
+                 int box_rows, int box_tiles, bool swizzle, CUtensorMap* tm)
+{
+  encode_tiled_fn enc = get_encode_tiled();
+  if (!enc)
+    return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
+  const cuuint64_t gdim[4] = { 16, (cuuint64_t)rows, (cuuint64_t)tiles,
+                               (cuuint64_t)planes };
+  const cuuint64_t gstr[3] = { 128, (cuuint64_t)rows * 128,
+                               (cuuint64_t)rows * tiles * 128 };
+  const cuuint32_t box[4] = { 16, (cuuint32_t)box_rows, (cuuint32_t)box_tiles, 1 };
+  const cuuint32_t estr[4] = { 1, 1, 1, 1 };
+  const CUresult r = enc(
+    tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, base, gdim, gstr, box, estr,
+    CU_TENSOR_MAP_INTERLEAVE_NONE,
+    swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled (blocked) failed with code " +
+                               std::to_string((int)r));
+  return 0;
+}
 
 // rows per TMA box of the persistent tile kernels (PCfg<N>::BOXR)
 int
@@ -757,6 +787,8 @@ use_pipe(const pf_plan* pl, long long N, int kind, const PassArgs& a)
     if (rpp < 8 || (rpp & (rpp - 1)) != 0 || a.a_begin % 8 != 0)
       return false;
   }
+  if (a.blk_T > 256)
+    return false;
   // tile kernels: plain scale, 16-byte aligned lines, whole-line bulk copies
   if (a.scale != 1.0)
     return false;
@@ -786,9 +818,9 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     pl->pipe_mask = saved;
   }
   PassArgs a2 = a;
-  CUtensorMap tm;
   TileMapsHost tms;
-  const void* tmptr = &tm;
+  C2TMapsHost c2t;
+  const void* tmptr = &c2t;
   int grid = 0;
   if (pipe) {
     const int tpl = (int)(N / 32), lt = 8 * (32 / tpl);
@@ -803,9 +835,14 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
         boxr = std::min(boxr, a.rows_per_peer);
         // global column extent: the peers' buffers hold all lines
         const long long cols = a.ose; // row pitch = number of columns
-        for (int q = 0; q < a.n_peers; q++)
-          PF_TRY(make_tile_map_at(a.peer_out[q], cols, a.rows_per_peer, a.B,
-                                  a.ose, a.osb, boxr, &tms.m[q]));
+        for (int q = 0; q < a.n_peers; q++) {
+          if (a.blk_T > 0)
+            PF_TRY(make_blocked_map(a.peer_out[q], a.blk_rows, a.blk_T, a.B,
+                                    boxr, 1, true, &tms.m[q]));
+          else
+            PF_TRY(make_tile_map_at(a.peer_out[q], cols, a.rows_per_peer, a.B,
+                                    a.ose, a.osb, boxr, &tms.m[q]));
+        }
       } else {
         PF_TRY(make_tile_map(a, boxr, &tms.m[0]));
       }
@@ -813,7 +850,12 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
       tmptr = &tms;
     } else {
       ntiles = (long long)((a.A + lt - 1) / lt) * a.B;
-      PF_TRY(make_tile_map(a, pipe_box_rows(N), &tm));
+      PF_TRY(make_tile_map(a, pipe_box_rows(N), &c2t.out));
+      c2t.in = c2t.out;
+      if (a.blk_T > 0)
+        PF_TRY(make_blocked_map(const_cast<void*>(a.in), a.blk_rows, a.blk_T,
+                                a.A, 1, a.blk_T, false, &c2t.in));
+      tmptr = &c2t;
     }
     grid = (int)std::min<long long>(ntiles, pl->sm_count);
   }
@@ -1073,7 +1115,7 @@ set_table(const pf_plan* pl, PassArgs& a, const double* tab)
 // this rank's slab)
 int
 inverse_tail(pf_plan* pl, const cplx* Yin, long long layers, double* out_dev,
-             int transform)
+             int transform, bool blocked = false)
 {
   const long long* n = pl->n;
   const long long* c = pl->c;
@@ -1085,6 +1127,10 @@ inverse_tail(pf_plan* pl, const cplx* Yin, long long layers, double* out_dev,
     b.isa = layers * n[1];
     b.isb = n[1];
     b.n_valid = (int)n[1];
+    if (blocked) { // slab mode: Y[k0][k1/8][x2 local][k1%8]
+      b.blk_T = (int)(n[1] / 8);
+      b.blk_rows = (int)layers;
+    }
     b.out = pl->Z; // Z[x2][x1][k0]
     b.osb = c[1] * pl->m0p;
     b.ose = pl->m0p;
@@ -1257,7 +1303,9 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
       a.peer_out[q] = pl->send_stage[s] + (size_t)(k++) * pl->xbuf_elems;
   }
   a.out = a.peer_out[pl->rank];
-  long long rows, pitch; // geometry of one exchange buffer, in complex units
+  // geometry of the rows this rank contributes to one exchange buffer, in
+  // complex units: `rows` runs of `xwidth` elements at offset `xoff`
+  long long rows, pitch, xoff = 0, xwidth = 0;
   if (pl->dim == 3) {
     a.B = (int)m0; // a = k1 (split over ranks), b = k0, e = k2
     a.cma = m0 * (n[2] / 2);
@@ -1269,11 +1317,23 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.na_self = (int)n[1];
     a.nb_self = (int)n[0];
     a.plane_axis = 1;
-    a.osb = pl->cl * n[1]; // Y_q[k0][x2 local][k1]
+    a.osb = pl->cl * n[1]; // Y_q[k0][k1/8][x2 local][k1%8] (blocked)
     a.ose = n[1];
     a.keep = (int)c[2];
-    rows = m0 * pl->cl;
-    pitch = n[1];
+    if (n[1] % 8 == 0) {
+      a.blk_T = (int)(n[1] / 8);
+      a.blk_rows = (int)pl->cl;
+      // per plane k0 this rank's tiles are one contiguous run
+      rows = m0;
+      pitch = n[1] * pl->cl;
+      xoff = (long long)(pl->a_begin / 8) * pl->cl * 8;
+      xwidth = (long long)((pl->a_count + 7) / 8) * pl->cl * 8;
+    } else {
+      rows = m0 * pl->cl;
+      pitch = n[1];
+      xoff = pl->a_begin;
+      xwidth = pl->a_count;
+    }
     if (a.A > 0)
       PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
   } else {
@@ -1292,6 +1352,8 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.keep = (int)c[1];
     rows = pl->cl;
     pitch = pl->m0p;
+    xoff = pl->a_begin;
+    xwidth = pl->a_count;
     if (a.A > 0)
       PF_TRY(run_pass(pl, n[1], pf::K_GEN_TILE, a));
   }
@@ -1308,11 +1370,11 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
         if (q == pl->rank)
           continue;
         const cplx* src =
-          pl->send_stage[s] + (size_t)(k++) * pl->xbuf_elems + pl->a_begin;
-        cplx* dst = slab_buffer(pl, pl->peer_block[q], s) + pl->a_begin;
+          pl->send_stage[s] + (size_t)(k++) * pl->xbuf_elems + xoff;
+        cplx* dst = slab_buffer(pl, pl->peer_block[q], s) + xoff;
         PF_CUDA(cudaMemcpy2DAsync(dst, (size_t)pitch * sizeof(cplx), src,
                                   (size_t)pitch * sizeof(cplx),
-                                  (size_t)pl->a_count * sizeof(cplx),
+                                  (size_t)xwidth * sizeof(cplx),
                                   (size_t)rows, cudaMemcpyDeviceToDevice,
                                   pl->copy_stream));
       }
@@ -1338,7 +1400,7 @@ slab_issue_tail(pf_plan* pl, unsigned long long e, double* out_dev,
                                         pl->d_timeout);
   pl->launches++;
   PF_TRY(inverse_tail(pl, slab_buffer(pl, pl->slab_block, s), pl->cl, out_dev,
-                      transform));
+                      transform, pl->dim == 3 && pl->n[1] % 8 == 0));
   // publish "buffer s consumed"
   k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsB, P, pl->rank, e);
   pl->launches++;

@@ -91,6 +91,11 @@ struct PassArgs
   int n_peers, rows_per_peer;
   void* peer_out[8];
   int box_rows; // persistent pass A: element rows per tensor store
+  // blocked exchange layout (3D slab mode), blk_T > 0: the buffer between
+  // pass A and pass B is [b][tile = a/8][row][a%8] with blk_T tiles per
+  // plane and blk_rows rows per tile, so that the rows a rank sends to one
+  // peer form contiguous blocks (long NVLink bursts)
+  int blk_T, blk_rows;
 
   // ---- contiguous line stores (re/im, lambda): line*pitch + e ------------
   void* out2;           // second line set (imag part / spare field)

@@ -154,13 +154,13 @@ extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
       break;
     }
     case K_C2T_INV: {
-      const CUtensorMap tm = *reinterpret_cast<const CUtensorMap*>(tmap);
+      const C2TMaps tm = *reinterpret_cast<const C2TMaps*>(tmap);
       e = launch_pipe(kp_c2t<N, +1>, P::THREADS, P::SMEM_TILE, grid, st, a, tw2,
                       tm);
       break;
     }
     case K_C2T_FWD: {
-      const CUtensorMap tm = *reinterpret_cast<const CUtensorMap*>(tmap);
+      const C2TMaps tm = *reinterpret_cast<const C2TMaps*>(tmap);
       e = launch_pipe(kp_c2t<N, -1>, P::THREADS, P::SMEM_TILE, grid, st, a, tw2,
                       tm);
       break;

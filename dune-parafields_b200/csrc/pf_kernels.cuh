@@ -362,7 +362,8 @@ tile_base(const PassArgs& p, int b, int first_line)
 template <int N>
 __device__ __forceinline__ void
 tile_store_peers(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t,
-                 const PassArgs& p, long long base_off, int lines_valid)
+                 const PassArgs& p, long long base_off, int lines_valid, int b,
+                 int a0)
 {
   using K = KCfg<N>;
   __syncthreads();
@@ -381,7 +382,12 @@ tile_store_peers(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t,
       const int owner = e / p.rows_per_peer;
       const int el = e - owner * p.rows_per_peer;
       cplx* o = reinterpret_cast<cplx*>(p.peer_out[owner]);
-      o[base_off + (long long)el * p.ose + l] = stage[stage_slot<N>(e, l)];
+      if (p.blk_T > 0) {
+        const int ag = a0 + l; // global line
+        o[(((long long)b * p.blk_T + (ag >> 3)) * p.blk_rows + el) * 8 +
+          (ag & 7)] = stage[stage_slot<N>(e, l)];
+      } else
+        o[base_off + (long long)el * p.ose + l] = stage[stage_slot<N>(e, l)];
     }
   }
 }
@@ -410,7 +416,8 @@ k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
   const int lv = min(K::LPC, p.A - at * K::LPC);
   if (p.n_peers > 1)
     tile_store_peers<N>(v, sm, lic, t, p,
-                        (long long)b * p.osb + p.a_begin + at * K::LPC, lv);
+                        (long long)b * p.osb + p.a_begin + at * K::LPC, lv, b,
+                        p.a_begin + at * K::LPC);
   else
     tile_store<N>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
 }
@@ -465,9 +472,22 @@ k_c2t(const PassArgs p, const cplx* __restrict__ tw2)
   const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
   const int a = at * K::LPC + lic;
   cplx v[K::E];
-  const cplx* line = reinterpret_cast<const cplx*>(p.in) +
-                     (long long)a * p.isa + (long long)b * p.isb;
-  load_contig<N>(v, line, t, p.n_valid, a < p.A);
+  if (p.blk_T > 0) {
+    // blocked exchange layout: line (a = plane, b = row), element e = 8*tile+j
+    const cplx* base = reinterpret_cast<const cplx*>(p.in) +
+                       ((long long)a * p.blk_T * p.blk_rows + b) * 8;
+#pragma unroll
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      v[q] = (a < p.A && e < p.n_valid)
+               ? __ldg(base + (long long)(e >> 3) * p.blk_rows * 8 + (e & 7))
+               : make_double2(0., 0.);
+    }
+  } else {
+    const cplx* line = reinterpret_cast<const cplx*>(p.in) +
+                       (long long)a * p.isa + (long long)b * p.isb;
+    load_contig<N>(v, line, t, p.n_valid, a < p.A);
+  }
   line_fft<N, DIR>(v, sm + lic * K::C::PITCH, t, tw2);
   const int lv = min(K::LPC, p.A - at * K::LPC);
   tile_store<N>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC), p.ose, lv,

@@ -112,6 +112,24 @@ tma_store_3d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2)
                : "memory");
 }
 __device__ __forceinline__ void
+tma_store_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3)
+{
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group "
+               "[%0, {%2, %3, %4, %5}], [%1];" ::"l"(tm),
+               "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+// global -> shared tensor load of one box, completion counted on `bar`
+__device__ __forceinline__ void
+tma_load_4d(const CUtensorMap* tm, uint32_t dst, uint32_t bar, int c0, int c1,
+            int c2, int c3)
+{
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::"
+               "complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+               "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void
 bulk_commit()
 {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -292,9 +310,14 @@ store_warp_loop_gen(const PassArgs& p, const TileMaps* tms, const PSmem<N>& sm,
           for (int r0 = 0; r0 < rows; r0 += boxr) {
             const int g = c * P::SR + r0;
             const int owner = g / rpp;
-            tma_store_3d(&tms->m[owner], st + sub * P::SUB_BYTES + r0 * 128,
-                         2 * (p.a_begin + at * P::LT + sub * 8),
-                         g - owner * rpp, b);
+            if (p.blk_T > 0)
+              tma_store_4d(&tms->m[owner], st + sub * P::SUB_BYTES + r0 * 128, 0,
+                           g - owner * rpp,
+                           (p.a_begin + at * P::LT + sub * 8) >> 3, b);
+            else
+              tma_store_3d(&tms->m[owner], st + sub * P::SUB_BYTES + r0 * 128,
+                           2 * (p.a_begin + at * P::LT + sub * 8),
+                           g - owner * rpp, b);
           }
         }
       }
@@ -342,11 +365,18 @@ kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
 // ===========================================================================
 // pass B / F1 / E1: contiguous complex lines -> FFT -> transposed tile (k_c2t)
 // ===========================================================================
+// output tile map and (blocked exchange layout only) input line map
+struct C2TMaps
+{
+  CUtensorMap out, in;
+};
+
 template <int N, int DIR>
 __global__ void __launch_bounds__(PCfg<N>::THREADS, 1)
 kp_c2t(const PassArgs p, const cplx* __restrict__ tw2,
-       const __grid_constant__ CUtensorMap tm)
+       const __grid_constant__ C2TMaps maps)
 {
+  const CUtensorMap& tm = maps.out;
   using P = PCfg<N>;
   extern __shared__ unsigned char smem_raw[];
   PSmem<N> sm(smem_raw);
@@ -371,10 +401,15 @@ kp_c2t(const PassArgs p, const cplx* __restrict__ tw2,
     if (lane == 0) {
       fence_proxy_async();
       mbar_expect_tx(inbar, (uint32_t)nv * line_bytes);
-      for (int l = 0; l < nv; l++)
-        bulk_load(smem_u32(sm.slot(warp * P::LPW + l)),
-                  in + (long long)(a0 + l) * p.isa + (long long)b * p.isb,
-                  line_bytes, inbar);
+      for (int l = 0; l < nv; l++) {
+        if (p.blk_T > 0) // line (plane a, row b): blk_T segments of 128 bytes
+          tma_load_4d(&maps.in, smem_u32(sm.slot(warp * P::LPW + l)), inbar, 0,
+                      b, 0, a0 + l);
+        else
+          bulk_load(smem_u32(sm.slot(warp * P::LPW + l)),
+                    in + (long long)(a0 + l) * p.isa + (long long)b * p.isb,
+                    line_bytes, inbar);
+      }
     }
   };
   uint32_t it = 0, ph = 0;
