@@ -176,6 +176,26 @@ k_derive_table(const double* __restrict__ lam, double* __restrict__ out,
   out[i] = r;
 }
 
+// same with a padded output pitch (rows of P values at pitch Pg >= P, padding
+// zeroed): the sigma table of generateField keeps its rows 16-byte aligned so
+// that a row can travel by one bulk copy (kp_gen3)
+__global__ void
+k_derive_table_padded(const double* __restrict__ lam, double* __restrict__ out,
+                      size_t rows, long long P, long long Pg, int mode)
+{
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * (size_t)Pg)
+    return;
+  const size_t r = i / (size_t)Pg;
+  const long long e = (long long)(i % (size_t)Pg);
+  double v = 0.;
+  if (e < P) {
+    const double l = lam[r * (size_t)P + e];
+    v = mode == 0 ? sqrt(l) / sqrt(2.) : (mode == 1 ? sqrt(l) : 1. / l);
+  }
+  out[i] = v;
+}
+
 struct GatherArgs
 {
   int dim;
@@ -437,6 +457,7 @@ struct pf_plan
   bool compact = false;   // DCT matrix backend semantics (iso / axiparallel)
   bool hermitian = false; // R2C field backend (dim > 1); 1D uses DFT backends
   long long rows = 0, P = 0; // table rows and row pitch
+  long long Pg = 0;          // pitch of sig_gen (P rounded up to even)
   size_t tab_elems = 0;
   size_t D = 1, Next = 1;
 
@@ -494,8 +515,10 @@ struct pf_plan
   // PF_PIPE=0 in the environment selects the plain kernels everywhere
   // (pass A stays on the plain kernel: it is issue-bound and the plain
   // kernel keeps 12 warps per SM against 8 FFT warps, profiles/r01b)
+  bool gen3_force = false; // tests: take kp_gen3 whenever it is applicable
+  // bit K_GEN3: grouped persistent pass A (kp_gen3), 12 FFT warps per SM
   unsigned pipe_mask = (1u << pf::K_C2T_INV) | (1u << pf::K_C2T_FWD) |
-                       (1u << pf::K_C2R);
+                       (1u << pf::K_C2R) | (1u << pf::K_GEN3);
 };
 
 namespace {
@@ -584,6 +607,7 @@ plan_resize(pf_plan* pl)
     pl->P = pl->n[0];
   }
   pl->tab_elems = (size_t)pl->rows * pl->P;
+  pl->Pg = (pl->P + 1) & ~1LL;
 
   // covariance parameters (matrix.hh:624-648, covariance.hh:17-136)
   pf::CovParams& cv = pl->cov;
@@ -701,7 +725,8 @@ twiddles(pf_plan* pl, long long N, const cplx** out)
 // (the tile axis), dim1 = element row e < keep, dim2 = b
 int
 make_tile_map_at(void* base, long long cols, long long rows, long long planes,
-                 long long ose, long long osb, int boxr, CUtensorMap* tm)
+                 long long ose, long long osb, int boxr, CUtensorMap* tm,
+                 int box_cols = 8)
 {
   encode_tiled_fn enc = get_encode_tiled();
   if (!enc)
@@ -712,11 +737,14 @@ make_tile_map_at(void* base, long long cols, long long rows, long long planes,
   const cuuint64_t plane =
     planes > 1 ? (cuuint64_t)osb * 16 : row * (cuuint64_t)rows;
   const cuuint64_t gstr[2] = { row, plane };
-  const cuuint32_t box[3] = { 16, (cuuint32_t)boxr, 1 };
+  // box_cols complex columns per row: 8 -> 128-byte rows, 4 -> 64-byte rows,
+  // staged with the matching swizzle
+  const cuuint32_t box[3] = { (cuuint32_t)(2 * box_cols), (cuuint32_t)boxr, 1 };
   const cuuint32_t estr[3] = { 1, 1, 1 };
   const CUresult r =
     enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, gdim, gstr, box, estr,
-        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+        CU_TENSOR_MAP_INTERLEAVE_NONE,
+        box_cols == 4 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " +
@@ -822,7 +850,33 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
   C2TMapsHost c2t;
   const void* tmptr = &c2t;
   int grid = 0;
-  if (pipe) {
+  int launch_kind = kind;
+  // grouped persistent pass A: single rank, lines of 512 / 1024, at most
+  // half of the line kept, sigma rows 16-byte aligned
+  // (measured on B200: ahead of the per-tile kernel only for N = 1024 and
+  // grids of many waves; K2's N = 512 and small 2D problems stay plain)
+  const bool gen3_size =
+    pl->gen3_force ? (N == 512 || N == 1024)
+                   : (N == 1024 &&
+                      (long long)((a.A + 3) / 4) * a.B >= 8LL * pl->sm_count);
+  const bool gen3 =
+    kind == pf::K_GEN_TILE && a.n_peers <= 1 && gen3_size &&
+    (pl->pipe_mask & (1u << pf::K_GEN3)) && !(pl->pipe_mask & 1u) &&
+    a.keep >= 1 && a.keep <= N / 2 && a.scale == 1.0 && a.a_begin == 0 &&
+    a.tab_pitch % 2 == 0 && (reinterpret_cast<uintptr_t>(a.tab) & 15) == 0 &&
+    (long long)(a.tab_mirror_e ? N / 2 + 2 : N) <= a.tab_pitch &&
+    pipe_launcher_for(N);
+  if (gen3) {
+    const int lpc = N == 1024 ? 4 : 8;
+    const long long ntiles = (long long)((a.A + lpc - 1) / lpc) * a.B;
+    const int boxr = (int)std::min<long long>(256, N / 2);
+    PF_TRY(make_tile_map_at(a.out, a.A, a.keep, a.B, a.ose, a.osb, boxr,
+                            &tms.m[0], lpc));
+    tmptr = &tms;
+    grid = (int)std::min<long long>((ntiles + 2) / 3, pl->sm_count);
+    launch_kind = pf::K_GEN3;
+    pipe = true;
+  } else if (pipe) {
     const int tpl = (int)(N / 32), lt = 8 * (32 / tpl);
     long long ntiles;
     if (kind == pf::K_C2R) {
@@ -865,7 +919,7 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     cudaEventCreate(&e1);
     cudaEventRecord(e0, pl->stream);
   }
-  const int e = pipe ? pipe_launcher_for(N)(kind, &a2, tw, tmptr, grid, pl->stream)
+  const int e = pipe ? pipe_launcher_for(N)(launch_kind, &a2, tw, tmptr, grid, pl->stream)
                      : fn(kind, &a, tw, pl->stream);
   if (pl->profiling) {
     cudaEventRecord(e1, pl->stream);
@@ -1075,6 +1129,22 @@ ensure_table(pf_plan* pl, double** tab, int mode)
   return 0;
 }
 
+// sigma table of generateField: padded pitch Pg
+int
+ensure_sig_gen(pf_plan* pl, int mode)
+{
+  PF_TRY(ensure_eigen(pl));
+  if (pl->sig_gen)
+    return 0;
+  const size_t total = (size_t)pl->rows * pl->Pg;
+  PF_TRY(dev_alloc(&pl->sig_gen, total));
+  k_derive_table_padded<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
+    pl->lam, pl->sig_gen, (size_t)pl->rows, pl->P, pl->Pg, mode);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return 0;
+}
+
 int
 ensure_work(pf_plan* pl)
 {
@@ -1165,13 +1235,14 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   if (pl->nranks > 1)
     return generate_slab_dev(pl, noise_kind, seed, realization, noise_dev,
                              out_dev, transform);
-  PF_TRY(ensure_table(pl, &pl->sig_gen, pl->hermitian ? 0 : 1));
+  PF_TRY(ensure_sig_gen(pl, pl->hermitian ? 0 : 1));
   PF_TRY(ensure_work(pl));
   const long long* n = pl->n;
   const long long* c = pl->c;
   const long long m0 = pl->m0;
   PassArgs a = blank_args();
   set_table(pl, a, pl->sig_gen);
+  a.tab_pitch = pl->Pg;
   a.noise_kind = noise_kind;
   a.keys = pf::philox_keys(seed);
   a.realization = realization;
@@ -1263,7 +1334,7 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
   if (!pl->connected)
     return fail(PF_ERR_INVALID,
                 "slab mode: call pf_slab_connect on every rank first");
-  PF_TRY(ensure_table(pl, &pl->sig_gen, 0));
+  PF_TRY(ensure_sig_gen(pl, 0));
   if (pl->dim == 3)
     PF_TRY(dev_alloc(&pl->Z, (size_t)pl->cl * pl->c[1] * pl->m0p));
   const long long* n = pl->n;
@@ -1286,6 +1357,7 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
   }
   PassArgs a = blank_args();
   set_table(pl, a, pl->sig_gen);
+  a.tab_pitch = pl->Pg;
   a.noise_kind = noise_kind;
   a.keys = pf::philox_keys(seed);
   a.realization = realization;
@@ -1693,6 +1765,8 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
                          pl->device);
   if (const char* env = getenv("PF_PIPE"))
     pl->pipe_mask = (unsigned)strtoul(env, nullptr, 0);
+  if (const char* env = getenv("PF_GEN3")) // "force": skip the size heuristic
+    pl->gen3_force = std::string(env) == "force";
   pl->nranks = desc->n_ranks > 1 ? desc->n_ranks : 1;
   pl->rank = pl->nranks > 1 ? desc->rank : 0;
   if (pl->nranks > 8 || pl->rank < 0 || pl->rank >= pl->nranks) {

@@ -48,7 +48,8 @@ enum
   K_LAMBDA = 7,     // contiguous complex -> fwd FFT -> eigenvalues  (E2)
   K_LAMBDA_COV = 8, // covariance eval (1D) -> fwd FFT -> eigenvalues
   K_SPEC_TILE = 9,  // contiguous -> fwd FFT * g(lambda) inv FFT -> tile (F2+A)
-  K_SPEC_REIM = 10  // real line (1D) -> fwd * g inv -> real line
+  K_SPEC_REIM = 10, // real line (1D) -> fwd * g inv -> real line
+  K_GEN3 = 16       // pass A, grouped persistent form (pipe launcher only)
 };
 
 // noise sources of K_GEN_*

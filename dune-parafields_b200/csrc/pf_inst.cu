@@ -153,6 +153,24 @@ extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
                         grid, st, a, tw2, tms);
       break;
     }
+#if PF_N >= 512
+    case K_GEN3: {
+      // grouped pass A: `tmap` points to a TileMaps whose m[0] describes the
+      // output with LPC*16-byte boxes in the matching swizzle mode
+      using G = G3Cfg<N>;
+      const TileMaps tms = *reinterpret_cast<const TileMaps*>(tmap);
+      if (a.noise_kind == NOISE_PHILOX_FAST)
+        e = launch_pipe(kp_gen3<N, NOISE_PHILOX_FAST>, G::THREADS, G::SMEM, grid,
+                        st, a, tw2, tms);
+      else if (a.noise_kind == NOISE_PHILOX_F64)
+        e = launch_pipe(kp_gen3<N, NOISE_PHILOX_F64>, G::THREADS, G::SMEM, grid,
+                        st, a, tw2, tms);
+      else
+        e = launch_pipe(kp_gen3<N, NOISE_INJECTED>, G::THREADS, G::SMEM, grid,
+                        st, a, tw2, tms);
+      break;
+    }
+#endif
     case K_C2T_INV: {
       const C2TMaps tm = *reinterpret_cast<const C2TMaps*>(tmap);
       e = launch_pipe(kp_c2t<N, +1>, P::THREADS, P::SMEM_TILE, grid, st, a, tw2,

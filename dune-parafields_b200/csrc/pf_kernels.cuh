@@ -284,6 +284,77 @@ load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
   }
 }
 
+// load_noise split in two for kernels that receive the sigma row through
+// shared memory (kp_gen3): unit normals first, the scaling afterwards.  Same
+// products as load_noise, so the results are bit-identical.
+template <int N, int NOISE>
+__device__ __forceinline__ void
+gen_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t)
+{
+  using C = LineCfg<N>;
+  constexpr int H = C::E / 2;
+  const unsigned long long cbase =
+    (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
+  const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
+#pragma unroll
+  for (int q = 0; q < H; q++) {
+    const int e = t + C::TPL * q;
+    double2 n1, n2;
+    if constexpr (NOISE == NOISE_INJECTED) {
+      n1 = __ldg(p.noise + ibase + (long long)e * p.ime);
+      n2 = __ldg(p.noise + ibase + (long long)(e + N / 2) * p.ime);
+    } else {
+      const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
+      if constexpr (NOISE == NOISE_PHILOX_FAST) {
+        const uint4 w = philox4x32_r<7>(ctr, p.realization, p.keys);
+        n1 = box_muller_fast(w.x, w.y);
+        n2 = box_muller_fast(w.z, w.w);
+      } else {
+        const uint4 w = philox4x32_r<10>(ctr, p.realization, p.keys);
+        n1 = box_muller_f64(w.x, w.y);
+        n2 = box_muller_f64(w.z, w.w);
+      }
+    }
+    v[q] = n1;
+    v[q + H] = n2;
+  }
+}
+
+// srow: the line's sigma row (shared memory), indexed like table_row()
+template <int N>
+__device__ __forceinline__ void
+scale_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, const double* srow,
+            int a, int b, int t)
+{
+  using C = LineCfg<N>;
+  constexpr int H = C::E / 2;
+  constexpr double SQRT2 = 1.41421356237309504880168872420969808;
+  const int dir2 = p.tab_mirror_e ? -1 : 1;
+  const double* srow2 = srow + N / 2;
+#pragma unroll
+  for (int q = 0; q < H; q++) {
+    const int e = t + C::TPL * q;
+    const double s1 = srow[e], s2 = srow2[dir2 * e];
+    v[q] = make_double2(s1 * v[q].x, s1 * v[q].y);
+    v[q + H] = make_double2(s2 * v[q + H].x, s2 * v[q + H].y);
+  }
+  if (p.hermitian) {
+    const bool a_self = (2 * a) % p.na_self == 0;
+    const bool b_self = (2 * b) % p.nb_self == 0;
+    const bool plane = p.corrected && (p.plane_axis == 0 ? a_self : b_self);
+    if (plane) {
+#pragma unroll
+      for (int q = 0; q < C::E; q++)
+        v[q] = make_double2(v[q].x * SQRT2, v[q].y * SQRT2);
+    }
+    if (t == 0 && a_self && b_self) {
+      const double f = plane ? 1.0 : SQRT2;
+      v[0] = make_double2(v[0].x * f, 0.);
+      v[H] = make_double2(v[H].x * f, 0.);
+    }
+  }
+}
+
 template <int N>
 __device__ __forceinline__ void
 load_contig(cplx (&v)[LineCfg<N>::E], const cplx* __restrict__ line, int t,
@@ -318,6 +389,18 @@ stage_slot(int e, int l)
     return e * K::SP + l;
 }
 
+// row pitch of the stage in complex numbers and the slot of (e, l); for the
+// swizzled layouts the swizzle term depends on e only through bits that a
+// step of PF_THREADS / LPC rows leaves unchanged, so a thread's slots (and
+// output addresses) advance by a constant per step
+template <int N>
+__device__ __forceinline__ constexpr int
+stage_pitch()
+{
+  using K = KCfg<N>;
+  return (K::LPC == 4 || K::LPC == 8) ? K::LPC : K::SP;
+}
+
 template <int N>
 __device__ __forceinline__ void
 tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
@@ -326,19 +409,49 @@ tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
 {
   using K = KCfg<N>;
   __syncthreads(); // exchange area is about to be reused as the stage
+  if (scale == 1.0) {
 #pragma unroll
-  for (int q = 0; q < K::E; q++) {
-    const int e = t + K::TPL * q;
-    if (e < keep)
-      stage[stage_slot<N>(e, lic)] =
-        make_double2(v[q].x * scale, v[q].y * scale);
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      if (e < keep)
+        stage[stage_slot<N>(e, lic)] = v[q];
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < K::E; q++) {
+      const int e = t + K::TPL * q;
+      if (e < keep)
+        stage[stage_slot<N>(e, lic)] =
+          make_double2(v[q].x * scale, v[q].y * scale);
+    }
   }
   __syncthreads();
-  const int total = keep * K::LPC;
-  for (int idx = threadIdx.x; idx < total; idx += PF_THREADS) {
-    const int l = idx % K::LPC, e = idx / K::LPC;
-    if (l < lines_valid)
-      obase[(long long)e * ose + l] = stage[stage_slot<N>(e, l)];
+  // read-out: thread -> (row e0 + i*STEP, line l); loads batched four deep so
+  // that the shared-memory latency is paid once per batch
+  constexpr int STEP = PF_THREADS / K::LPC;
+  constexpr int SSTEP = STEP * stage_pitch<N>();
+  static_assert(PF_THREADS % K::LPC == 0, "tile read-out mapping");
+  const int l = threadIdx.x % K::LPC, e0 = threadIdx.x / K::LPC;
+  if (l >= lines_valid)
+    return;
+  const cplx* sp = stage + stage_slot<N>(e0, l);
+  cplx* op = obase + (long long)e0 * ose + l;
+  const long long ostep = (long long)STEP * ose;
+  int e = e0;
+  for (; e + 3 * STEP < keep; e += 4 * STEP) {
+    const cplx a0 = sp[0], a1 = sp[SSTEP], a2 = sp[2 * SSTEP],
+               a3 = sp[3 * SSTEP];
+    op[0] = a0;
+    op[ostep] = a1;
+    op[2 * ostep] = a2;
+    op[3 * ostep] = a3;
+    sp += 4 * SSTEP;
+    op += 4 * ostep;
+  }
+  for (; e < keep; e += STEP) {
+    op[0] = sp[0];
+    sp += SSTEP;
+    op += ostep;
   }
 }
 
@@ -494,6 +607,64 @@ k_c2t(const PassArgs p, const cplx* __restrict__ tw2)
                 p.scale);
 }
 
+// epilogue of pass C: registers (x = line L0, y = line L1, thread t owns
+// elements t + TPL*q) -> two real output lines, restricted to e < keep, value
+// transform fused.  Pointers and bounds are materialised once; the common case
+// (both lines valid, scale 1) is a run of predicated 8-byte stores.
+template <int N, int TR, bool SCALE>
+__device__ __forceinline__ void
+store_real_pair_impl(const cplx (&v)[LineCfg<N>::E], double* __restrict__ o0,
+                     double* __restrict__ o1, bool v0, bool v1, int t, int keep,
+                     double scale, double tparam)
+{
+  using C = LineCfg<N>;
+  if (v0 && v1) {
+#pragma unroll
+    for (int q = 0; q < C::E; q++) {
+      if (t + C::TPL * q < keep) {
+        double x = v[q].x, y = v[q].y;
+        if constexpr (SCALE) {
+          x *= scale;
+          y *= scale;
+        }
+        o0[C::TPL * q] = apply_transform_c<TR>(x, tparam);
+        o1[C::TPL * q] = apply_transform_c<TR>(y, tparam);
+      }
+    }
+  } else if (v0) {
+#pragma unroll
+    for (int q = 0; q < C::E; q++) {
+      if (t + C::TPL * q < keep) {
+        double x = v[q].x;
+        if constexpr (SCALE)
+          x *= scale;
+        o0[C::TPL * q] = apply_transform_c<TR>(x, tparam);
+      }
+    }
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void
+store_real_pair(const cplx (&v)[LineCfg<N>::E], const PassArgs& p, long long L0,
+                bool v0, bool v1, int t)
+{
+  double* out = reinterpret_cast<double*>(p.out);
+  double* o0 = out + L0 * p.out_pitch + t;
+  double* o1 = o0 + p.out_pitch;
+  const int keep = p.keep;
+  const double scale = p.scale, tparam = p.tparam;
+  dispatch_transform(p.transform, [&](auto trc) {
+    constexpr int TR = decltype(trc)::value;
+    if (scale == 1.0)
+      store_real_pair_impl<N, TR, false>(v, o0, o1, v0, v1, t, keep, scale,
+                                         tparam);
+    else
+      store_real_pair_impl<N, TR, true>(v, o0, o1, v0, v1, t, keep, scale,
+                                        tparam);
+  });
+}
+
 // pass C: two half-spectrum lines (m0 = N/2+1 complex each) -> one complex
 // inverse FFT -> two real lines, restricted to e < keep, value transform
 // fused.  c2r semantics of FFTW on non-Hermitian input: Im at k0 in {0,N/2}
@@ -528,22 +699,7 @@ k_c2r(const PassArgs p, const cplx* __restrict__ tw2)
       v[q] = make_double2(xa.x + xb.y, xb.x - xa.y);
   }
   line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
-  double* out = reinterpret_cast<double*>(p.out);
-  dispatch_transform(p.transform, [&](auto trc) {
-    constexpr int TR = decltype(trc)::value;
-#pragma unroll
-    for (int q = 0; q < K::E; q++) {
-      const int e = t + K::TPL * q;
-      if (e < p.keep) {
-        if (v0)
-          out[L0 * p.out_pitch + e] =
-            apply_transform_c<TR>(v[q].x * p.scale, p.tparam);
-        if (v1)
-          out[L1 * p.out_pitch + e] =
-            apply_transform_c<TR>(v[q].y * p.scale, p.tparam);
-      }
-    }
-  });
+  store_real_pair<N>(v, p, L0, v0, v1, t);
 }
 
 // F0 / E0: two real lines (loaded or covariance-evaluated) -> one complex

@@ -230,26 +230,34 @@ stage_out(const cplx (&v)[LineCfg<N>::E], const PSmem<N>& sm, int slot, int t,
           int keep, uint32_t& it)
 {
   using P = PCfg<N>;
+  // chunk c holds element rows [c*SR, (c+1)*SR): registers QPC*c .. QPC*c+QPC-1
+  // of every thread, row r = t + TPL*j inside the chunk, so the swizzle term
+  // (r & 7 == t & 7) and all offsets but the thread's own are compile-time
+  constexpr int QPC = P::SR / P::TPL;
+  constexpr int NCH = P::E / QPC;
+  static_assert(P::SR % P::TPL == 0 && P::TPL % 8 == 0 && P::E % QPC == 0,
+                "stage_out chunk mapping");
   const int l8 = slot & 7;
   const int nchunk = (keep + P::SR - 1) / P::SR;
-  for (int c = 0; c < nchunk; c++, it++) {
-    const int s = it & 1;
-    mbar_wait(sm.bar(P::CW + 2 + s, true), ((it >> 1) & 1) ^ 1);
-    unsigned char* st = sm.stage(s) + (slot >> 3) * P::SUB_BYTES;
-    const int lo = c * P::SR;
-    const int hi = min(keep, lo + P::SR);
+  const uint32_t toff =
+    (uint32_t)(slot >> 3) * P::SUB_BYTES + t * 128 + ((l8 ^ (t & 7)) << 4);
 #pragma unroll
-    for (int q = 0; q < P::E; q++) {
-      const int e = t + P::TPL * q;
-      if (e >= lo && e < hi) {
-        const int r = e - lo;
-        *reinterpret_cast<cplx*>(st + r * 128 + ((l8 ^ (r & 7)) << 4)) = v[q];
+  for (int c = 0; c < NCH; c++) {
+    if (c < nchunk) {
+      const int s = it & 1;
+      mbar_wait(sm.bar(P::CW + 2 + s, true), ((it >> 1) & 1) ^ 1);
+      unsigned char* st = sm.stage(s) + toff;
+#pragma unroll
+      for (int j = 0; j < QPC; j++) {
+        if (t + P::TPL * (QPC * c + j) < keep)
+          *reinterpret_cast<cplx*>(st + j * P::TPL * 128) = v[QPC * c + j];
       }
+      fence_proxy_async();
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0)
+        mbar_arrive(sm.bar(P::CW + s, true));
+      it++;
     }
-    fence_proxy_async();
-    __syncwarp();
-    if ((threadIdx.x & 31) == 0)
-      mbar_arrive(sm.bar(P::CW + s, true));
   }
 }
 
@@ -360,6 +368,121 @@ kp_gen(const PassArgs p, const cplx* __restrict__ tw2,
     line_fft<N, +1>(v, buf, t, tw2);
     stage_out<N>(v, sm, slot, t, p.keep, it);
   }
+}
+
+// ===========================================================================
+// pass A, grouped form (kp_gen3): one CTA per SM, three independent groups of
+// four warps (the register file holds twelve 168-register FFT warps and no
+// more, so no warp is spent on a store role).  Per tile of LPC lines a group
+//   1. starts bulk copies of the lines' sigma rows into its landing zone,
+//   2. generates the unit normals in registers (Philox + Box-Muller),
+//   3. waits for the rows, scales, runs the line FFTs,
+//   4. stages the transposed tile with the TMA swizzle and hands it to ONE
+//      tensor store, which drains while the group is already generating the
+//      next tile's noise (the stage is only needed again at the next FFT).
+// Shared memory per group = the exchange buffers of its lines (66 KB), reused
+// as stage [0, 32 KB) and sigma landing zone [32 KB, 64 KB).
+// ===========================================================================
+template <int N>
+struct G3Cfg
+{
+  using K = KCfg<N>;
+  static constexpr int GROUPS = 3;
+  static constexpr int THREADS = GROUPS * PF_THREADS;
+  static constexpr int ROWB = K::LPC * 16;          // bytes per stage row
+  static constexpr int REGION = (int)K::exch_bytes; // per group
+  static constexpr int MAXKEEP = N / 2;
+  static constexpr int STAGE_BYTES = MAXKEEP * ROWB;
+  static constexpr int SIG_OFF = STAGE_BYTES;
+  static constexpr int SIG_LINE = N * 8;
+  static constexpr int BOXR = MAXKEEP < 256 ? MAXKEEP : 256;
+  static constexpr int SMEM = GROUPS * REGION + 64 + 1024;
+  static_assert(K::LPC == 4 || K::LPC == 8, "64- or 128-byte stage rows");
+  static_assert(REGION % 1024 == 0, "swizzle atoms need aligned regions");
+  static_assert(SIG_OFF + K::LPC * SIG_LINE <= REGION, "landing zone");
+  static_assert(MAXKEEP % BOXR == 0, "whole boxes inside the stage");
+};
+
+__device__ __forceinline__ void
+group_sync(int g)
+{
+  asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(PF_THREADS) : "memory");
+}
+
+template <int N, int NOISE>
+__global__ void __launch_bounds__(G3Cfg<N>::THREADS, 1)
+kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
+        const __grid_constant__ TileMaps tms)
+{
+  using G = G3Cfg<N>;
+  using K = KCfg<N>;
+  using C = LineCfg<N>;
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* base = align1024(smem_raw);
+  const int g = threadIdx.x / PF_THREADS, tg = threadIdx.x % PF_THREADS;
+  const int lic = tg / C::TPL, t = tg % C::TPL;
+  unsigned char* region = base + g * G::REGION;
+  cplx* stage = reinterpret_cast<cplx*>(region);
+  cplx* xbuf = stage + lic * C::PITCH;
+  const double* srow =
+    reinterpret_cast<const double*>(region + G::SIG_OFF + lic * G::SIG_LINE);
+  const uint32_t bar = smem_u32(base + G::GROUPS * G::REGION) + 8u * g;
+  if (tg == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+  }
+  __syncthreads();
+  const int ntA = (p.A + K::LPC - 1) / K::LPC;
+  const long long ntiles = (long long)ntA * p.B;
+  const uint32_t sig_bytes = (uint32_t)(p.tab_mirror_e ? N / 2 + 2 : N) * 8u;
+  const int a_last = p.a_begin + p.A - 1;
+  const int keep = p.keep;
+  uint32_t ph = 0;
+  bool pending = false;
+  for (long long T = (long long)blockIdx.x * G::GROUPS + g; T < ntiles;
+       T += (long long)gridDim.x * G::GROUPS) {
+    const int at = (int)(T % ntA), b = (int)(T / ntA);
+    const int a0 = p.a_begin + at * K::LPC;
+    // lines beyond A recompute the last valid line; the tensor store clips
+    const int a = min(a0 + lic, a_last);
+    if (tg == 0) {
+      mbar_expect_tx(bar, K::LPC * sig_bytes);
+#pragma unroll
+      for (int l = 0; l < K::LPC; l++)
+        bulk_load(smem_u32(region + G::SIG_OFF + l * G::SIG_LINE),
+                  table_row(p, min(a0 + l, a_last), b), sig_bytes, bar);
+    }
+    cplx v[C::E];
+    gen_noise<N, NOISE>(v, p, a, b, t);
+    mbar_wait(bar, ph);
+    ph ^= 1;
+    scale_noise<N>(v, p, srow, a, b, t);
+    // the previous tile's tensor store must have read the stage before the
+    // exchange buffers (same memory) are written again
+    if (tg == 0 && pending)
+      bulk_wait_read0();
+    group_sync(g);
+    line_fft<N, +1>(v, xbuf, t, tw2);
+    group_sync(g);
+#pragma unroll
+    for (int q = 0; q < C::E; q++) {
+      const int e = t + C::TPL * q;
+      if (e < keep)
+        stage[stage_slot<N>(e, lic)] = v[q];
+    }
+    fence_proxy_async();
+    group_sync(g);
+    if (tg == 0) {
+      for (int r0 = 0; r0 < keep; r0 += G::BOXR)
+        tma_store_3d(&tms.m[0], smem_u32(region) + r0 * G::ROWB,
+                     2 * at * K::LPC, r0, b);
+      bulk_commit();
+      pending = true;
+    }
+  }
+  if (tg == 0 && pending)
+    bulk_wait0();
 }
 
 // ===========================================================================
@@ -483,7 +606,6 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
   long long T = blockIdx.x;
   if (T < ntiles)
     issue(T);
-  double* out = reinterpret_cast<double*>(p.out);
   for (; T < ntiles; T += gridDim.x) {
     const long long L0 = 2 * (T * P::LT + slot), L1 = L0 + 1;
     const bool v0 = L0 < nl, v1 = L1 < nl;
@@ -513,21 +635,7 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
     if (Tn < ntiles)
       issue(Tn);
     line_fft_phase2_compute<N, +1>(v, t, tw2);
-    dispatch_transform(p.transform, [&](auto trc) {
-      constexpr int TR = decltype(trc)::value;
-#pragma unroll
-      for (int q = 0; q < P::E; q++) {
-        const int e = t + P::TPL * q;
-        if (e < p.keep) {
-          if (v0)
-            out[L0 * p.out_pitch + e] =
-              apply_transform_c<TR>(v[q].x * p.scale, p.tparam);
-          if (v1)
-            out[L1 * p.out_pitch + e] =
-              apply_transform_c<TR>(v[q].y * p.scale, p.tparam);
-        }
-      }
-    });
+    store_real_pair<N>(v, p, L0, v0, v1, t);
   }
 }
 

@@ -31,6 +31,12 @@ CASES = [
     dict(cells=[512, 4], covariance="spherical", corr_length=0.2),
     dict(cells=[32, 32, 32], covariance="exponential", corr_length=0.1),
     dict(cells=[2, 2], covariance="exponential", corr_length=0.5),
+    # pass A lines of 512 / 1024: grouped persistent kernel (kp_gen3), ragged
+    # tile counts so that clipped tensor stores are covered
+    dict(cells=[8, 2, 256], covariance="exponential", corr_length=0.1),
+    dict(cells=[4, 1, 512], covariance="spherical", corr_length=0.2),
+    dict(cells=[64, 512], covariance="exponential", corr_length=0.05),
+    dict(cells=[32, 256], covariance="cubic", corr_length=[0.08, 0.03, 0.03, 0.05], anisotropy="geometric", approximate=True),
 ]
 
 
@@ -152,3 +158,23 @@ def test_zero_rhs_returns_copy(m):
     with m.Plan([16, 16]) as p:
         x = p.solve(np.zeros((16, 16)))
         assert np.all(x == 0) and p.cg_iterations_used == 0
+
+
+@pytest.mark.parametrize("case", [CASES[-4], CASES[-3], CASES[-2], dict(cells=[256, 256], covariance="exponential", corr_length=0.1), dict(cells=[16, 16, 512], covariance="spherical", corr_length=0.1)], ids=ids)
+@pytest.mark.parametrize("rng", ["fast", "fp64"])
+def test_grouped_pass_a_equals_plain_kernels(m, case, rng, monkeypatch):
+    """device noise: the grouped persistent pass A (default) and the plain
+    per-tile kernels (PF_PIPE=0) compute the same products in the same order"""
+    monkeypatch.setenv("PF_GEN3", "force")  # small grids: skip the size heuristic
+    with m.Plan(rng_mode=rng, **case) as p:
+        a = [p.generate(seed=7, realization=r) for r in range(3)]
+        noise = np.random.default_rng(2).standard_normal(2 * p.noise_entries)
+        fa = p.generate_from_noise(noise)
+    monkeypatch.delenv("PF_GEN3")
+    monkeypatch.setenv("PF_PIPE", "0")
+    with m.Plan(rng_mode=rng, **case) as p:
+        b = [p.generate(seed=7, realization=r) for r in range(3)]
+        fb = p.generate_from_noise(noise)
+    assert np.array_equal(fa, fb)
+    for x, y in zip(a, b):
+        assert np.isfinite(x).all() and np.array_equal(x, y)
