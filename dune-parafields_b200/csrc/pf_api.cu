@@ -480,6 +480,11 @@ struct pf_plan
   bool eig_valid = false;
   cudaStream_t stream = nullptr;
   cudaStream_t copy_stream = nullptr;
+  // slab exchange by DMA: one stream per destination so that several copy
+  // engines drive NVLink at once (PF_SLAB_STREAMS limits the fan-out)
+  cudaStream_t peer_stream[8] = {};
+  cudaEvent_t ev_gate = nullptr, ev_peer[8] = {};
+  int peer_streams = 0;
   cudaEvent_t ev_done[2] = { nullptr, nullptr }, ev_copied[2] = { nullptr, nullptr };
   unsigned long long launches = 0;
   // optional per-pass timing (CUDA events on the plan's stream)
@@ -490,6 +495,15 @@ struct pf_plan
   pf::CovParams cov{};
   int device = 0;
   int sm_count = 148;
+  // slab mode, kernel exchange (peer stores): pass A of realization r+1 and
+  // the tail (passes B, C) of realization r run CONCURRENTLY on disjoint sets
+  // of SMs -- pass A is NVLink-bound there and leaves SMs idle -- by capping
+  // the grids of the persistent kernels: sm_cap (0 = all SMs) applies to the
+  // launches issued while it is set
+  int sm_cap = 0;
+  int split_a = 0;               // SMs given to pass A (0: no overlap)
+  cudaStream_t tail_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // ---- slab mode (one process per GPU) -------------------------------------
   int nranks = 1, rank = 0;
   long long cl = 1;          // local layers of the last dimension
@@ -911,7 +925,7 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
                                 a.A, 1, a.blk_T, false, &c2t.in));
       tmptr = &c2t;
     }
-    grid = (int)std::min<long long>(ntiles, pl->sm_count);
+    grid = (int)std::min<long long>(ntiles, pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count);
   }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (pl->profiling) {
@@ -1437,19 +1451,30 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
         slab_flags(pl, pl->slab_block, 1), P, e - 2, pl->d_timeout);
       pl->launches++;
     }
-    if (pl->a_count > 0)
-      for (int q = 0, k = 0; q < P; q++) {
-        if (q == pl->rank)
-          continue;
-        const cplx* src =
-          pl->send_stage[s] + (size_t)(k++) * pl->xbuf_elems + xoff;
+    if (pl->a_count > 0) {
+      const int ns = pl->peer_streams;
+      if (ns > 1)
+        PF_CUDA(cudaEventRecord(pl->ev_gate, pl->copy_stream));
+      // destinations in ring order starting behind this rank, so that at any
+      // time the ranks target different peers
+      for (int i = 1; i < P; i++) {
+        const int q = (pl->rank + i) % P;
+        const int k = q < pl->rank ? q : q - 1; // staging slot of peer q
+        const cplx* src = pl->send_stage[s] + (size_t)k * pl->xbuf_elems + xoff;
         cplx* dst = slab_buffer(pl, pl->peer_block[q], s) + xoff;
+        cudaStream_t st = ns > 1 ? pl->peer_stream[i % ns] : pl->copy_stream;
+        if (ns > 1 && i <= ns)
+          PF_CUDA(cudaStreamWaitEvent(st, pl->ev_gate, 0));
         PF_CUDA(cudaMemcpy2DAsync(dst, (size_t)pitch * sizeof(cplx), src,
                                   (size_t)pitch * sizeof(cplx),
                                   (size_t)xwidth * sizeof(cplx),
-                                  (size_t)rows, cudaMemcpyDeviceToDevice,
-                                  pl->copy_stream));
+                                  (size_t)rows, cudaMemcpyDeviceToDevice, st));
       }
+      for (int j = 0; j < ns && ns > 1; j++) {
+        PF_CUDA(cudaEventRecord(pl->ev_peer[j], pl->peer_stream[j]));
+        PF_CUDA(cudaStreamWaitEvent(pl->copy_stream, pl->ev_peer[j], 0));
+      }
+    }
     k_slab_signal<<<1, 32, 0, pl->copy_stream>>>(pl->d_flagsA, P, pl->rank, e);
     pl->launches++;
     PF_CUDA(cudaEventRecord(pl->ev_x[s], pl->copy_stream));
@@ -1802,6 +1827,11 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     }
     pl->slab_block = static_cast<unsigned char*>(blk);
     pl->peer_block[pl->rank] = blk;
+    // measured on B200 (profiles/r01q, r01r): from 4 ranks on, stores to
+    // peer memory straight from pass A, overlapped with the previous tail on
+    // the other SMs, beat the staged DMA exchange; with 2 ranks the DMA
+    // exchange wins
+    pl->slab_dma = pl->nranks < 4;
     if (const char* env = getenv("PF_SLAB_EXCHANGE"))
       pl->slab_dma = strcmp(env, "peer") != 0;
     for (int i = 0; i < 2; i++) {
@@ -1811,6 +1841,30 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     cudaDeviceSynchronize();
   }
   cudaStreamCreateWithFlags(&pl->copy_stream, cudaStreamNonBlocking);
+  if (pl->nranks > 1) {
+    cudaStreamCreateWithFlags(&pl->tail_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&pl->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&pl->ev_join, cudaEventDisableTiming);
+    // default split for the kernel exchange: pass A is NVLink-bound, the tail
+    // HBM-bound; about 55 % of the SMs for pass A balances the two on B200
+    // (the tail needs SM time ~ 1/P, the NVLink-bound pass A a time ~
+    // (P-1)/P^2: about 2/3 of the SMs for pass A at 4 ranks, 4/7 at 8)
+    if (!pl->slab_dma)
+      pl->split_a = (pl->nranks >= 8 ? pl->sm_count * 4 / 7
+                                     : pl->sm_count * 2 / 3) & ~1;
+    if (const char* env = getenv("PF_SLAB_SPLIT"))
+      pl->split_a = std::max(0, std::min(pl->sm_count - 8, atoi(env)));
+    pl->peer_streams = pl->nranks - 1;
+    if (const char* env = getenv("PF_SLAB_STREAMS"))
+      pl->peer_streams = std::max(1, std::min(pl->nranks - 1, atoi(env)));
+    if (pl->peer_streams > 1) {
+      cudaEventCreateWithFlags(&pl->ev_gate, cudaEventDisableTiming);
+      for (int i = 0; i < pl->peer_streams; i++) {
+        cudaStreamCreateWithFlags(&pl->peer_stream[i], cudaStreamNonBlocking);
+        cudaEventCreateWithFlags(&pl->ev_peer[i], cudaEventDisableTiming);
+      }
+    }
+  }
   for (int i = 0; i < 2; i++) {
     cudaEventCreateWithFlags(&pl->ev_done[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&pl->ev_copied[i], cudaEventDisableTiming);
@@ -1857,6 +1911,20 @@ pf_plan_destroy(pf_plan* pl)
     cudaFree(pl->d_timeout);
   if (pl->copy_stream)
     cudaStreamDestroy(pl->copy_stream);
+  if (pl->tail_stream)
+    cudaStreamDestroy(pl->tail_stream);
+  if (pl->ev_fork)
+    cudaEventDestroy(pl->ev_fork);
+  if (pl->ev_join)
+    cudaEventDestroy(pl->ev_join);
+  for (int i = 0; i < 8; i++) {
+    if (pl->peer_stream[i])
+      cudaStreamDestroy(pl->peer_stream[i]);
+    if (pl->ev_peer[i])
+      cudaEventDestroy(pl->ev_peer[i]);
+  }
+  if (pl->ev_gate)
+    cudaEventDestroy(pl->ev_gate);
   for (int i = 0; i < 2; i++) {
     if (pl->ev_done[i])
       cudaEventDestroy(pl->ev_done[i]);
@@ -2106,14 +2174,39 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
     // of realization r+1 is issued before the tail of realization r, so the
     // NVLink transfer overlaps compute
     unsigned long long e_prev = 0, e = 0;
+    // kernel exchange with an SM split: pass A stays on the plan's stream,
+    // the tails go to a second stream and both run on their share of the SMs
+    const bool split = pl->split_a > 0 && !pl->slab_dma && count > 1;
+    cudaStream_t main_stream = pl->stream;
+    if (split) {
+      PF_CUDA(cudaEventRecord(pl->ev_fork, main_stream));
+      PF_CUDA(cudaStreamWaitEvent(pl->tail_stream, pl->ev_fork, 0));
+    }
+    auto tail = [&](unsigned long long ep, double* o) -> int {
+      if (split) {
+        pl->stream = pl->tail_stream;
+        pl->sm_cap = pl->sm_count - pl->split_a;
+      }
+      const int rc = slab_issue_tail(pl, ep, o, tr);
+      pl->stream = main_stream;
+      pl->sm_cap = 0;
+      return rc;
+    };
     for (size_t r = 0; r < count; r++) {
-      PF_TRY(slab_issue_a(pl, nk, seed, first + r, nullptr, &e));
+      pl->sm_cap = split ? pl->split_a : 0;
+      const int rc = slab_issue_a(pl, nk, seed, first + r, nullptr, &e);
+      pl->sm_cap = 0;
+      PF_TRY(rc);
       if (r > 0)
-        PF_TRY(slab_issue_tail(pl, e_prev, out + (r - 1) * pl->Dl, tr));
+        PF_TRY(tail(e_prev, out + (r - 1) * pl->Dl));
       e_prev = e;
     }
     if (count > 0)
-      PF_TRY(slab_issue_tail(pl, e_prev, out + (count - 1) * pl->Dl, tr));
+      PF_TRY(tail(e_prev, out + (count - 1) * pl->Dl));
+    if (split) {
+      PF_CUDA(cudaEventRecord(pl->ev_join, pl->tail_stream));
+      PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_join, 0));
+    }
     return 0;
   }
   if (dev) {
