@@ -102,6 +102,17 @@ bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
+// same with an L2 evict-last hint: rows that a mirrored line reads again soon
+__device__ __forceinline__ void
+bulk_load_keep(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes"
+               ".L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+               : "memory");
+}
 // shared -> global tensor store of one box at (c0, c1, c2)
 __device__ __forceinline__ void
 tma_store_3d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2)
@@ -450,8 +461,8 @@ kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
       mbar_expect_tx(bar, K::LPC * sig_bytes);
 #pragma unroll
       for (int l = 0; l < K::LPC; l++)
-        bulk_load(smem_u32(region + G::SIG_OFF + l * G::SIG_LINE),
-                  table_row(p, min(a0 + l, a_last), b), sig_bytes, bar);
+        bulk_load_keep(smem_u32(region + G::SIG_OFF + l * G::SIG_LINE),
+                       table_row(p, min(a0 + l, a_last), b), sig_bytes, bar);
     }
     cplx v[C::E];
     gen_noise<N, NOISE>(v, p, a, b, t);
