@@ -44,6 +44,7 @@ WORKLOADS = {
     # SURVEY.md 8(d) synthetic inputs
     "K3": dict(cells=[512, 512, 512], covariance="spherical", corr_length=0.1, label="3D 512^3 spherical l=0.1, factor 2 (1024^3 fp64 torus)"),
     "K2": dict(cells=[256, 256, 256], covariance="gaussian", corr_length=[0.05, 0.03, 0.02], anisotropy="axiparallel", transform="logNormal", approximate=True, label="3D 256^3 gaussian axiparallel + logNormal (512^3 torus)"),
+    "K4": dict(cells=[8192, 8192], covariance="cubic", corr_length=[0.08, 0.03, 0.03, 0.05], anisotropy="geometric", approximate=True, label="2D 8192^2 cubic, geometric anisotropy (16384^2 torus, four-step lines)"),
     "K1": dict(cells=[512, 512], covariance="exponential", corr_length=0.05, label="2D 512^2 exponential l=0.05 (1024^2 torus)"),
     "K5": dict(cells=[256, 256, 256], covariance="exponential", corr_length=0.05, label="3D 256^3 exponential (512^3 torus)"),
     "S3": dict(cells=[128, 128, 128], covariance="spherical", corr_length=0.1, label="3D 128^3 spherical (256^3 torus)"),

@@ -377,6 +377,7 @@ k_uncorrelated(size_t n, unsigned long long seed, unsigned long long q0,
 } // namespace
 
 #include "pf_rng.cuh"
+#include "pf_long.cuh"
 
 namespace {
 
@@ -466,6 +467,12 @@ struct pf_plan
   double* sig = nullptr;
   double* inv = nullptr;
   std::map<long long, cplx*> tw; // twiddle tables per line length
+  // 2D plans with an axis longer than 1024 (pf_long.cuh): n[i] = LN1[i] * LN2[i]
+  bool long2d = false;
+  long long LN1[2] = { 1, 1 }, LN2[2] = { 1, 1 };
+  long long mcols = 0;            // columns of Z: LN1[0] * (LN2[0]/2 + 1)
+  std::map<long long, cplx*> twl; // exp(-2 pi i m / n) per long line length
+  cplx *LY = nullptr, *LU = nullptr; // step buffers of the long passes
   cplx* Y = nullptr;
   cplx* Z = nullptr;
   cplx* V = nullptr;
@@ -573,6 +580,8 @@ free_sized(pf_plan* pl)
   dev_free(&pl->Y);
   dev_free(&pl->Z);
   dev_free(&pl->V);
+  dev_free(&pl->LY);
+  dev_free(&pl->LU);
   dev_free(&pl->spare);
   pl->spare_valid = false;
   pl->eig_valid = false;
@@ -598,11 +607,15 @@ plan_resize(pf_plan* pl)
   for (int i = 0; i < pl->dim; i++) {
     pl->c[i] = d.cells[i];
     pl->n[i] = (long long)pl->factor * d.cells[i];
-    if (!supported_n(pl->n[i]))
+    const bool long_ok = pl->dim == 2 && pl->nranks <= 1 &&
+                         pl->n[i] > 1024 && pl->n[i] <= 16384 &&
+                         (pl->n[i] & (pl->n[i] - 1)) == 0;
+    if (!supported_n(pl->n[i]) && !long_ok)
       return fail(PF_ERR_INVALID,
                   "unsupported extended size " + std::to_string(pl->n[i]) +
                     " in dimension " + std::to_string(i) +
-                    " (this build supports powers of two, 2..1024)");
+                    " (this build supports powers of two, 2..1024, and up to "
+                    "16384 for single-GPU 2D fields)");
     pl->D *= pl->c[i];
     pl->Next *= pl->n[i];
   }
@@ -610,6 +623,17 @@ plan_resize(pf_plan* pl)
   pl->compact = pl->dim > 1 && d.anisotropy != PF_ANISO_GEOMETRIC;
   pl->m0 = pl->hermitian ? pl->n[0] / 2 + 1 : pl->n[0];
   pl->m0p = (pl->m0 + 7) / 8 * 8;
+  pl->long2d = false;
+  if (pl->dim == 2 && (pl->n[0] > 1024 || pl->n[1] > 1024)) {
+    pl->long2d = true;
+    for (int i = 0; i < 2; i++) {
+      pl->LN2[i] = std::min<long long>(pl->n[i], 1024);
+      pl->LN1[i] = pl->n[i] / pl->LN2[i];
+    }
+    // Z columns in the permuted order of the long c2r axis (pf_long.cuh)
+    pl->mcols = pl->LN1[0] * (pl->LN2[0] / 2 + 1);
+    pl->m0p = (pl->mcols + 7) / 8 * 8;
+  }
   if (pl->dim == 3) {
     pl->rows = (pl->compact ? pl->n[1] / 2 + 1 : pl->n[1]) * pl->m0;
     pl->P = pl->compact ? pl->n[2] / 2 + 1 : pl->n[2];
@@ -975,6 +999,145 @@ blank_args()
 }
 
 // ---------------------------------------------------------------------------
+// long lines (2D, n up to 16384): host side of pf_long.cuh
+// ---------------------------------------------------------------------------
+int
+long_twiddles(pf_plan* pl, long long n, const cplx** out)
+{
+  auto it = pl->twl.find(n);
+  if (it != pl->twl.end()) {
+    *out = it->second;
+    return 0;
+  }
+  cplx* d = nullptr;
+  PF_TRY(dev_alloc(&d, (size_t)n));
+  pf::k_long_twiddles<<<(unsigned)((n + 255) / 256), 256, 0, pl->stream>>>(d, n);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  pl->twl[n] = d;
+  *out = d;
+  return 0;
+}
+
+template <int SRC, int DIR>
+int
+launch_long1(pf_plan* pl, int N1, const pf::LongArgs& g, const PassArgs& p,
+             long long lines)
+{
+  const dim3 grid((unsigned)((g.N2 + 255) / 256), (unsigned)lines);
+  switch (N1) {
+    case 1:
+      pf::k_long1<1, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      break;
+    case 2:
+      pf::k_long1<2, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      break;
+    case 4:
+      pf::k_long1<4, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      break;
+    case 8:
+      pf::k_long1<8, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      break;
+    case 16:
+      pf::k_long1<16, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      break;
+    default:
+      return fail(PF_ERR_INVALID, "long line: unsupported split");
+  }
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return 0;
+}
+
+// forward FFT of `lines` contiguous lines of n = N1*N2 complex numbers:
+// step 1 (covariance evaluation or complex input) into Y, step 2 = k_c2t with
+// (a = j1, b = line), whose tile store interleaves the sub-lines back into
+// natural order: out[line*out_pitch + j1 + N1*e], e < keep
+int
+long_fft_forward(pf_plan* pl, int axis, bool from_cov, const cplx* in,
+                 long long in_pitch, long long lines, cplx* Y, cplx* out,
+                 long long out_pitch, long long keep)
+{
+  const long long n = pl->n[axis];
+  const int N1 = (int)pl->LN1[axis], N2 = (int)pl->LN2[axis];
+  pf::LongArgs g;
+  memset(&g, 0, sizeof(g));
+  g.N2 = N2;
+  g.n = n;
+  PF_TRY(long_twiddles(pl, n, &g.tw));
+  g.in = in;
+  g.in_pitch = in_pitch;
+  g.out = Y;
+  PassArgs p = blank_args();
+  p.cov = pl->cov;
+  if (from_cov)
+    PF_TRY((launch_long1<pf::LSRC_COV, -1>(pl, N1, g, p, lines)));
+  else
+    PF_TRY((launch_long1<pf::LSRC_CPLX, -1>(pl, N1, g, p, lines)));
+  PassArgs a = blank_args();
+  a.A = N1;
+  a.B = (int)lines;
+  a.in = Y;
+  a.isa = N2;
+  a.isb = n;
+  a.n_valid = N2;
+  a.out = out;
+  a.osb = out_pitch;
+  a.ose = N1;
+  a.keep = (int)keep;
+  return run_pass(pl, N2, pf::K_C2T_FWD, a);
+}
+
+// eigenvalues of a 2D plan with long lines: full complex transforms (one-time
+// cost), axis 0 first, transpose, axis 1, then real part / N with the census
+int
+eigen_long2d(pf_plan* pl)
+{
+  const long long* n = pl->n;
+  const long long m0 = pl->m0;
+  const double invN = 1.0 / (double)pl->Next;
+  // k0 <= n0/2 needs sub-line outputs e <= N2/2 (a few columns more than m0)
+  const long long keep0 = pl->LN2[0] / 2 + 1;
+  const long long w0 = pl->LN1[0] * keep0; // >= m0 columns per row
+  cplx *Y = nullptr, *C1 = nullptr, *C1T = nullptr, *C2 = nullptr;
+  const unsigned saved_mask = pl->pipe_mask;
+  pl->pipe_mask = 0; // one-time work: plain kernels
+  int rc = dev_alloc(&Y, (size_t)n[0] * n[1]);
+  if (rc == 0)
+    rc = dev_alloc(&C1, (size_t)n[1] * w0);
+  if (rc == 0) // axis 0: lines x1, covariance evaluated in step 1
+    rc = long_fft_forward(pl, 0, true, nullptr, 0, n[1], Y, C1, w0, keep0);
+  if (rc == 0)
+    rc = dev_alloc(&C1T, (size_t)m0 * n[1]);
+  if (rc == 0) {
+    const dim3 grid((unsigned)((m0 + 31) / 32), (unsigned)((n[1] + 31) / 32));
+    pf::k_long_transpose<<<grid, dim3(32, 8), 0, pl->stream>>>(C1, w0, C1T, n[1],
+                                                             n[1], m0);
+    rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "transpose");
+    pl->launches++;
+  }
+  if (rc == 0)
+    rc = dev_alloc(&C2, (size_t)m0 * n[1]);
+  if (rc == 0) // axis 1: lines k0
+    rc = long_fft_forward(pl, 1, false, C1T, n[1], m0, Y, C2, n[1], pl->LN2[1]);
+  if (rc == 0) {
+    const long long total = m0 * pl->P;
+    pf::k_long_lambda<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
+      C2, n[1], pl->lam, m0, pl->P, invN, pl->d.threshold, pl->census,
+      pl->census + 3);
+    rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "lambda");
+    pl->launches++;
+  }
+  pl->pipe_mask = saved_mask;
+  cudaStreamSynchronize(pl->stream);
+  cudaFree(Y);
+  cudaFree(C1);
+  cudaFree(C1T);
+  cudaFree(C2);
+  return rc;
+}
+
+// ---------------------------------------------------------------------------
 // eigenvalues: Matrix::fillTransformedMatrix, matrix.hh:232-331
 // ---------------------------------------------------------------------------
 int
@@ -1003,6 +1166,8 @@ eigen_once(pf_plan* pl)
     a.smallest_bits = pl->census + 3;
     a.threshold = pl->d.threshold;
     PF_TRY(run_pass(pl, n[0], pf::K_LAMBDA_COV, a));
+  } else if (pl->dim == 2 && pl->long2d) {
+    PF_TRY(eigen_long2d(pl));
   } else if (pl->dim == 2) {
     cplx* U = nullptr;
     PF_TRY(dev_alloc(&U, (size_t)m0 * n[1]));
@@ -1235,6 +1400,106 @@ inverse_tail(pf_plan* pl, const cplx* Yin, long long layers, double* out_dev,
   return 0;
 }
 
+// generateField for a 2D plan with long lines (pf_long.cuh); `a` carries the
+// noise source, keys and sigma table as prepared by generate_dev
+int
+generate_long2d(pf_plan* pl, PassArgs a, double* out_dev, int transform)
+{
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  const int N1a = (int)pl->LN1[1], N2a = (int)pl->LN2[1]; // pass A axis (k1)
+  const int N1c = (int)pl->LN1[0], N2c = (int)pl->LN2[0]; // c2r axis (k0)
+  PF_TRY(dev_alloc(&pl->LY, (size_t)pl->mcols * n[1]));
+  // ---- pass A, step 1: noise * sigma -> DFT over k1 -> twiddle -> Y --------
+  a.cma = 1; // counter / injected index of (k0, e): k0 + m0 * e
+  a.cmb = 0;
+  a.cme = m0;
+  a.ima = 1;
+  a.imb = 0;
+  a.ime = m0;
+  a.na_self = (int)n[0];
+  a.nb_self = 1;
+  a.plane_axis = 0;
+  pf::LongArgs g;
+  memset(&g, 0, sizeof(g));
+  g.N2 = N2a;
+  g.n = n[1];
+  g.n_half = n[1] / 2;
+  PF_TRY(long_twiddles(pl, n[1], &g.tw));
+  g.perm_n1 = N1c;
+  g.perm_m = N2c / 2 + 1;
+  g.k0_max = n[0] / 2;
+  g.out = pl->LY;
+  if (a.noise_kind == pf::NOISE_PHILOX_FAST)
+    PF_TRY((launch_long1<pf::LSRC_NOISE_FAST, +1>(pl, N1a, g, a, pl->mcols)));
+  else if (a.noise_kind == pf::NOISE_PHILOX_F64)
+    PF_TRY((launch_long1<pf::LSRC_NOISE_F64, +1>(pl, N1a, g, a, pl->mcols)));
+  else
+    PF_TRY((launch_long1<pf::LSRC_NOISE_INJECTED, +1>(pl, N1a, g, a, pl->mcols)));
+  // ---- pass A, step 2: sub-lines (a = column, b = j1) -> Z[x1][column],
+  //      x1 = j1 + N1a * e, restricted to x1 < c1 -----------------------------
+  PassArgs b = blank_args();
+  b.A = (int)pl->mcols;
+  b.B = N1a;
+  b.in = pl->LY;
+  b.isa = n[1];
+  b.isb = N2a;
+  b.n_valid = N2a;
+  b.out = pl->Z;
+  b.osb = pl->m0p;
+  b.ose = (long long)N1a * pl->m0p;
+  b.keep = (int)((c[1] + N1a - 1) / N1a);
+  PF_TRY(run_pass(pl, N2a, pf::K_C2T_INV, b));
+  // ---- pass C ---------------------------------------------------------------
+  if (N1c == 1) {
+    PassArgs cc = blank_args(); // natural column order: the short-line kernel
+    cc.A = (int)c[1];
+    cc.B = 1;
+    cc.in = pl->Z;
+    cc.isa = pl->m0p;
+    cc.out = out_dev;
+    cc.out_pitch = c[0];
+    cc.keep = (int)c[0];
+    cc.transform = transform;
+    cc.tparam = pl->d.boxcox_lambda;
+    return run_pass(pl, n[0], pf::K_C2R, cc);
+  }
+  const long long pairs = (c[1] + 1) / 2;
+  PF_TRY(dev_alloc(&pl->LU, (size_t)pairs * n[0]));
+  PassArgs u = blank_args();
+  u.A = N1c;
+  u.B = (int)pairs;
+  u.in = pl->Z;
+  u.isa = pl->m0p;
+  u.n_valid = (int)c[1];
+  u.out = pl->LU;
+  u.long_n1 = N1c;
+  PF_TRY(long_twiddles(pl, n[0], &u.long_tw));
+  PF_TRY(run_pass(pl, N2c, pf::K_LONG_C2R1, u));
+  const dim3 grid((unsigned)((N2c + 255) / 256), (unsigned)pairs);
+  const double tp = pl->d.boxcox_lambda;
+  switch (N1c) {
+    case 2:
+      pf::k_long_c2r2<2><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+      break;
+    case 4:
+      pf::k_long_c2r2<4><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+      break;
+    case 8:
+      pf::k_long_c2r2<8><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+      break;
+    case 16:
+      pf::k_long_c2r2<16><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+      break;
+    default:
+      return fail(PF_ERR_INVALID, "long line: unsupported split");
+  }
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return 0;
+}
+
 int
 generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
                   unsigned long long realization, const double2* noise_dev,
@@ -1281,6 +1546,8 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.keep = (int)c[2];
     PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
     PF_TRY(inverse_tail(pl, pl->Y, c[2], out_dev, transform));
+  } else if (pl->dim == 2 && pl->long2d) {
+    PF_TRY(generate_long2d(pl, a, out_dev, transform));
   } else if (pl->dim == 2) {
     a.A = (int)m0; // a = k0, e = k1
     a.B = 1;
@@ -1520,6 +1787,10 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
 int
 apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
 {
+  if (pl->long2d)
+    return fail(PF_ERR_INVALID,
+                "covariance operators need extended sizes <= 1024 in this "
+                "build (sampling supports up to 16384 in 2D)");
   double** tabp = op == PF_OP_MATRIX ? &pl->lam
                   : op == PF_OP_ROOT ? &pl->sig
                                      : &pl->inv;
@@ -1883,6 +2154,8 @@ pf_plan_destroy(pf_plan* pl)
   prof_collect(pl);
   free_sized(pl);
   for (auto& kv : pl->tw)
+    cudaFree(kv.second);
+  for (auto& kv : pl->twl)
     cudaFree(kv.second);
   dev_free(&pl->dev_io[0]);
   dev_free(&pl->dev_io[1]);

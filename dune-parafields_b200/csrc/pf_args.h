@@ -49,6 +49,7 @@ enum
   K_LAMBDA_COV = 8, // covariance eval (1D) -> fwd FFT -> eigenvalues
   K_SPEC_TILE = 9,  // contiguous -> fwd FFT * g(lambda) inv FFT -> tile (F2+A)
   K_SPEC_REIM = 10, // real line (1D) -> fwd * g inv -> real line
+  K_LONG_C2R1 = 11, // long c2r axis, step 1: permuted half spectra -> sub-FFT
   K_GEN3 = 16       // pass A, grouped persistent form (pipe launcher only)
 };
 
@@ -128,6 +129,10 @@ struct PassArgs
   // ---- covariance evaluation ------------------------------------------------
   CovParams cov;
   int cov_axis_a, cov_axis_b; // torus axis indexed by a / b (-1: none)
+
+  // ---- long lines (n = long_n1 * N > 1024, 2D): see pf_long in pf_api.cu -----
+  int long_n1;             // sub-transforms per long line
+  const double2* long_tw;  // exp(-2 pi i m / n), m < n
 
   // ---- eigenvalue census (matrix.hh:283-306) --------------------------------
   unsigned long long* census; // [small, zero, negative]

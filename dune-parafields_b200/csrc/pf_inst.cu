@@ -99,6 +99,11 @@ extern "C" int PF_CAT(pf_launch_n, PF_N)(int kind, const PassArgs* ap,
       e = launch(k_spec<N, false>, a, tw2, ntA * a.B, K::smem_tile(a.keep),
                  st);
       break;
+    case K_LONG_C2R1: {
+      const long long nt = (a.long_n1 + K::LPC - 1) / K::LPC;
+      e = launch(k_long_c2r1<N>, a, tw2, nt * a.B, K::exch_bytes, st);
+      break;
+    }
     case K_SPEC_REIM:
       e = launch(k_spec<N, true>, a, tw2, ntA * a.B, K::exch_bytes, st);
       break;

@@ -702,6 +702,64 @@ k_c2r(const PassArgs p, const cplx* __restrict__ tw2)
   store_real_pair<N>(v, p, L0, v0, v1, t);
 }
 
+// Long c2r axis (n0 = N1 * N > 1024), step 1 of 2.  The half-spectrum rows
+// arrive PERMUTED: column k1 * (N/2+1) + k2 holds k0 = k1 + N1 * k2 (pass A
+// writes them that way), so that sub-transform k1 -- the N-point inverse FFT
+// over k2' of V[k1 + N1 k2'], V = A + iB Hermitian-extended as in k_c2r --
+// reads two contiguous rows: k1 forwards and its mirror N1 - k1 backwards.
+// Output U[pair][k1][j2] * W_n0^{+ j2 k1}; step 2 (k_long_c2r2, pf_api.cu)
+// finishes with an N1-point transform over k1.
+// Lines: a = k1 < A = N1, b = pair; p.n_valid = number of real lines.
+template <int N>
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_long_c2r1(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using K = KCfg<N>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int lic = threadIdx.x / K::TPL, t = threadIdx.x % K::TPL;
+  constexpr int M = N / 2 + 1;
+  const int N1 = p.long_n1;
+  const int ntA = (N1 + K::LPC - 1) / K::LPC;
+  const int at = blockIdx.x % ntA, b = blockIdx.x / ntA;
+  const int k1 = at * K::LPC + lic;
+  const bool valid = k1 < N1;
+  const long long L0 = 2ll * b, L1 = L0 + 1;
+  const bool v0 = valid && L0 < p.n_valid, v1 = valid && L1 < p.n_valid;
+  const cplx* in = reinterpret_cast<const cplx*>(p.in);
+  const int kr = valid ? (N1 - k1) % N1 : 0;
+  const cplx* a_dir = in + L0 * p.isa + (long long)(valid ? k1 : 0) * M;
+  const cplx* a_mir = in + L0 * p.isa + (long long)kr * M;
+  const cplx* b_dir = a_dir + p.isa;
+  const cplx* b_mir = a_mir + p.isa;
+  cplx v[K::E];
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int e = t + K::TPL * q;
+    const bool direct = (2 * e < N) || (k1 == 0 && 2 * e == N);
+    const int col = direct ? e : (k1 == 0 ? N - e : N - 1 - e);
+    const cplx xa = v0 ? __ldg((direct ? a_dir : a_mir) + col)
+                       : make_double2(0., 0.);
+    const cplx xb = v1 ? __ldg((direct ? b_dir : b_mir) + col)
+                       : make_double2(0., 0.);
+    if (k1 == 0 && (e == 0 || 2 * e == N))
+      v[q] = make_double2(xa.x, xb.x);
+    else if (direct)
+      v[q] = make_double2(xa.x - xb.y, xa.y + xb.x);
+    else
+      v[q] = make_double2(xa.x + xb.y, xb.x - xa.y);
+  }
+  line_fft<N, +1>(v, sm + lic * K::C::PITCH, t, tw2);
+  if (!valid)
+    return;
+  cplx* out = reinterpret_cast<cplx*>(p.out) + ((long long)b * N1 + k1) * N;
+#pragma unroll
+  for (int q = 0; q < K::E; q++) {
+    const int j2 = t + K::TPL * q;
+    out[j2] = cmulc(v[q], __ldg(p.long_tw + (long long)j2 * k1));
+  }
+}
+
 // F0 / E0: two real lines (loaded or covariance-evaluated) -> one complex
 // forward FFT -> split into the two half spectra -> tile store.
 // Lines a (tile axis, pairs a, a+1), b; element e = x0.

@@ -1,0 +1,81 @@
+"""GPU parity for 2D fields whose extended size exceeds the 1024-point warp
+FFT (pf_long.cuh, the route BASELINE.json's K4 -- 16384^2 torus -- takes):
+eigenvalues and fields from the reference noise stream against the CPU oracle,
+1e-10 relative to the max norm (fp64)."""
+import numpy as np
+import pytest
+
+from oracle import oracle_lib as ol
+from util import pfb, rel
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+GEO = dict(covariance="cubic", corr_length=[0.08, 0.03, 0.03, 0.05], anisotropy="geometric", approximate=True)
+CASES = [
+    # long c2r axis only (n0 = 2048), short pass-A axis
+    dict(cells=[1024, 8], covariance="exponential", corr_length=0.05),
+    # long pass-A axis only (n1 = 4096)
+    dict(cells=[8, 2048], covariance="exponential", corr_length=0.05),
+    # both long, different splits
+    dict(cells=[2048, 1024], covariance="exponential", corr_length=0.05),
+    # K4's matrix backend (geometric anisotropy: half-spectrum table), scaled down
+    dict(cells=[1024, 1024], **GEO),
+    # the longest lines: 16384 on either axis
+    dict(cells=[8192, 4], covariance="spherical", corr_length=0.1),
+    dict(cells=[4, 8192], covariance="matern32", corr_length=0.02),
+    dict(cells=[4096, 16], **GEO),
+]
+
+
+def ids(c):
+    return "x".join(map(str, c["cells"])) + "-" + c["covariance"] + "-" + c.get("anisotropy", "none")
+
+
+@pytest.fixture(scope="module")
+def m():
+    return pfb()
+
+
+@pytest.mark.parametrize("case", CASES, ids=ids)
+def test_long_eigenvalues_and_field(m, case):
+    o = ol.Oracle(**case)
+    lam_o = o.lambda_natural().ravel()
+    noise = o.reference_noise(20240611)
+    f_o = o.generate_from_noise(noise)
+    with m.Plan(**case) as p:
+        st = p.compute_eigenvalues()
+        lam = p.eigenvalues(m.LAMBDA_NATURAL)
+        assert lam.shape == lam_o.shape
+        assert rel(lam, lam_o) < TOL
+        assert st["negative"] == o.stats["negative"] or case.get("approximate")
+        assert rel(p.eigenvalues(m.LAMBDA_REFERENCE), o.lambda_stored()) < TOL
+        assert p.noise_entries == o.noise_entries
+        f = p.generate_from_noise(noise)
+        assert f.shape == f_o.shape
+        assert rel(f, f_o) < TOL
+
+
+def test_long_device_noise_statistics(m):
+    # device Philox path: finite, reproducible, unit-ish variance for a short
+    # correlation length, fused value transform consistent with the raw field
+    case = dict(cells=[2048, 1024], covariance="exponential", corr_length=0.01, transform="logNormal")
+    with m.Plan(**case) as p:
+        a = p.generate(seed=3, realization=1)
+        b = p.generate(seed=3, realization=1)
+        c = p.generate(seed=3, realization=2)
+        t = p.generate(seed=3, realization=1, apply_transform=True)
+    assert np.isfinite(a).all() and np.array_equal(a, b) and not np.array_equal(a, c)
+    assert abs(a.var() - 1.0) < 0.05 and abs(a.mean()) < 0.05
+    assert rel(t, np.exp(a)) < 1e-13
+
+
+def test_long_operators_fail_loudly(m):
+    with m.Plan([1024, 8], covariance="exponential", corr_length=0.05) as p:
+        with pytest.raises(m.PfError, match="covariance operators need extended sizes"):
+            p.apply("matrix", np.zeros((8, 1024)))
+
+
+def test_long_3d_unsupported(m):
+    with pytest.raises(m.PfError, match="unsupported extended size"):
+        m.Plan([1024, 4, 4], covariance="exponential", corr_length=0.05)
