@@ -471,7 +471,7 @@ struct pf_plan
   bool long2d = false;
   long long LN1[2] = { 1, 1 }, LN2[2] = { 1, 1 };
   long long mcols = 0;            // columns of Z: LN1[0] * (LN2[0]/2 + 1)
-  std::map<long long, cplx*> twl; // exp(-2 pi i m / n) per long line length
+  std::map<long long, cplx*> twl; // [a][b] = exp(-2 pi i a b / n) per long line length
   cplx *LY = nullptr, *LU = nullptr; // step buffers of the long passes
   cplx* Y = nullptr;
   cplx* Z = nullptr;
@@ -1011,7 +1011,8 @@ long_twiddles(pf_plan* pl, long long n, const cplx** out)
   }
   cplx* d = nullptr;
   PF_TRY(dev_alloc(&d, (size_t)n));
-  pf::k_long_twiddles<<<(unsigned)((n + 255) / 256), 256, 0, pl->stream>>>(d, n);
+  pf::k_long_twiddles<<<(unsigned)((n + 255) / 256), 256, 0, pl->stream>>>(
+    d, n, (int)std::min<long long>(n, 1024));
   PF_CUDA(cudaGetLastError());
   pl->launches++;
   pl->twl[n] = d;

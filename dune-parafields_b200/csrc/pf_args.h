@@ -132,7 +132,7 @@ struct PassArgs
 
   // ---- long lines (n = long_n1 * N > 1024, 2D): see pf_long in pf_api.cu -----
   int long_n1;             // sub-transforms per long line
-  const double2* long_tw;  // exp(-2 pi i m / n), m < n
+  const double2* long_tw;  // [k1][j2] = exp(-2 pi i k1 j2 / n)
 
   // ---- eigenvalue census (matrix.hh:283-306) --------------------------------
   unsigned long long* census; // [small, zero, negative]

@@ -756,7 +756,7 @@ k_long_c2r1(const PassArgs p, const cplx* __restrict__ tw2)
 #pragma unroll
   for (int q = 0; q < K::E; q++) {
     const int j2 = t + K::TPL * q;
-    out[j2] = cmulc(v[q], __ldg(p.long_tw + (long long)j2 * k1));
+    out[j2] = cmulc(v[q], __ldg(p.long_tw + (long long)k1 * N + j2));
   }
 }
 

@@ -27,7 +27,7 @@ struct LongArgs
 {
   int N2;            // sub-line length (<= 1024)
   long long n;       // N1 * N2
-  const cplx* tw;    // exp(-2 pi i m / n), m < n
+  const cplx* tw;    // [j1][k2] = exp(-2 pi i j1 k2 / n), j1 < N1, k2 < N2
   // noise source: output column a' = k1_0 * perm_m + k2_0 stands for
   // k0 = k1_0 + perm_n1 * k2_0 (identity when perm_n1 == 1)
   int perm_n1, perm_m;
@@ -132,7 +132,7 @@ k_long1(const LongArgs g, const PassArgs p)
       Dft<N1, DIR, 1>::run(v);
 #pragma unroll
       for (int j = 0; j < N1; j++) {
-        const cplx w = __ldg(g.tw + (long long)j * k2);
+        const cplx w = __ldg(g.tw + (long long)j * N2 + k2);
         out[(long long)j * N2 + k2] = DIR < 0 ? cmul(v[j], w) : cmulc(v[j], w);
       }
     } else {
@@ -154,7 +154,7 @@ k_long1(const LongArgs g, const PassArgs p)
     Dft<N1, DIR, 1>::run(v);
 #pragma unroll
     for (int j = 0; j < N1; j++) {
-      const cplx w = __ldg(g.tw + (long long)j * k2);
+      const cplx w = __ldg(g.tw + (long long)j * N2 + k2);
       out[(long long)j * N2 + k2] =
         j == 0 ? v[0] : (DIR < 0 ? cmul(v[j], w) : cmulc(v[j], w));
     }
@@ -261,15 +261,17 @@ k_long_lambda(const cplx* __restrict__ C, long long c_pitch, double* __restrict_
   }
 }
 
-// exp(-2 pi i m / n)
+// tw[a * N2 + b] = exp(-2 pi i a b / n), a < N1, b < N2: the inter-step
+// twiddles laid out so that consecutive threads read consecutive entries
 __global__ void
-k_long_twiddles(cplx* __restrict__ tw, long long n)
+k_long_twiddles(cplx* __restrict__ tw, long long n, int N2)
 {
-  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (m < n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const long long a = i / N2, b = i % N2;
     double s, c;
-    sincospi(-2.0 * (double)m / (double)n, &s, &c);
-    tw[m] = make_double2(c, s);
+    sincospi(-2.0 * (double)(a * b) / (double)n, &s, &c);
+    tw[i] = make_double2(c, s);
   }
 }
 
