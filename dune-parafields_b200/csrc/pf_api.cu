@@ -436,6 +436,44 @@ k_slab_wait(const unsigned long long* mine, int n, unsigned long long epoch,
   }
 }
 
+// cross-rank combination of one scalar (CG dot products, norms): thread i
+// publishes this rank's value in slot [seq & 1][me] of rank i, then waits for
+// rank i's value here; thread 0 combines the n values in rank order, so every
+// rank gets the same bits.  Slots live behind the flag arrays (16 u64 in).
+__global__ void
+k_slab_reduce(unsigned long long* const* flags, unsigned long long* mine, int n,
+              int me, unsigned long long seq, int mode, double* value,
+              int* timeout_flag)
+{
+  __shared__ double vals[8];
+  const int i = threadIdx.x;
+  const int par = (int)(seq & 1);
+  if (i < n) {
+    volatile unsigned long long* slot = flags[i] + 16 + 2 * (par * 8 + me);
+    slot[1] = (unsigned long long)__double_as_longlong(*value);
+    __threadfence_system();
+    slot[0] = seq;
+    __threadfence_system();
+    const volatile unsigned long long* in = mine + 16 + 2 * (par * 8 + i);
+    const long long t0 = clock64();
+    while (in[0] < seq) {
+      if (clock64() - t0 > 8000000000ll) {
+        *timeout_flag = 1;
+        break;
+      }
+    }
+    __threadfence_system();
+    vals[i] = __longlong_as_double((long long)in[1]);
+  }
+  __syncthreads();
+  if (i == 0) {
+    double r = vals[0];
+    for (int q = 1; q < n; q++)
+      r = red_combine(r, vals[q], mode);
+    *value = r;
+  }
+}
+
 inline unsigned
 grid_for(size_t n, int threads = 256)
 {
@@ -517,6 +555,9 @@ struct pf_plan
   size_t Dl = 1;             // cells of the local slab
   int a_begin = 0, a_count = 0; // pass A lines owned by this rank
   size_t xbuf_elems = 0;     // complex elements of one exchange buffer
+  long long a_chunk = 0, a_total = 0; // rank q owns lines [q*a_chunk, ...) of a_total
+  size_t fwd_elems = 0;      // forward-exchange region of the operators
+  unsigned long long red_seq = 0; // cross-rank reductions issued so far
   unsigned char* slab_block = nullptr; // [2 exchange buffers][flags]
   void* peer_block[8] = { nullptr };
   unsigned long long** d_flagsA = nullptr; // device arrays of peer pointers
@@ -724,6 +765,11 @@ plan_resize(pf_plan* pl)
     const long long b1 = std::min<long long>(A, chunk * (pl->rank + 1));
     pl->a_begin = (int)b0;
     pl->a_count = (int)(b1 - b0);
+    pl->a_chunk = chunk;
+    pl->a_total = A;
+    // operators: rank q receives its lines with the FULL last axis
+    pl->fwd_elems = (size_t)std::min<long long>(A, chunk) *
+                    (pl->dim == 3 ? pl->m0 : 1) * pl->c[pl->dim - 1];
     pl->xbuf_elems = pl->dim == 3 ? (size_t)pl->m0 * pl->cl * pl->n[1]
                                   : (size_t)pl->cl * pl->m0p;
   }
@@ -1606,6 +1652,13 @@ slab_flags(const pf_plan* pl, void* block, int which)
          8 * which;
 }
 
+cplx*
+slab_fwd(const pf_plan* pl, void* block)
+{
+  return reinterpret_cast<cplx*>(static_cast<unsigned char*>(block) +
+                                 2 * pl->xbuf_elems * sizeof(cplx) + 512);
+}
+
 // first half of a slab-mode realization: pass A + start of the exchange.
 // Returns the epoch of this realization in *epoch_out.
 int
@@ -1783,11 +1836,158 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   return slab_issue_tail(pl, e, out_dev, transform);
 }
 
+// The same operators in slab mode (P ranks, fields distributed over the last
+// dimension as in fieldtraits.hh:281-282).  Two exchanges, mirroring the two
+// FFTW-MPI transposes of the reference's forward and backward transforms:
+//   forward : after the local F0 / F1 passes every rank sends, for the lines
+//             of rank q, its cl samples of the last axis into q's forward
+//             region (strided DMA copies) -- epoch e1;
+//   backward: the fused spectral pass writes its transposed tiles into the
+//             owners' exchange buffers (peer stores, as pass A) -- epoch e2;
+// then passes B and C run on the local layers.
+int
+apply_slab_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
+{
+  if (!pl->connected)
+    return fail(PF_ERR_INVALID,
+                "slab mode: call pf_slab_connect on every rank first");
+  double** tabp = op == PF_OP_MATRIX ? &pl->lam
+                  : op == PF_OP_ROOT ? &pl->sig
+                                     : &pl->inv;
+  if (op == PF_OP_MATRIX)
+    PF_TRY(ensure_eigen(pl));
+  else
+    PF_TRY(ensure_table(pl, tabp, op == PF_OP_ROOT ? 1 : 2));
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0, cl = pl->cl;
+  const int P = pl->nranks;
+  const double invN = 1.0 / (double)pl->Next;
+  const long long clast = c[pl->dim - 1];
+  const long long rows_per_line = pl->dim == 3 ? m0 : 1; // rows per a-line
+  if (pl->dim == 3)
+    PF_TRY(dev_alloc(&pl->Z, (size_t)cl * c[1] * pl->m0p));
+  PF_TRY(dev_alloc(&pl->V, (size_t)pl->a_total * rows_per_line * cl));
+  // ---- local forward passes -------------------------------------------------
+  if (pl->dim == 3) {
+    cplx* Up = pl->Z; // pruned U[cl][m0][c1]
+    PassArgs f0 = blank_args(); // F0: x0 lines, (a,b) = (x1, x2 local)
+    f0.A = (int)c[1];
+    f0.B = (int)cl;
+    f0.in = in_dev;
+    f0.isa = c[0];
+    f0.isb = c[1] * c[0];
+    f0.n_valid = (int)c[0];
+    f0.out = Up;
+    f0.osb = m0 * c[1];
+    f0.ose = c[1];
+    f0.keep = (int)m0;
+    PF_TRY(run_pass(pl, n[0], pf::K_R2C_LOAD, f0));
+    PassArgs f1 = blank_args(); // F1: x1 lines, (a,b) = (x2 local, k0)
+    f1.A = (int)cl;
+    f1.B = (int)m0;
+    f1.in = Up;
+    f1.isa = m0 * c[1];
+    f1.isb = c[1];
+    f1.n_valid = (int)c[1];
+    f1.out = pl->V; // V[k1][k0][x2 local]
+    f1.osb = cl;
+    f1.ose = m0 * cl;
+    f1.keep = (int)n[1];
+    PF_TRY(run_pass(pl, n[1], pf::K_C2T_FWD, f1));
+  } else {
+    PassArgs f0 = blank_args(); // F0: x0 lines, a = x1 local
+    f0.A = (int)cl;
+    f0.B = 1;
+    f0.in = in_dev;
+    f0.isa = c[0];
+    f0.n_valid = (int)c[0];
+    f0.out = pl->V; // V[k0][x1 local]
+    f0.osb = 0;
+    f0.ose = cl;
+    f0.keep = (int)m0;
+    PF_TRY(run_pass(pl, n[0], pf::K_R2C_LOAD, f0));
+  }
+  // ---- forward exchange, epoch e1 ---------------------------------------------
+  const unsigned long long e1 = ++pl->epoch;
+  if (e1 > 2) {
+    k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
+                                          e1 - 2, pl->d_timeout);
+    pl->launches++;
+  }
+  for (int i = 0; i < P; i++) {
+    const int q = (pl->rank + i) % P;
+    const long long qb = std::min<long long>(pl->a_total, pl->a_chunk * q);
+    const long long qe = std::min<long long>(pl->a_total, pl->a_chunk * (q + 1));
+    const long long rows = (qe - qb) * rows_per_line;
+    if (rows <= 0)
+      continue;
+    const cplx* src = pl->V + (size_t)qb * rows_per_line * cl;
+    cplx* dst = slab_fwd(pl, pl->peer_block[q]) + (size_t)pl->rank * cl;
+    PF_CUDA(cudaMemcpy2DAsync(dst, (size_t)clast * sizeof(cplx), src,
+                              (size_t)cl * sizeof(cplx), (size_t)cl * sizeof(cplx),
+                              (size_t)rows, cudaMemcpyDeviceToDevice, pl->stream));
+  }
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e1);
+  k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e1,
+                                        pl->d_timeout);
+  pl->launches += 2;
+  // ---- fused spectral pass, tiles stored into the owners' buffers, epoch e2 ---
+  const unsigned long long e2 = ++pl->epoch;
+  const int s2 = (int)(e2 & 1);
+  if (e2 > 2) {
+    k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
+                                          e2 - 2, pl->d_timeout);
+    pl->launches++;
+  }
+  PassArgs s = blank_args();
+  set_table(pl, s, *tabp);
+  s.a_begin = pl->a_begin;
+  s.A = pl->a_count;
+  s.in = slab_fwd(pl, pl->slab_block);
+  s.n_valid = (int)clast;
+  s.scale = invN;
+  s.keep = (int)clast;
+  s.n_peers = P;
+  s.rows_per_peer = (int)cl;
+  for (int q = 0; q < P; q++)
+    s.peer_out[q] = slab_buffer(pl, pl->peer_block[q], s2);
+  s.out = s.peer_out[pl->rank];
+  if (pl->dim == 3) {
+    s.B = (int)m0; // lines (a = k1 local, b = k0) along x2
+    s.isa = m0 * clast;
+    s.isb = clast;
+    s.osb = cl * n[1];
+    s.ose = n[1];
+    if (n[1] % 8 == 0) {
+      s.blk_T = (int)(n[1] / 8);
+      s.blk_rows = (int)cl;
+    }
+    if (s.A > 0)
+      PF_TRY(run_pass(pl, n[2], pf::K_SPEC_TILE, s));
+  } else {
+    s.B = 1; // lines a = k0 local along x1
+    s.isa = clast;
+    s.osb = 0;
+    s.ose = pl->m0p;
+    if (s.A > 0)
+      PF_TRY(run_pass(pl, n[1], pf::K_SPEC_TILE, s));
+  }
+  // forward region consumed (e1), tiles delivered (e2)
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsB, P, pl->rank, e1);
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e2);
+  pl->launches += 2;
+  PF_CUDA(cudaGetLastError());
+  return slab_issue_tail(pl, e2, out_dev, 0);
+}
+
 // multiplyExtended / multiplyRootExtended / multiplyInverseExtended
 // (matrix.hh:1459-1662) on device fields; in_dev may equal out_dev
 int
 apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
 {
+  if (pl->nranks > 1)
+    return apply_slab_dev(pl, op, in_dev, out_dev);
   if (pl->long2d)
     return fail(PF_ERR_INVALID,
                 "covariance operators need extended sizes <= 1024 in this "
@@ -1900,6 +2100,12 @@ reduce_dev(pf_plan* pl, size_t nn, const double* x, const double* y,
                                                            pl->red_partial);
   k_reduce2<<<1, RED_THREADS, 0, pl->stream>>>(std::max(nb, 1), pl->red_partial,
                                                mode, pl->red_partial + RED_BLOCKS);
+  if (pl->nranks > 1) {
+    k_slab_reduce<<<1, 32, 0, pl->stream>>>(
+      pl->d_flagsA, slab_flags(pl, pl->slab_block, 0), pl->nranks, pl->rank,
+      ++pl->red_seq, mode, pl->red_partial + RED_BLOCKS, pl->d_timeout);
+    pl->launches++;
+  }
   PF_CUDA(cudaGetLastError());
   pl->launches += 2;
   PF_CUDA(cudaMemcpyAsync(result_host, pl->red_partial + RED_BLOCKS,
@@ -2085,7 +2291,10 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
   if (pl->nranks > 1) {
     // exchange block: two buffers + flag arrays, one cudaMalloc so that one
     // IPC handle describes it
-    const size_t bytes = 2 * pl->xbuf_elems * sizeof(cplx) + 256;
+    // [buffer 0][buffer 1][flags A, B, reduction slots: 512 bytes][forward
+    // exchange region of the covariance operators]
+    const size_t bytes =
+      2 * pl->xbuf_elems * sizeof(cplx) + 512 + pl->fwd_elems * sizeof(cplx);
     void* blk = nullptr;
     if (cudaMalloc(&blk, bytes) != cudaSuccess ||
         cudaMemset(blk, 0, bytes) != cudaSuccess ||
@@ -2592,17 +2801,15 @@ pf_apply(pf_plan* pl, int op, const double* in, double* out)
   PF_TRY(check_plan(pl));
   if (op < 0 || op > 2 || !in || !out)
     return fail(PF_ERR_INVALID, "bad argument");
-  if (pl->nranks > 1)
-    return fail(PF_ERR_INVALID, "pf_apply is not available in slab mode yet "
-                                "(single-GPU plans only)");
+  // slab mode: `in` / `out` are this rank's layers (Dl values)
   Staged si;
-  PF_TRY(stage_in(pl, in, pl->D, si));
+  PF_TRY(stage_in(pl, in, pl->Dl, si));
   const bool dev = is_device_ptr(out);
-  PF_TRY(dev_alloc(&pl->dev_io[0], pl->D));
+  PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
   double* dst = dev ? out : pl->dev_io[0];
   PF_TRY(apply_dev(pl, op, si.dev, dst));
   if (!dev)
-    PF_CUDA(cudaMemcpyAsync(out, dst, pl->D * sizeof(double),
+    PF_CUDA(cudaMemcpyAsync(out, dst, pl->Dl * sizeof(double),
                             cudaMemcpyDeviceToHost, pl->stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
   return 0;
@@ -2616,10 +2823,9 @@ pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
   PF_TRY(check_plan(pl));
   if (!in || !out)
     return fail(PF_ERR_INVALID, "null argument");
-  if (pl->nranks > 1)
-    return fail(PF_ERR_INVALID, "pf_solve is not available in slab mode yet "
-                                "(single-GPU plans only)");
-  const size_t D = pl->D;
+  // slab mode: vectors are this rank's layers, scalar products are combined
+  // over the ranks in rank order (k_slab_reduce)
+  const size_t D = pl->Dl;
   Staged si;
   PF_TRY(stage_in(pl, in, D, si));
   const double* b = si.dev; // "solution"

@@ -476,7 +476,7 @@ template <int N>
 __device__ __forceinline__ void
 tile_store_peers(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t,
                  const PassArgs& p, long long base_off, int lines_valid, int b,
-                 int a0)
+                 int a0, double scale)
 {
   using K = KCfg<N>;
   __syncthreads();
@@ -485,7 +485,7 @@ tile_store_peers(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t,
     const int e = t + K::TPL * q;
     if (e < p.keep)
       stage[stage_slot<N>(e, lic)] =
-        make_double2(v[q].x * p.scale, v[q].y * p.scale);
+        make_double2(v[q].x * scale, v[q].y * scale);
   }
   __syncthreads();
   const int total = p.keep * K::LPC;
@@ -530,7 +530,7 @@ k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
   if (p.n_peers > 1)
     tile_store_peers<N>(v, sm, lic, t, p,
                         (long long)b * p.osb + p.a_begin + at * K::LPC, lv, b,
-                        p.a_begin + at * K::LPC);
+                        p.a_begin + at * K::LPC, p.scale);
   else
     tile_store<N>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
 }
@@ -938,7 +938,8 @@ k_spec(const PassArgs p, const cplx* __restrict__ tw2)
   }
   line_fft<N, -1>(v, sm + lic * K::C::PITCH, t, tw2);
   if (valid) {
-    const double* row = table_row(p, a, b);
+    // slab mode: this rank holds the lines a_begin .. a_begin + A - 1
+    const double* row = table_row(p, p.a_begin + a, b);
 #pragma unroll
     for (int q = 0; q < K::E; q++) {
       const int e = t + K::TPL * q;
@@ -961,8 +962,13 @@ k_spec(const PassArgs p, const cplx* __restrict__ tw2)
     }
   } else {
     const int lv = min(K::LPC, p.A - at * K::LPC);
-    tile_store<N>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC), p.ose,
-                  lv, 1.0);
+    if (p.n_peers > 1)
+      tile_store_peers<N>(v, sm, lic, t, p,
+                          (long long)b * p.osb + p.a_begin + at * K::LPC, lv, b,
+                          p.a_begin + at * K::LPC, 1.0);
+    else
+      tile_store<N>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC), p.ose,
+                    lv, 1.0);
   }
 }
 
