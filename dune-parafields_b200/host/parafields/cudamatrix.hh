@@ -58,7 +58,7 @@ private:
   enum { dim = Traits::dim };
   static_assert(std::is_same<RF, double>::value,
                 "the CUDA path computes in fp64 (RangeField must be double)");
-  static_assert(dim >= 1 && dim <= 3, "CudaMatrix supports dim 1, 2, 3");
+  // dim 4 compiles (the reference CLI instantiates it) and reports at run time
 
   const std::shared_ptr<Traits> traits;
   mutable pf_plan* plan = nullptr;
@@ -129,11 +129,13 @@ public:
       plan = nullptr;
     }
     filled = false;
+    if (dim < 1 || dim > 3)
+      throw std::runtime_error{ "CudaMatrix supports dim 1, 2, 3" };
     const auto& config = (*traits).config;
     pf_desc d;
     pf_desc_default(&d);
     d.dim = dim;
-    for (unsigned int i = 0; i < dim; i++) {
+    for (unsigned int i = 0; i < (dim <= 3 ? dim : 3); i++) {
       d.cells[i] = (*traits).cells[i];
       d.extensions[i] = (*traits).extensions[i];
     }
