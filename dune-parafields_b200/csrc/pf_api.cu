@@ -575,8 +575,9 @@ struct pf_plan
   cudaEvent_t ev_a[2] = { nullptr, nullptr }, ev_x[2] = { nullptr, nullptr };
   // bit mask of pass kinds routed to the persistent TMA kernels (N >= 256);
   // PF_PIPE=0 in the environment selects the plain kernels everywhere
-  // (pass A stays on the plain kernel: it is issue-bound and the plain
-  // kernel keeps 12 warps per SM against 8 FFT warps, profiles/r01b)
+  // (bit K_GEN_TILE, the 8-warp persistent pass A kp_gen, is off by default:
+  // pass A is dispatch-bound and needs 12 FFT warps per SM; kp_gen remains
+  // the slab-mode pass A, where it stores to peer memory)
   bool gen3_force = false; // tests: take kp_gen3 whenever it is applicable
   // bit K_GEN3: grouped persistent pass A (kp_gen3), 12 FFT warps per SM
   unsigned pipe_mask = (1u << pf::K_C2T_INV) | (1u << pf::K_C2T_FWD) |

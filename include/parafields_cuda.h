@@ -182,7 +182,10 @@ size_t pf_local_domain_size(const pf_plan* plan);
  * rank's memory over NVLink (the FFTW-MPI transpose of
  * r2cfieldbackend.hh:250-274 fused into the producing kernel) and
  * synchronises the ranks with flags in peer memory; `out` receives the local
- * slab.  All ranks must issue the same sequence of pf_generate* calls. */
+ * slab.  pf_apply and pf_solve work on the distributed field too (`in` / `out`
+ * = this rank's layers; forward exchange by DMA, backward exchange by peer
+ * stores, scalar products combined over the ranks in rank order).  All ranks
+ * must issue the same sequence of pf_generate*, pf_apply and pf_solve calls. */
 #define PF_SLAB_HANDLE_BYTES 64
 int pf_slab_handle(pf_plan* plan, void* handle_out);
 int pf_slab_connect(pf_plan* plan, const void* handles, int count);
