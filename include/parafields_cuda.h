@@ -117,8 +117,11 @@ typedef struct pf_desc
   unsigned cg_iterations;   /* randomField.cgIterations (100)                 */
   int parity_mode;          /* 0 reference sampler, 1 corrected  */
   int rng_mode;             /* 0 Philox + fp32 Box-Muller, 1 fp64 Box-Muller  */
-  int census_quirk;         /* 1: R2C census walks interleaved re/im of the
-                               first half like the reference (Appendix C.3)   */
+  int census_quirk;         /* reserved (accepted, ignored): the reference's
+                               R2C census walks interleaved re/im of half the
+                               entries; this library
+                               always scans and clamps every real part, which
+                               is identical for valid embeddings             */
   unsigned max_factor;      /* embedding-factor retry bound, 0 = no retry     */
   int device;               /* CUDA device ordinal, -1 = current              */
   /* slab decomposition over the GPUs of one node, one process per GPU
