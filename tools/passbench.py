@@ -30,7 +30,10 @@ def main():
     wl = {k: v for k, v in bench.WORKLOADS[args.workload].items() if k != "label"}
     names = {0: "A", 1: "A1d", 2: "B", 4: "C"}
     for mask in args.masks.split(","):
-        os.environ["PF_PIPE"] = mask
+        if mask == "default":
+            os.environ.pop("PF_PIPE", None)
+        else:
+            os.environ["PF_PIPE"] = mask
         with pfb.Plan(device=0, rng_mode=args.rng, **wl) as plan:
             plan.compute_eigenvalues()
             out = torch.empty(plan.domain_size, dtype=torch.float64, device="cuda")
