@@ -37,6 +37,7 @@ COVARIANCE = {
     "generalizedCauchy": 9,
     "cubic": 10,
     "whiteNoise": 11,
+    "matern": 12,  # general nu = cov_param[0] (stochastic.maternNu)
 }
 ANISOTROPY = {"none": 0, "axiparallel": 1, "geometric": 2}
 TRANSFORM = {"none": 0, "logNormal": 1, "foldedNormal": 2, "sign": 3, "boxCox": 4}

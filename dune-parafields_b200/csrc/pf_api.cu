@@ -547,6 +547,17 @@ struct pf_plan
   // launches issued while it is set
   int sm_cap = 0;
   int split_a = 0;               // SMs given to pass A (0: no overlap)
+  // one GPU, 3D, pf_generate_batch into device memory (experiment, off by
+  // default): pass A of realization r+1 on split_one SMs, writing the other Y
+  // buffer, beside the tail of realization r on the remaining SMs
+  // (PF_SPLIT=<SMs>).  Measured on B200 at K3 (profiles/r02g): results
+  // bit-identical, but SLOWER (206/s at 100 SMs against 233/s sequential):
+  // passes B and C need all 148 SMs to reach their 6 TB/s -- their time scales
+  // with 1/SMs like pass A's, so there is no idle resource to overlap into.
+  int split_one = 0;
+  cplx* Y2 = nullptr;            // second pass A output for that pipeline
+  cplx* y_override = nullptr;    // generate_dev: pass A output / tail input
+  int gen_phase = 0;             // generate_dev: 0 both, 1 pass A only, 2 tail only
   cudaStream_t tail_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // ---- slab mode (one process per GPU) -------------------------------------
@@ -620,6 +631,7 @@ free_sized(pf_plan* pl)
   dev_free(&pl->sig);
   dev_free(&pl->inv);
   dev_free(&pl->Y);
+  dev_free(&pl->Y2);
   dev_free(&pl->Z);
   dev_free(&pl->V);
   dev_free(&pl->LY);
@@ -698,6 +710,31 @@ plan_resize(pf_plan* pl)
   cv.variance = d.variance;
   cv.p0 = d.cov_param[0];
   cv.p1 = d.cov_param[1];
+  if (d.covariance == PF_COV_MATERN) {
+    // constants of MaternCovariance (covariance.hh:541-545) and the
+    // Gamma-function terms of Temme's series for K_nu (pf_kernels.cuh)
+    const double nu = d.cov_param[0];
+    const double nl = std::floor(nu + 0.5), mu = nu - nl;
+    const double gampl = 1. / std::tgamma(1. + mu);
+    const double gammi = 1. / std::tgamma(1. - mu);
+    double gam1;
+    if (std::abs(mu) < 0.01) {
+      // odd part of the Taylor series of 1/Gamma(1+z) (Abramowitz & Stegun 6.1.34)
+      const double m2 = mu * mu;
+      gam1 = -(0.5772156649015329 +
+               m2 * (-0.0420026350340952 +
+                     m2 * (-0.0421977345555443 + m2 * 0.0072189432466630)));
+    } else
+      gam1 = (gammi - gampl) / (2. * mu);
+    cv.mt[0] = std::sqrt(2. * nu);
+    cv.mt[1] = std::pow(2., 1. - nu) / std::tgamma(nu);
+    cv.mt[2] = mu;
+    cv.mt[3] = nl;
+    cv.mt[4] = gampl;
+    cv.mt[5] = gammi;
+    cv.mt[6] = gam1;
+    cv.mt[7] = 0.5 * (gammi + gampl);
+  }
   for (int i = 0; i < pl->dim; i++) {
     cv.h[i] = d.extensions[i] / d.cells[i];
     cv.half[i] = 0.5 * d.extensions[i] * pl->factor;
@@ -958,7 +995,8 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
     PF_TRY(make_tile_map_at(a.out, a.A, a.keep, a.B, a.ose, a.osb, boxr,
                             &tms.m[0], lpc));
     tmptr = &tms;
-    grid = (int)std::min<long long>((ntiles + 2) / 3, pl->sm_count);
+    grid = (int)std::min<long long>((ntiles + 2) / 3,
+                                    pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count);
     launch_kind = pf::K_GEN3;
     pipe = true;
   } else if (pipe) {
@@ -1588,12 +1626,15 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.na_self = (int)n[1];
     a.nb_self = (int)n[0];
     a.plane_axis = 1;
-    a.out = pl->Y; // Y[k0][x2][k1]
+    cplx* Yb = pl->y_override ? pl->y_override : pl->Y;
+    a.out = Yb; // Y[k0][x2][k1]
     a.osb = c[2] * n[1];
     a.ose = n[1];
     a.keep = (int)c[2];
-    PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
-    PF_TRY(inverse_tail(pl, pl->Y, c[2], out_dev, transform));
+    if (pl->gen_phase != 2)
+      PF_TRY(run_pass(pl, n[2], pf::K_GEN_TILE, a));
+    if (pl->gen_phase != 1)
+      PF_TRY(inverse_tail(pl, Yb, c[2], out_dev, transform));
   } else if (pl->dim == 2 && pl->long2d) {
     PF_TRY(generate_long2d(pl, a, out_dev, transform));
   } else if (pl->dim == 2) {
@@ -2227,8 +2268,11 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
   *out = nullptr;
   if (desc->dim < 1 || desc->dim > 3)
     return fail(PF_ERR_INVALID, "dimension must be 1, 2 or 3");
-  if (desc->covariance < 0 || desc->covariance > PF_COV_WHITE_NOISE)
+  if (desc->covariance < 0 || desc->covariance > PF_COV_MATERN)
     return fail(PF_ERR_INVALID, "covariance structure not known");
+  // covariance.hh:547-548 (nu = 0 divides by Gamma(0) there; rejected too)
+  if (desc->covariance == PF_COV_MATERN && !(desc->cov_param[0] > 0.))
+    return fail(PF_ERR_INVALID, "matern nu has to be positive");
   if (desc->anisotropy < 0 || desc->anisotropy > 2)
     return fail(PF_ERR_INVALID,
                 "stochastic.anisotropy must be \"none\", \"axiparallel\" or "
@@ -2271,6 +2315,8 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     pl->pipe_mask = (unsigned)strtoul(env, nullptr, 0);
   if (const char* env = getenv("PF_GEN3")) // "force": skip the size heuristic
     pl->gen3_force = std::string(env) == "force";
+  if (const char* env = getenv("PF_SPLIT")) // SMs for pass A in the one-GPU pipeline
+    pl->split_one = atoi(env);
   pl->nranks = desc->n_ranks > 1 ? desc->n_ranks : 1;
   pl->rank = pl->nranks > 1 ? desc->rank : 0;
   if (pl->nranks > 8 || pl->rank < 0 || pl->rank >= pl->nranks) {
@@ -2615,6 +2661,21 @@ pf_get_eigenvalues(pf_plan* pl, double* out, size_t count, int layout)
   return 0;
 }
 
+// does pf_generate_batch pipeline pass A against the tails on one GPU?  Only
+// where pass A is the grouped persistent kernel (run_pass: 3D, lines of 1024,
+// many waves), because the overlap works by capping persistent grids
+static bool
+overlap_one(const pf_plan* pl)
+{
+  if (pl->nranks > 1 || pl->dim != 3 || pl->n[2] != 1024 || pl->gen3_force)
+    return false;
+  if (pl->split_one < 8 || pl->split_one > pl->sm_count - 8)
+    return false;
+  if (!(pl->pipe_mask & (1u << pf::K_GEN3)) || (pl->pipe_mask & 1u))
+    return false;
+  return (long long)((pl->n[1] + 3) / 4) * pl->m0 >= 8LL * pl->sm_count;
+}
+
 int
 pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
                   double* out, int apply_transform)
@@ -2692,6 +2753,56 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
       PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_join, 0));
     }
     return 0;
+  }
+  if (dev && count > 1 && overlap_one(pl)) {
+    // one GPU, 3D: pass A of realization r+1 (dispatch-bound, split_one SMs,
+    // plan stream) runs beside the tail of realization r (HBM-bound, the other
+    // SMs, tail stream); two Y buffers, events order producer and consumer
+    PF_TRY(ensure_work(pl));
+    PF_TRY(dev_alloc(&pl->Y2, (size_t)pl->m0 * pl->c[2] * pl->n[1]));
+    if (!pl->tail_stream) {
+      PF_CUDA(cudaStreamCreateWithFlags(&pl->tail_stream, cudaStreamNonBlocking));
+      PF_CUDA(cudaEventCreateWithFlags(&pl->ev_fork, cudaEventDisableTiming));
+      PF_CUDA(cudaEventCreateWithFlags(&pl->ev_join, cudaEventDisableTiming));
+    }
+    for (int i = 0; i < 2; i++) {
+      if (!pl->ev_a[i])
+        PF_CUDA(cudaEventCreateWithFlags(&pl->ev_a[i], cudaEventDisableTiming));
+      if (!pl->ev_x[i])
+        PF_CUDA(cudaEventCreateWithFlags(&pl->ev_x[i], cudaEventDisableTiming));
+    }
+    cudaStream_t main_stream = pl->stream;
+    PF_CUDA(cudaEventRecord(pl->ev_fork, main_stream));
+    PF_CUDA(cudaStreamWaitEvent(pl->tail_stream, pl->ev_fork, 0));
+    int rc = 0;
+    for (size_t r = 0; r < count && rc == 0; r++) {
+      const int b = (int)(r & 1);
+      cplx* Yb = b ? pl->Y2 : pl->Y;
+      if (r >= 2) // the tail of realization r-2 has read this buffer
+        PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_x[b], 0));
+      pl->y_override = Yb;
+      pl->gen_phase = 1;
+      pl->sm_cap = r == 0 ? 0 : pl->split_one; // nothing runs beside the first
+      rc = generate_dev(pl, nk, seed, first + r, nullptr, nullptr, nullptr, tr);
+      if (rc == 0 && cudaEventRecord(pl->ev_a[b], main_stream) == cudaSuccess &&
+          cudaStreamWaitEvent(pl->tail_stream, pl->ev_a[b], 0) == cudaSuccess) {
+        pl->stream = pl->tail_stream;
+        pl->gen_phase = 2;
+        pl->sm_cap = r + 1 == count ? 0 : pl->sm_count - pl->split_one;
+        rc = generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->Dl,
+                          nullptr, tr);
+        if (rc == 0 && cudaEventRecord(pl->ev_x[b], pl->tail_stream) != cudaSuccess)
+          rc = fail(PF_ERR_CUDA, "event record failed");
+      } else if (rc == 0)
+        rc = fail(PF_ERR_CUDA, "event record failed");
+      pl->stream = main_stream;
+      pl->y_override = nullptr;
+      pl->gen_phase = 0;
+      pl->sm_cap = 0;
+    }
+    PF_CUDA(cudaEventRecord(pl->ev_join, pl->tail_stream));
+    PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_join, 0));
+    return rc;
   }
   if (dev) {
     for (size_t r = 0; r < count; r++)

@@ -19,7 +19,8 @@ enum
   COV_CAUCHY = 8,
   COV_GEN_CAUCHY = 9,
   COV_CUBIC = 10,
-  COV_WHITE_NOISE = 11
+  COV_WHITE_NOISE = 11,
+  COV_MATERN = 12 // general nu, covariance.hh:527-581
 };
 
 struct CovParams
@@ -28,7 +29,11 @@ struct CovParams
   int cov;
   int aniso;         // 0 none 1 axiparallel 2 geometric
   double variance;
-  double p0, p1;     // expGamma | cauchyAlpha, cauchyBeta
+  double p0, p1;     // expGamma | cauchyAlpha, cauchyBeta | maternNu
+  // general Matern (host-prepared, pf_api.cu): [0] sqrt(2 nu), [1] 2^(1-nu) /
+  // Gamma(nu), [2] mu = nu - round(nu), [3] round(nu), [4] 1/Gamma(1+mu),
+  // [5] 1/Gamma(1-mu), [6] Temme's Gamma_1(mu), [7] Gamma_2(mu)
+  double mt[8];
   double h[3];       // meshsize
   double half[3];    // 0.5 * ext * factor  (mirror threshold, matrix.hh:640)
   double period[3];  // ext * factor

@@ -105,6 +105,80 @@ dispatch_transform(int kind, F&& f)
 }
 
 // ---------------------------------------------------------------------------
+// modified Bessel function of the second kind K_nu(x), x > 0, real order
+// nu = mu + nl with |mu| <= 1/2 -- what covariance.hh:565-573 takes from
+// gsl_sf_bessel_Knu (GSL, absent here).  Published algorithm: Temme's series
+// (J. Comput. Phys. 19 (1975) 324) for x < 2, Steed's continued fraction CF2
+// in the Thompson-Barnett form for x >= 2, then the upward recurrence
+// K_{v+1} = K_{v-1} + (2 v / x) K_v (stable for K).  The Gamma-function
+// constants of mu come from the host (CovParams::mt).
+// ---------------------------------------------------------------------------
+static __device__ __noinline__ double
+bessel_k_nu(const double* mt, double x)
+{
+  const double mu = mt[2], mu2 = mu * mu;
+  const int nl = (int)mt[3];
+  const double EPS = 1e-16;
+  double kmu, kmu1;
+  if (x < 2.) {
+    const double b = 0.5 * x, lg = -log(b), sg = mu * lg;
+    const double pimu = 3.14159265358979323846 * mu;
+    const double fsin = fabs(pimu) < 1e-8 ? 1. : pimu / sin(pimu);
+    const double fsinh = fabs(sg) < 1e-8 ? 1. : sinh(sg) / sg;
+    double f = fsin * (mt[6] * cosh(sg) + mt[7] * fsinh * lg);
+    const double ex = exp(sg);
+    double p = 0.5 * ex / mt[4], q = 0.5 / (ex * mt[5]);
+    double c = 1., sum = f, sum1 = p;
+    const double b2 = b * b;
+    for (int i = 1; i < 500; i++) {
+      f = (i * f + p + q) / (i * (double)i - mu2);
+      c *= b2 / i;
+      p /= i - mu;
+      q /= i + mu;
+      const double del = c * f;
+      sum += del;
+      sum1 += c * (p - i * f);
+      if (fabs(del) < fabs(sum) * EPS)
+        break;
+    }
+    kmu = sum;
+    kmu1 = sum1 * (2. / x);
+  } else {
+    double b = 2. * (1. + x), d = 1. / b, h = d, delh = d;
+    double q1 = 0., q2 = 1.;
+    const double a1 = 0.25 - mu2;
+    double q = a1, c = a1, a = -a1;
+    double s = 1. + q * delh;
+    for (int i = 2; i < 500; i++) {
+      a -= 2 * (i - 1);
+      c = -a * c / i;
+      const double qn = (q1 - b * q2) / a;
+      q1 = q2;
+      q2 = qn;
+      q += c * qn;
+      b += 2.;
+      d = 1. / (b + a * d);
+      delh = (b * d - 1.) * delh;
+      h += delh;
+      const double dels = q * delh;
+      s += dels;
+      if (fabs(dels) < fabs(s) * EPS)
+        break;
+    }
+    h = a1 * h;
+    kmu = sqrt(3.14159265358979323846 / (2. * x)) * exp(-x) / s;
+    kmu1 = kmu * (mu + x + 0.5 - h) / x;
+  }
+  const double xi2 = 2. / x;
+  for (int i = 1; i <= nl; i++) {
+    const double kn = (mu + i) * xi2 * kmu1 + kmu;
+    kmu = kmu1;
+    kmu1 = kn;
+  }
+  return kmu;
+}
+
+// ---------------------------------------------------------------------------
 // covariance on the torus, matrix.hh:624-648 + covariance.hh (same arithmetic
 // as the reference functors)
 // ---------------------------------------------------------------------------
@@ -166,6 +240,12 @@ cov_function(const CovParams& c, const double* x)
       const double h2 = h * h, h3 = h2 * h, h5 = h3 * h2, h7 = h5 * h2;
       return c.variance *
              (1. - 7. * h2 + 8.75 * h3 - 3.5 * h5 + 0.75 * h7);
+    }
+    case COV_MATERN: { // covariance.hh:565-573
+      if (h < 1e-10)
+        return c.variance;
+      const double z = c.mt[0] * h;
+      return c.variance * c.mt[1] * pow(z, c.p0) * bessel_k_nu(c.mt, z);
     }
   }
   return 0.;

@@ -80,6 +80,7 @@ private:
       { "separableExponential", PF_COV_SEPARABLE_EXPONENTIAL },
       { "matern32", PF_COV_MATERN32 },
       { "matern52", PF_COV_MATERN52 },
+      { "matern", PF_COV_MATERN },
       { "dampedOscillation", PF_COV_DAMPED_OSCILLATION },
       { "gammaExponential", PF_COV_GAMMA_EXPONENTIAL },
       { "cauchy", PF_COV_CAUCHY },
@@ -90,11 +91,6 @@ private:
     for (const auto& e : table)
       if (name == e.first)
         return e.second;
-    if (name == "matern")
-      throw std::runtime_error{
-        "general Matern covariance needs the GSL library (use matern32 or "
-        "matern52 on the CUDA path)"
-      };
     if (name == "custom-iso" || name == "custom-aniso")
       throw std::runtime_error{
         "custom covariance classes are host functors and cannot be evaluated "
@@ -173,6 +169,10 @@ public:
 
     if (d.covariance == PF_COV_GAMMA_EXPONENTIAL)
       d.cov_param[0] = config.template get<RF>("stochastic.expGamma");
+    // covariance.hh:541 (the reference needs GSL for this functor; the CUDA
+    // path evaluates K_nu on the device)
+    if (d.covariance == PF_COV_MATERN)
+      d.cov_param[0] = config.template get<double>("stochastic.maternNu");
     if (d.covariance == PF_COV_GENERALIZED_CAUCHY) {
       d.cov_param[0] = config.template get<RF>("stochastic.cauchyAlpha");
       d.cov_param[1] = config.template get<RF>("stochastic.cauchyBeta");

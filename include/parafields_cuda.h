@@ -57,7 +57,9 @@ typedef enum pf_covariance
   PF_COV_CAUCHY = 8,
   PF_COV_GENERALIZED_CAUCHY = 9,
   PF_COV_CUBIC = 10,
-  PF_COV_WHITE_NOISE = 11
+  PF_COV_WHITE_NOISE = 11,
+  PF_COV_MATERN = 12 /* general nu (covariance.hh:527-581; the reference needs
+                        GSL's K_nu for it, here a device function)       */
 } pf_covariance;
 
 /* stochastic.anisotropy, matrix.hh:496-508 */
@@ -105,7 +107,7 @@ typedef struct pf_desc
   unsigned embedding_factor; /* embedding.factor (default 2)                  */
   int covariance;           /* pf_covariance                                  */
   double variance;          /* stochastic.variance                            */
-  double cov_param[2];      /* expGamma | cauchyAlpha, cauchyBeta             */
+  double cov_param[2];      /* expGamma | cauchyAlpha, cauchyBeta | maternNu  */
   int anisotropy;           /* pf_anisotropy                                  */
   double corr_length[9];    /* stochastic.corrLength: 1 | dim | dim*dim
                                numbers, row major (NOT inverted)              */

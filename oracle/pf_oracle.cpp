@@ -79,7 +79,8 @@ enum
   COV_CAUCHY = 8,
   COV_GEN_CAUCHY = 9,
   COV_CUBIC = 10,
-  COV_WHITE_NOISE = 11
+  COV_WHITE_NOISE = 11,
+  COV_MATERN = 12
 };
 
 struct Stats
@@ -377,6 +378,22 @@ covariance(const OrcCfg& c, const double* x)
       return variance *
              (1. - 7. * std::pow(h_eff, 2) + 8.75 * std::pow(h_eff, 3) -
               3.5 * std::pow(h_eff, 5) + 0.75 * std::pow(h_eff, 7));
+  }
+  if (c.cov == COV_MATERN) { // covariance.hh:527-581, general nu = c.p0
+    // The reference calls gsl_sf_bessel_Knu (GSL, unpinned version, absent
+    // here); libstdc++'s std::cyl_bessel_k is the stand-in for it, and
+    // tests/test_oracle.py checks this functor against scipy.special.kv.
+    const double nu = c.p0;
+    if (nu < 0.)
+      throw std::runtime_error{ "matern nu has to be positive" };
+    if (h_eff < 1e-10)
+      return variance;
+    const double sqrtTwoNu = std::sqrt(2. * nu);
+    const double z = sqrtTwoNu * h_eff;
+    if (z > 700.) // K_nu underflows; std::cyl_bessel_k may raise instead
+      return 0.;
+    return variance * std::pow(2., 1. - nu) / std::tgamma(nu) *
+           std::pow(z, nu) * std::cyl_bessel_k(nu, z);
   }
   throw std::runtime_error{ "covariance structure not known" };
 }
