@@ -82,6 +82,10 @@ ABI_SYMBOLS = [
     "pf_vec_dot",
     "pf_vec_norm1",
     "pf_vec_norminf",
+    "pf_field_refine",
+    "pf_field_coarsen",
+    "pf_field_localize",
+    "pf_field_evaluate",
     "pf_device_alloc",
     "pf_device_free",
     "pf_memcpy",
@@ -193,6 +197,11 @@ def lib():
     L.pf_vec_dot.argtypes = [vp, sz, dp, dp, C.POINTER(C.c_double)]
     L.pf_vec_norm1.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
     L.pf_vec_norminf.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
+    up = C.POINTER(C.c_uint)
+    L.pf_field_refine.argtypes = [vp, C.c_int, up, dp, dp]
+    L.pf_field_coarsen.argtypes = [vp, C.c_int, up, dp, dp]
+    L.pf_field_localize.argtypes = [vp, C.c_int, up, up, up, dp, dp, C.c_double, dp]
+    L.pf_field_evaluate.argtypes = [vp, C.c_int, up, dp, dp, sz, dp, C.c_int, dp]
     L.pf_device_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.pf_device_free.argtypes = [vp, vp]
     L.pf_memcpy.argtypes = [vp, vp, vp, sz]
@@ -479,6 +488,57 @@ class Plan:
         else:
             n = x.numel()
         _check(lib().pf_transform(self._h, _ptr(x), _ptr(out), n))
+        return out
+
+    # -- resolution transfer, localisation, point evaluation ---------------------
+    # cells are given x-fastest (like grid.cells); numpy arrays are C-ordered,
+    # i.e. shaped reversed(cells)
+    @staticmethod
+    def _cells(cells):
+        return (C.c_uint * 3)(*(list(cells) + [1] * (3 - len(cells))))
+
+    def field_refine(self, cells, x, out=None):
+        """StochasticPart::refine (stochastic.hh:597-670); cells = old cells."""
+        if isinstance(x, np.ndarray):
+            x = np.ascontiguousarray(x, dtype=np.float64)
+            if out is None:
+                out = np.empty(tuple(2 * c for c in reversed(cells)), dtype=np.float64)
+        _check(lib().pf_field_refine(self._h, len(cells), self._cells(cells), _ptr(x), _ptr(out)))
+        return out
+
+    def field_coarsen(self, cells, x, out=None):
+        """StochasticPart::coarsen (stochastic.hh:679-755); cells = old (fine) cells."""
+        if isinstance(x, np.ndarray):
+            x = np.ascontiguousarray(x, dtype=np.float64)
+            if out is None:
+                out = np.empty(tuple(c // 2 for c in reversed(cells)), dtype=np.float64)
+        _check(lib().pf_field_coarsen(self._h, len(cells), self._cells(cells), _ptr(x), _ptr(out)))
+        return out
+
+    def field_localize(self, cells, extensions, center, radius, x, offset=None, global_cells=None):
+        """StochasticPart::localize (stochastic.hh:798-817), in place."""
+        d = len(cells)
+        ext = (C.c_double * 3)(*(list(extensions) + [1.0] * (3 - d)))
+        cen = (C.c_double * 3)(*(list(center) + [0.0] * (3 - d)))
+        off = self._cells(offset) if offset is not None else None
+        gc = self._cells(global_cells) if global_cells is not None else None
+        _check(lib().pf_field_localize(self._h, d, self._cells(cells), off, gc, ext, cen, radius, _ptr(x)))
+        return x
+
+    def field_evaluate(self, cells, extensions, field, locations, apply_transform=True, out=None):
+        """StochasticPart::evaluate + RandomField::evaluate's transform for n x dim locations."""
+        d = len(cells)
+        ext = (C.c_double * 3)(*(list(extensions) + [1.0] * (3 - d)))
+        if isinstance(locations, np.ndarray):
+            locations = np.ascontiguousarray(locations, dtype=np.float64)
+            npts = locations.size // d
+            if out is None:
+                out = np.empty(npts, dtype=np.float64)
+        else:
+            npts = locations.numel() // d
+        if isinstance(field, np.ndarray):
+            field = np.ascontiguousarray(field, dtype=np.float64)
+        _check(lib().pf_field_evaluate(self._h, d, self._cells(cells), ext, _ptr(field), npts, _ptr(locations), int(bool(apply_transform)), _ptr(out)))
         return out
 
     # -- vector space -----------------------------------------------------------

@@ -257,6 +257,175 @@ k_scale(size_t n, double alpha, double* __restrict__ x)
        i += (size_t)gridDim.x * blockDim.x)
     x[i] *= alpha;
 }
+// ValueTransform::apply (mutators.hh:36-162) on one value
+__device__ __forceinline__ double
+transform_value(double v, int kind, double lambda)
+{
+  switch (kind) {
+    case 1:
+      return exp(v);
+    case 2:
+      return fabs(v);
+    case 3:
+      return v < 0. ? -1. : 1.;
+    case 4:
+      return pow(v * lambda + 1, -lambda);
+    default:
+      return v;
+  }
+}
+
+// StochasticPart::refine (stochastic.hh:597-670), output driven: one thread
+// per pair of new cells along x0 (both children of one old cell), so every
+// warp writes 512 contiguous bytes; the old value is read once per thread and
+// shared through L1/L2 by the 2^(dim-1) threads that need it.
+// o* = old cells, rows = 2*o1*(2*o2) new rows.
+__global__ void
+k_refine(unsigned o0, unsigned o1, size_t rows, const double* __restrict__ in,
+         double2* __restrict__ out)
+{
+  const size_t total = rows * o0;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = t / o0;
+    const unsigned i0 = (unsigned)(t - row * o0);
+    const size_t n1 = 2 * (size_t)o1;
+    const size_t x2 = row / n1;
+    const size_t x1 = row - x2 * n1;
+    const double v = in[i0 + (size_t)o0 * ((x1 >> 1) + (size_t)o1 * (x2 >> 1))];
+    out[t] = make_double2(v, v);
+  }
+}
+
+// StochasticPart::coarsen (stochastic.hh:679-755): one thread per new cell,
+// 16-byte loads of the 2^(dim-1) fine row pairs, summed in the reference's
+// order (x0, then x1, then x2) so the result is bit-identical.
+// n* = new cells; the fine rows have 2*n0 entries.
+template <int DIM>
+__global__ void
+k_coarsen(unsigned n0, unsigned n1, size_t total,
+          const double2* __restrict__ in, double* __restrict__ out)
+{
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = t / n0;
+    const unsigned i0 = (unsigned)(t - row * n0);
+    const size_t i2 = DIM == 3 ? row / n1 : 0;
+    const size_t i1 = row - i2 * n1;
+    // index in units of double2 (fine row length n0 pairs)
+    const size_t base = i0 + (size_t)n0 * (2 * i1 + 2 * (size_t)n1 * 2 * i2);
+    const double2 a = in[base], b = in[base + n0];
+    double v = 0.;
+    v = __dadd_rn(v, a.x);
+    v = __dadd_rn(v, a.y);
+    v = __dadd_rn(v, b.x);
+    v = __dadd_rn(v, b.y);
+    if (DIM == 3) {
+      const size_t up = base + (size_t)n0 * 2 * n1;
+      const double2 c = in[up], d = in[up + n0];
+      v = __dadd_rn(v, c.x);
+      v = __dadd_rn(v, c.y);
+      v = __dadd_rn(v, d.x);
+      v = __dadd_rn(v, d.y);
+    }
+    out[t] = v / (DIM == 3 ? 8. : 4.);
+  }
+}
+
+struct FieldGeom
+{
+  int dim;
+  unsigned cells[3];  // local block
+  unsigned offset[3]; // first global index of the block
+  unsigned gcells[3]; // whole grid
+  double ext[3];
+  double center[3];
+};
+
+// StochasticPart::localize (stochastic.hh:798-817): cell centres by
+// indicesToCoords (fieldtraits.hh:461-469); explicit _rn operations keep the
+// distance free of contractions, so only exp() may differ from libm (1 ulp).
+__global__ void
+k_localize(FieldGeom g, size_t total, double factor, double radius,
+           double* __restrict__ data)
+{
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    size_t rest = t;
+    double dist = 0.;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      if (j < g.dim) {
+        const unsigned i = (unsigned)(rest % g.cells[j]);
+        rest /= g.cells[j];
+        const double loc =
+          __ddiv_rn(__dmul_rn((double)(i + g.offset[j]) + 0.5, g.ext[j]),
+                    (double)g.gcells[j]);
+        const double d = __dadd_rn(loc, -g.center[j]);
+        dist = __dadd_rn(dist, __dmul_rn(d, d));
+      }
+    }
+    const double w = __dmul_rn(
+      factor, exp(__ddiv_rn(__dmul_rn(-0.5, dist), __dmul_rn(radius, radius))));
+    data[t] = __dmul_rn(data[t], w);
+  }
+}
+
+// StochasticPart::evaluate (stochastic.hh:480-574) for a batch of locations
+// on one rank + RandomField::evaluate's value transform (randomfield.hh:
+// 585-595).  coordsToIndices: fieldtraits.hh:440-448.  A location on the
+// upper face of exactly one dimension reads the (zero-filled) overlap, on an
+// edge or corner it steps back into the last cell; anything outside the
+// closed box raises *bad.
+__global__ void
+k_evaluate(FieldGeom g, const double* __restrict__ field, size_t npoints,
+           const double* __restrict__ loc, int kind, double lambda,
+           double* __restrict__ out, int* __restrict__ bad)
+{
+  for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npoints;
+       p += (size_t)gridDim.x * blockDim.x) {
+    unsigned idx[3] = { 0, 0, 0 };
+    int outside = 0;
+    bool invalid = false;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      if (i < g.dim) {
+        const double x = loc[p * g.dim + i];
+        const double q =
+          __ddiv_rn(__dmul_rn(x, (double)g.cells[i] + 1e-6), g.ext[i]);
+        if (!(x >= 0.) || !(q < 4294967295.))
+          invalid = true;
+        else {
+          idx[i] = (unsigned)q; // truncation, like the reference's Index(...)
+          if (idx[i] > g.cells[i])
+            invalid = true;
+          else if (idx[i] == g.cells[i])
+            outside++;
+        }
+      }
+    }
+    double v;
+    if (invalid) {
+      *bad = 1;
+      v = nan("");
+    } else if (outside == 1) {
+      v = 0.;
+    } else {
+      size_t index = 0, stride = 1;
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        if (i < g.dim) {
+          const unsigned k = idx[i] == g.cells[i] ? idx[i] - 1 : idx[i];
+          index += stride * k;
+          stride *= g.cells[i];
+        }
+      }
+      v = field[index];
+    }
+    out[p] = invalid ? v : transform_value(v, kind, lambda);
+  }
+}
+
 __global__ void
 k_fill(size_t n, double v, double* __restrict__ x)
 {
@@ -2184,6 +2353,48 @@ stage_in(pf_plan* pl, const double* p, size_t nn, Staged& s)
   return 0;
 }
 
+// output (or in/out) array: the caller's pointer when it is device memory,
+// otherwise a device scratch that finish() copies back to the host
+struct StagedOut
+{
+  pf_plan* pl = nullptr;
+  double* dev = nullptr;
+  double* owned = nullptr;
+  double* host = nullptr;
+  size_t count = 0;
+  ~StagedOut()
+  {
+    if (owned)
+      cudaFree(owned);
+  }
+  int finish()
+  {
+    if (owned)
+      PF_CUDA(cudaMemcpyAsync(host, owned, count * sizeof(double),
+                              cudaMemcpyDeviceToHost, pl->stream));
+    PF_CUDA(cudaStreamSynchronize(pl->stream));
+    return 0;
+  }
+};
+
+int
+stage_out(pf_plan* pl, double* p, size_t nn, bool copy_in, StagedOut& s)
+{
+  s.pl = pl;
+  s.count = nn;
+  if (is_device_ptr(p)) {
+    s.dev = p;
+    return 0;
+  }
+  PF_TRY(dev_alloc(&s.owned, nn));
+  s.host = p;
+  s.dev = s.owned;
+  if (copy_in)
+    PF_CUDA(cudaMemcpyAsync(s.owned, p, nn * sizeof(double),
+                            cudaMemcpyHostToDevice, pl->stream));
+  return 0;
+}
+
 int
 check_plan(const pf_plan* pl)
 {
@@ -3037,32 +3248,31 @@ int
 pf_vec_axpy(pf_plan* pl, size_t nn, double alpha, const double* x, double* y)
 {
   PF_TRY(check_plan(pl));
-  if (is_device_ptr(x) && is_device_ptr(y)) {
-    k_axpy<<<grid_for(nn), 256, 0, pl->stream>>>(nn, alpha, x, y);
-    PF_CUDA(cudaGetLastError());
-    pl->launches++;
-    return 0;
-  }
-  if (is_device_ptr(x) || is_device_ptr(y))
-    return fail(PF_ERR_INVALID, "pf_vec_axpy: x and y must live in the same memory space");
-  for (size_t i = 0; i < nn; i++)
-    y[i] += alpha * x[i];
-  return 0;
+  const bool dev = is_device_ptr(y);
+  Staged sx;
+  StagedOut sy;
+  PF_TRY(stage_in(pl, x, nn, sx));
+  PF_TRY(stage_out(pl, y, nn, true, sy));
+  k_axpy<<<grid_for(nn), 256, 0, pl->stream>>>(nn, alpha, sx.dev, sy.dev);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  if (dev && !sx.owned)
+    return 0; // device arrays: asynchronous on the plan's stream
+  return sy.finish();
 }
 
 int
 pf_vec_scale(pf_plan* pl, size_t nn, double alpha, double* x)
 {
   PF_TRY(check_plan(pl));
-  if (is_device_ptr(x)) {
-    k_scale<<<grid_for(nn), 256, 0, pl->stream>>>(nn, alpha, x);
-    PF_CUDA(cudaGetLastError());
-    pl->launches++;
+  StagedOut sx;
+  PF_TRY(stage_out(pl, x, nn, true, sx));
+  k_scale<<<grid_for(nn), 256, 0, pl->stream>>>(nn, alpha, sx.dev);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  if (!sx.owned)
     return 0;
-  }
-  for (size_t i = 0; i < nn; i++)
-    x[i] *= alpha;
-  return 0;
+  return sx.finish();
 }
 
 static int
@@ -3092,6 +3302,162 @@ int
 pf_vec_norminf(pf_plan* pl, size_t nn, const double* x, double* result)
 {
   return vec_reduce(pl, nn, x, nullptr, 2, result);
+}
+
+// ---------------------------------------------------------------------------
+// resolution transfer, localisation, point evaluation
+// ---------------------------------------------------------------------------
+namespace {
+int
+field_dims(const char* who, int dim, const unsigned* cells, int min_dim,
+           size_t* count)
+{
+  if (dim < 1 || dim > 3)
+    return fail(PF_ERR_INVALID, "dimension of field has to be 1, 2 or 3");
+  if (dim < min_dim)
+    return fail(PF_ERR_INVALID, "not implemented"); // stochastic.hh:664,749
+  if (!cells)
+    return fail(PF_ERR_INVALID, std::string(who) + ": null cells");
+  size_t n = 1;
+  for (int i = 0; i < dim; i++) {
+    if (cells[i] == 0)
+      return fail(PF_ERR_INVALID, std::string(who) + ": empty dimension");
+    n *= cells[i];
+  }
+  *count = n;
+  return 0;
+}
+} // namespace
+
+int
+pf_field_refine(pf_plan* pl, int dim, const unsigned* cells, const double* in,
+                double* out)
+{
+  PF_TRY(check_plan(pl));
+  size_t n_old = 0;
+  PF_TRY(field_dims("pf_field_refine", dim, cells, 2, &n_old));
+  const size_t n_new = n_old << dim;
+  Staged si;
+  StagedOut so;
+  PF_TRY(stage_in(pl, in, n_old, si));
+  PF_TRY(stage_out(pl, out, n_new, false, so));
+  if (reinterpret_cast<uintptr_t>(so.dev) & 15)
+    return fail(PF_ERR_INVALID, "pf_field_refine: out must be 16-byte aligned");
+  const unsigned o2 = dim == 3 ? cells[2] : 1;
+  const size_t rows = 2 * (size_t)cells[1] * (dim == 3 ? 2 * (size_t)o2 : 1);
+  k_refine<<<grid_for(rows * cells[0]), 256, 0, pl->stream>>>(
+    cells[0], cells[1], rows, si.dev, reinterpret_cast<double2*>(so.dev));
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return so.finish();
+}
+
+int
+pf_field_coarsen(pf_plan* pl, int dim, const unsigned* cells, const double* in,
+                 double* out)
+{
+  PF_TRY(check_plan(pl));
+  size_t n_old = 0;
+  PF_TRY(field_dims("pf_field_coarsen", dim, cells, 2, &n_old));
+  for (int i = 0; i < dim; i++)
+    if (cells[i] % 2 != 0) // fieldtraits.hh:336-339
+      return fail(PF_ERR_INVALID, "cannot coarsen odd number of cells");
+  const size_t n_new = n_old >> dim;
+  Staged si;
+  StagedOut so;
+  PF_TRY(stage_in(pl, in, n_old, si));
+  PF_TRY(stage_out(pl, out, n_new, false, so));
+  if (reinterpret_cast<uintptr_t>(si.dev) & 15)
+    return fail(PF_ERR_INVALID, "pf_field_coarsen: in must be 16-byte aligned");
+  const double2* src = reinterpret_cast<const double2*>(si.dev);
+  if (dim == 3)
+    k_coarsen<3><<<grid_for(n_new), 256, 0, pl->stream>>>(
+      cells[0] / 2, cells[1] / 2, n_new, src, so.dev);
+  else
+    k_coarsen<2><<<grid_for(n_new), 256, 0, pl->stream>>>(
+      cells[0] / 2, cells[1] / 2, n_new, src, so.dev);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return so.finish();
+}
+
+int
+pf_field_localize(pf_plan* pl, int dim, const unsigned* cells,
+                  const unsigned* offset, const unsigned* global_cells,
+                  const double* extensions, const double* center,
+                  double radius, double* data)
+{
+  PF_TRY(check_plan(pl));
+  size_t n = 0;
+  PF_TRY(field_dims("pf_field_localize", dim, cells, 1, &n));
+  if (!extensions || !center)
+    return fail(PF_ERR_INVALID, "pf_field_localize: null geometry");
+  FieldGeom g{};
+  g.dim = dim;
+  for (int i = 0; i < dim; i++) {
+    g.cells[i] = cells[i];
+    g.offset[i] = offset ? offset[i] : 0;
+    g.gcells[i] = global_cells ? global_cells[i] : cells[i];
+    g.ext[i] = extensions[i];
+    g.center[i] = center[i];
+  }
+  StagedOut sd;
+  PF_TRY(stage_out(pl, data, n, true, sd));
+  const double factor = std::pow(2. * 3.14159, -(dim / 2.));
+  k_localize<<<grid_for(n), 256, 0, pl->stream>>>(g, n, factor, radius, sd.dev);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return sd.finish();
+}
+
+int
+pf_field_evaluate(pf_plan* pl, int dim, const unsigned* cells,
+                  const double* extensions, const double* field,
+                  size_t npoints, const double* locations,
+                  int apply_transform, double* out)
+{
+  PF_TRY(check_plan(pl));
+  size_t n = 0;
+  PF_TRY(field_dims("pf_field_evaluate", dim, cells, 1, &n));
+  if (!extensions)
+    return fail(PF_ERR_INVALID, "pf_field_evaluate: null extensions");
+  if (npoints == 0)
+    return 0;
+  FieldGeom g{};
+  g.dim = dim;
+  for (int i = 0; i < dim; i++) {
+    g.cells[i] = cells[i];
+    g.gcells[i] = cells[i];
+    g.ext[i] = extensions[i];
+  }
+  Staged sf, sl;
+  StagedOut so;
+  PF_TRY(stage_in(pl, field, n, sf));
+  PF_TRY(stage_in(pl, locations, npoints * dim, sl));
+  PF_TRY(stage_out(pl, out, npoints, false, so));
+  int* bad = nullptr;
+  PF_TRY(dev_alloc(&bad, 1));
+  cudaError_t e = cudaMemsetAsync(bad, 0, sizeof(int), pl->stream);
+  if (e == cudaSuccess) {
+    k_evaluate<<<grid_for(npoints), 256, 0, pl->stream>>>(
+      g, sf.dev, npoints, sl.dev, apply_transform ? pl->d.transform : 0,
+      pl->d.boxcox_lambda, so.dev, bad);
+    e = cudaGetLastError();
+    pl->launches++;
+  }
+  int flag = 0;
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(&flag, bad, sizeof(int), cudaMemcpyDeviceToHost,
+                        pl->stream);
+  int rc = e == cudaSuccess ? so.finish() : 0;
+  cudaFree(bad);
+  if (e != cudaSuccess)
+    return fail(PF_ERR_CUDA, cudaGetErrorString(e));
+  if (rc)
+    return rc;
+  if (flag)
+    return fail(PF_ERR_INVALID, "pf_field_evaluate: location outside the domain");
+  return 0;
 }
 
 int

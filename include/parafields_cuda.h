@@ -241,6 +241,41 @@ int pf_vec_dot(pf_plan* plan, size_t n, const double* x, const double* y,
 int pf_vec_norm1(pf_plan* plan, size_t n, const double* x, double* result);
 int pf_vec_norminf(pf_plan* plan, size_t n, const double* x, double* result);
 
+/* Resolution transfer, localisation and point evaluation of a field
+ * (SURVEY 8(f) rows 1 and 3).  Arrays may be device or host memory (host
+ * arrays are staged through the device, nothing is computed on the CPU);
+ * cells[] has dim entries, index 0 fastest.
+ *
+ * StochasticPart::refine, stochastic.hh:597-670: cells = OLD local cells,
+ * out holds 2^dim * prod(cells) doubles (16-byte aligned).  dim 2 or 3; 1D
+ * fails with the reference's "not implemented". */
+int pf_field_refine(pf_plan* plan, int dim, const unsigned* cells,
+                    const double* in, double* out);
+/* StochasticPart::coarsen, stochastic.hh:679-755: cells = OLD (fine) local
+ * cells, all even ("cannot coarsen odd number of cells",
+ * fieldtraits.hh:336-339); out holds prod(cells)/2^dim doubles; sums in the
+ * reference's order, bit-identical. */
+int pf_field_coarsen(pf_plan* plan, int dim, const unsigned* cells,
+                     const double* in, double* out);
+/* StochasticPart::localize, stochastic.hh:798-817 (cell centres by
+ * indicesToCoords, fieldtraits.hh:461-469), in place.  offset (first global
+ * index of the local block) and global_cells may be NULL on one rank. */
+int pf_field_localize(pf_plan* plan, int dim, const unsigned* cells,
+                      const unsigned* offset, const unsigned* global_cells,
+                      const double* extensions, const double* center,
+                      double radius, double* data);
+/* StochasticPart::evaluate (stochastic.hh:480-574, coordsToIndices
+ * fieldtraits.hh:440-448) for npoints locations (npoints x dim doubles) on
+ * one rank, followed by RandomField::evaluate's value transform
+ * (randomfield.hh:585-595) when apply_transform != 0.  A location on the
+ * upper face of exactly one dimension yields the reference's zero-filled
+ * overlap value; locations outside the closed box fail with PF_ERR_INVALID
+ * (undefined behaviour in the reference). */
+int pf_field_evaluate(pf_plan* plan, int dim, const unsigned* cells,
+                      const double* extensions, const double* field,
+                      size_t npoints, const double* locations,
+                      int apply_transform, double* out);
+
 /* device memory helpers so that a host-only caller (C++, cgo, ctypes) can
  * keep fields resident in HBM */
 int pf_device_alloc(pf_plan* plan, size_t bytes, void** ptr);

@@ -88,6 +88,11 @@ def lib():
         L.orc_multiply_inverse.argtypes = [C.POINTER(OrcCfg), dp, dp, dp, C.POINTER(C.c_uint)]
         L.orc_transform.argtypes = [C.c_int, C.c_double, C.c_size_t, dp]
         L.orc_torus_covariance.argtypes = [C.POINTER(OrcCfg), dp]
+        up = C.POINTER(C.c_uint)
+        L.orc_field_refine.argtypes = [C.c_int, up, dp, dp]
+        L.orc_field_coarsen.argtypes = [C.c_int, up, dp, dp]
+        L.orc_field_localize.argtypes = [C.c_int, up, up, up, dp, dp, C.c_double, dp]
+        L.orc_field_evaluate.argtypes = [C.c_int, up, dp, dp, C.c_size_t, dp, C.c_int, C.c_double, dp]
         _lib = L
     return _lib
 
@@ -279,3 +284,44 @@ def transform(kind, values, boxcox_lambda=0.0):
     v = np.array(values, dtype=np.float64).ravel().copy()
     _check(lib().orc_transform(TRANSFORM[kind], boxcox_lambda, v.size, _dp(v)))
     return v.reshape(np.shape(values))
+
+
+def _up(seq):
+    return (C.c_uint * 3)(*(list(seq) + [1] * (3 - len(seq))))
+
+
+def field_refine(cells, field):
+    """StochasticPart::refine, stochastic.hh:597-670; cells = old cells (x fastest)."""
+    f = np.ascontiguousarray(field, dtype=np.float64).ravel()
+    out = np.empty(f.size * 2 ** len(cells))
+    _check(lib().orc_field_refine(len(cells), _up(cells), _dp(f), _dp(out)))
+    return out.reshape(tuple(2 * c for c in reversed(cells)))
+
+
+def field_coarsen(cells, field):
+    """StochasticPart::coarsen, stochastic.hh:679-755; cells = old (fine) cells."""
+    f = np.ascontiguousarray(field, dtype=np.float64).ravel()
+    out = np.empty(max(f.size // 2 ** len(cells), 1))
+    _check(lib().orc_field_coarsen(len(cells), _up(cells), _dp(f), _dp(out)))
+    return out.reshape(tuple(c // 2 for c in reversed(cells)))
+
+
+def field_localize(cells, extensions, center, radius, field, offset=None, global_cells=None):
+    """StochasticPart::localize, stochastic.hh:798-817."""
+    d = len(cells)
+    f = np.array(field, dtype=np.float64).ravel().copy()
+    ext = np.asarray(extensions, dtype=np.float64)
+    cen = np.asarray(center, dtype=np.float64)
+    _check(lib().orc_field_localize(d, _up(cells), _up(offset or [0] * d), _up(global_cells or cells), _dp(ext), _dp(cen), radius, _dp(f)))
+    return f.reshape(tuple(reversed(cells)))
+
+
+def field_evaluate(cells, extensions, field, locations, transform="none", boxcox_lambda=0.0):
+    """StochasticPart::evaluate (stochastic.hh:480-574) + value transform, one rank."""
+    d = len(cells)
+    f = np.ascontiguousarray(field, dtype=np.float64).ravel()
+    loc = np.ascontiguousarray(locations, dtype=np.float64).reshape(-1, d)
+    ext = np.asarray(extensions, dtype=np.float64)
+    out = np.empty(loc.shape[0])
+    _check(lib().orc_field_evaluate(d, _up(cells), _dp(ext), _dp(f), loc.shape[0], _dp(loc), TRANSFORM[transform], boxcox_lambda, _dp(out)))
+    return out

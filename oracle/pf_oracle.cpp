@@ -7,12 +7,17 @@
 // links, loads or calls it.  Only tests/, __graft_entry__.smoke() and
 // bench.py's cpu_baseline / --impl reference legs may use it.
 //
-// Parity status: the reference ships no golden vectors and cannot be built in
-// this environment (FFTW3-MPI, MPI, dune-common absent), so the
-// oracle is pinned by (i) first-principles identities checked in tests/
-// (naive O(N^2) DFTs, dense circulant algebra, numpy/pocketfft as a second
-// implementation) and (ii) the libstdc++ RNG known-answer values of
-// SURVEY.md section 8(a) row a11.  "parity unpinned by the reference".
+// Parity status: PINNED BY THE REFERENCE ITSELF.  The reference ships no
+// golden vectors, but its path compiles from its own UNMODIFIED headers once
+// the absent third-party libraries (FFTW3-MPI, MPI, dune-common) are replaced
+// by single-rank stand-ins (oracle/shim/, oracle/ref_driver.cpp ->
+// oracle/_ref/libpf_ref.so, built by oracle/Makefile).  This restatement is
+// checked against that build live (tests/test_reference_live.py) and through
+// committed fixtures it produced (tests/golden/ref_*.npz, tests/test_golden.py),
+// in addition to first-principles identities (naive O(N^2) DFTs, dense
+// circulant algebra, numpy/pocketfft) and the libstdc++ RNG known-answer
+// values of SURVEY.md section 8(a) row a11.  What stays unpinned is FFTW's own
+// rounding (library absent) -- see DESIGN.md section 4.
 //
 // Every function cites the reference file:line it follows.  Paths are
 // relative to /root/reference/ext/parafields-core/include/parafields/.
@@ -1114,6 +1119,156 @@ orc_torus_covariance(const OrcCfg* cfg, double* out)
     size_t idx[3] = { 0, 0, 0 };
     indexToIndices(index, idx, bound, s.dim);
     out[index] = torus_cov(*cfg, s, g, idx);
+  }
+  ORC_CATCH
+}
+
+// StochasticPart::refine (stochastic.hh:597-670): every cell of the old
+// level becomes 2^dim cells with the same value.  cells = OLD local cells.
+int
+orc_field_refine(int dim, const unsigned* cells, const double* in, double* out)
+{
+  ORC_TRY
+  if (dim == 1)
+    throw std::runtime_error{ "not implemented" }; // stochastic.hh:664-665
+  if (dim != 2 && dim != 3)
+    throw std::runtime_error{ "dimension of field has to be 1, 2 or 3" };
+  const size_t o0 = cells[0], o1 = cells[1], o2 = dim == 3 ? cells[2] : 1;
+  const size_t n0 = 2 * o0, n1 = 2 * o1;
+  for (size_t i2 = 0; i2 < o2; i2++)
+    for (size_t i1 = 0; i1 < o1; i1++)
+      for (size_t i0 = 0; i0 < o0; i0++) {
+        const double v = in[i0 + o0 * (i1 + o1 * i2)];
+        const size_t base =
+          2 * i0 + n0 * (2 * i1 + n1 * (dim == 3 ? 2 * i2 : 0));
+        out[base] = v;
+        out[base + 1] = v;
+        out[base + n0] = v;
+        out[base + n0 + 1] = v;
+        if (dim == 3) {
+          out[base + n1 * n0] = v;
+          out[base + n1 * n0 + 1] = v;
+          out[base + n1 * n0 + n0] = v;
+          out[base + n1 * n0 + n0 + 1] = v;
+        }
+      }
+  ORC_CATCH
+}
+
+// StochasticPart::coarsen (stochastic.hh:679-755): mean of the 2^dim fine
+// cells, summed in the reference's order.  cells = OLD (fine) local cells;
+// odd counts are refused by the traits (fieldtraits.hh:336-339).
+int
+orc_field_coarsen(int dim, const unsigned* cells, const double* in, double* out)
+{
+  ORC_TRY
+  if (dim == 1)
+    throw std::runtime_error{ "not implemented" }; // stochastic.hh:749-750
+  if (dim != 2 && dim != 3)
+    throw std::runtime_error{ "dimension of field has to be 1, 2 or 3" };
+  for (int i = 0; i < dim; i++)
+    if (cells[i] % 2 != 0)
+      throw std::runtime_error{ "cannot coarsen odd number of cells" };
+  const size_t o0 = cells[0], o1 = cells[1];
+  const size_t n0 = o0 / 2, n1 = o1 / 2, n2 = dim == 3 ? cells[2] / 2 : 1;
+  for (size_t i2 = 0; i2 < n2; i2++)
+    for (size_t i1 = 0; i1 < n1; i1++)
+      for (size_t i0 = 0; i0 < n0; i0++) {
+        const size_t old =
+          2 * i0 + o0 * (2 * i1 + o1 * (dim == 3 ? 2 * i2 : 0));
+        double v = 0.;
+        v += in[old];
+        v += in[old + 1];
+        v += in[old + o0];
+        v += in[old + o0 + 1];
+        if (dim == 3) {
+          v += in[old + o1 * o0];
+          v += in[old + o1 * o0 + 1];
+          v += in[old + o1 * o0 + o0];
+          v += in[old + o1 * o0 + o0 + 1];
+        }
+        out[i0 + n0 * (i1 + n1 * i2)] = v / (dim == 3 ? 8 : 4);
+      }
+  ORC_CATCH
+}
+
+// StochasticPart::localize (stochastic.hh:798-817) with indicesToCoords
+// (fieldtraits.hh:461-469): data *= (2*3.14159)^(-dim/2) exp(-|x-c|^2/(2 r^2)).
+// cells / offset describe the local block, gcells the whole grid.
+int
+orc_field_localize(int dim, const unsigned* cells, const unsigned* offset,
+                   const unsigned* gcells, const double* extensions,
+                   const double* center, double radius, double* data)
+{
+  ORC_TRY
+  size_t bound[3] = { 1, 1, 1 };
+  size_t n = 1;
+  for (int i = 0; i < dim; i++) {
+    bound[i] = cells[i];
+    n *= cells[i];
+  }
+  const double factor = std::pow(2. * 3.14159, -(dim / 2.));
+  for (size_t index = 0; index < n; index++) {
+    size_t idx[3] = { 0, 0, 0 };
+    indexToIndices(index, idx, bound, dim);
+    double distSquared = 0.;
+    for (int j = 0; j < dim; j++) {
+      const unsigned g = (unsigned)idx[j] + offset[j];
+      const double loc = (g + 0.5) * extensions[j] / gcells[j];
+      distSquared += (loc - center[j]) * (loc - center[j]);
+    }
+    data[index] *= factor * std::exp(-0.5 * distSquared / (radius * radius));
+  }
+  ORC_CATCH
+}
+
+// StochasticPart::evaluate (stochastic.hh:480-574) on one rank, where
+// dataToEval is a copy and the 2*dim overlap arrays stay zero-filled
+// (stochastic.hh:838-852), followed by RandomField::evaluate's value
+// transform (randomfield.hh:585-595; no trend part).  coordsToIndices:
+// fieldtraits.hh:440-448.  A location on the upper boundary of exactly one
+// dimension reads the (zero) overlap; on an edge or corner the reference
+// steps back into the last cell.  Locations outside the closed box are
+// undefined behaviour in the reference and refused here (return 1).
+int
+orc_field_evaluate(int dim, const unsigned* cells, const double* extensions,
+                   const double* field, size_t npoints, const double* loc,
+                   int transform, double boxcox_lambda, double* out)
+{
+  ORC_TRY
+  for (size_t p = 0; p < npoints; p++) {
+    unsigned idx[3] = { 0, 0, 0 };
+    int outside = 0;
+    for (int i = 0; i < dim; i++) {
+      const double x = loc[p * dim + i];
+      if (!(x >= 0.))
+        throw std::runtime_error{ "location outside the domain" };
+      idx[i] = (unsigned)(x * (cells[i] + 1e-6) / extensions[i]);
+      if (idx[i] > cells[i])
+        throw std::runtime_error{ "location outside the domain" };
+      if (idx[i] == cells[i])
+        outside++;
+    }
+    double v;
+    if (outside == 1 && dim <= 3)
+      v = 0.; // overlap[2i+1], never filled on one rank
+    else {
+      for (int i = 0; i < dim; i++)
+        if (idx[i] == cells[i])
+          idx[i]--;
+      size_t index = 0, stride = 1;
+      for (int i = 0; i < dim; i++) {
+        index += stride * idx[i];
+        stride *= cells[i];
+      }
+      v = field[index];
+    }
+    out[p] = v;
+  }
+  if (transform != 0) {
+    int rc = orc_transform(transform, boxcox_lambda, npoints, out);
+    if (rc != 0)
+      return rc;
   }
   ORC_CATCH
 }

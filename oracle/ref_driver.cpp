@@ -72,6 +72,9 @@ struct RefBase
   virtual void stored_lambda(double* out) = 0;
   virtual void bulk(double* out) = 0;
   virtual double dot_self() = 0;
+  virtual void refine() = 0;
+  virtual void coarsen() = 0;
+  virtual void evaluate(size_t n, const double* loc, double* out) = 0;
 };
 
 template<unsigned int dim>
@@ -204,6 +207,32 @@ struct Ref : RefBase
       out[i] = v[i][0];
   }
   double dot_self() override { return (*field) * (*field); }
+  // RandomField::refineMatrix + refine (randomfield.hh:825-880)
+  void refine() override
+  {
+    field->refineMatrix();
+    field->refine();
+  }
+  void coarsen() override
+  {
+    field->coarsenMatrix();
+    field->coarsen();
+  }
+  // RandomField::localize cannot be instantiated: stochastic.hh:806 calls the
+  // non-static Traits::indicesToCoords without an object (compile error), so
+  // the oracle's localize stays pinned by its closed form only.
+  // RandomField::evaluate (randomfield.hh:585-595), point by point
+  void evaluate(size_t n, const double* loc, double* out) override
+  {
+    typename Traits::DomainType x;
+    typename Traits::RangeType v;
+    for (size_t p = 0; p < n; p++) {
+      for (unsigned i = 0; i < dim; i++)
+        x[i] = loc[p * dim + i];
+      field->evaluate(x, v);
+      out[p] = v[0];
+    }
+  }
 };
 
 template<class F>
@@ -330,6 +359,22 @@ ref_dot_self(void* h)
   double d = 0.;
   guarded([&] { d = static_cast<RefBase*>(h)->dot_self(); });
   return d;
+}
+
+int
+ref_refine(void* h)
+{
+  return guarded([&] { static_cast<RefBase*>(h)->refine(); });
+}
+int
+ref_coarsen(void* h)
+{
+  return guarded([&] { static_cast<RefBase*>(h)->coarsen(); });
+}
+int
+ref_evaluate(void* h, size_t n, const double* loc, double* out)
+{
+  return guarded([&] { static_cast<RefBase*>(h)->evaluate(n, loc, out); });
 }
 
 // the reference's fallback RNG backend (backends/cpprngbackend.hh) on its own

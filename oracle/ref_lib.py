@@ -39,6 +39,9 @@ def lib():
         L.ref_dot_self.restype = C.c_double
         L.ref_dot_self.argtypes = [C.c_void_p]
         L.ref_rng.argtypes = [C.c_uint, C.c_size_t, C.c_void_p]
+        L.ref_refine.argtypes = [C.c_void_p]
+        L.ref_coarsen.argtypes = [C.c_void_p]
+        L.ref_evaluate.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -158,6 +161,25 @@ class Reference:
 
     def dot_self(self):
         return lib().ref_dot_self(self.h)
+
+    def refine(self):
+        """refineMatrix + refine (randomfield.hh:825-880); cells double."""
+        self._ck(lib().ref_refine(self.h))
+        self.cells = [2 * c for c in self.cells]
+        return self.get()
+
+    def coarsen(self):
+        """coarsenMatrix + coarsen (randomfield.hh:890-945); cells halve."""
+        self._ck(lib().ref_coarsen(self.h))
+        self.cells = [c // 2 for c in self.cells]
+        return self.get()
+
+    def evaluate(self, locations):
+        """RandomField::evaluate (randomfield.hh:585-595) at n x dim locations."""
+        loc = np.ascontiguousarray(locations, dtype=np.float64).reshape(-1, len(self.cells))
+        out = np.empty(loc.shape[0])
+        self._ck(lib().ref_evaluate(self.h, loc.shape[0], loc.ctypes.data, out.ctypes.data))
+        return out
 
 
 def rng(seed, n):
