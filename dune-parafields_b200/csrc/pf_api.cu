@@ -275,26 +275,34 @@ transform_value(double v, int kind, double lambda)
   }
 }
 
-// StochasticPart::refine (stochastic.hh:597-670), output driven: one thread
-// per pair of new cells along x0 (both children of one old cell), so every
-// warp writes 512 contiguous bytes; the old value is read once per thread and
-// shared through L1/L2 by the 2^(dim-1) threads that need it.
-// o* = old cells, rows = 2*o1*(2*o2) new rows.
+// StochasticPart::refine (stochastic.hh:597-670): blockIdx.y / z walk the old
+// rows and planes (no index division), threads walk the old cells of a row;
+// a thread reads one old value and stores it as one 16-byte pair into each
+// of the 2^(dim-1) new rows, so a warp writes 512 contiguous bytes per row.
+// o* = old cells; new rows have o0 pairs.
+template <int DIM>
 __global__ void
-k_refine(unsigned o0, unsigned o1, size_t rows, const double* __restrict__ in,
+k_refine(unsigned o0, unsigned o1, unsigned o2, const double* __restrict__ in,
          double2* __restrict__ out)
 {
-  const size_t total = rows * o0;
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (size_t)gridDim.x * blockDim.x) {
-    const size_t row = t / o0;
-    const unsigned i0 = (unsigned)(t - row * o0);
-    const size_t n1 = 2 * (size_t)o1;
-    const size_t x2 = row / n1;
-    const size_t x1 = row - x2 * n1;
-    const double v = in[i0 + (size_t)o0 * ((x1 >> 1) + (size_t)o1 * (x2 >> 1))];
-    out[t] = make_double2(v, v);
-  }
+  for (unsigned i2 = blockIdx.z; i2 < o2; i2 += gridDim.z)
+    for (unsigned i1 = blockIdx.y; i1 < o1; i1 += gridDim.y) {
+      const double* __restrict__ src = in + (size_t)o0 * (i1 + (size_t)o1 * i2);
+      double2* __restrict__ r0 =
+        out + (size_t)o0 * (2 * (size_t)i1 + 2 * (size_t)o1 * (DIM == 3 ? 2 * (size_t)i2 : 0));
+      double2* __restrict__ r1 = r0 + (size_t)o0 * 2 * o1; // plane 2 i2 + 1
+      for (unsigned i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < o0;
+           i0 += gridDim.x * blockDim.x) {
+        const double v = src[i0];
+        const double2 w = make_double2(v, v);
+        r0[i0] = w;
+        r0[i0 + o0] = w;
+        if (DIM == 3) {
+          r1[i0] = w;
+          r1[i0 + o0] = w;
+        }
+      }
+    }
 }
 
 // StochasticPart::coarsen (stochastic.hh:679-755): one thread per new cell,
@@ -342,33 +350,73 @@ struct FieldGeom
   double center[3];
 };
 
-// StochasticPart::localize (stochastic.hh:798-817): cell centres by
-// indicesToCoords (fieldtraits.hh:461-469); explicit _rn operations keep the
-// distance free of contractions, so only exp() may differ from libm (1 ulp).
+// StochasticPart::localize (stochastic.hh:798-817) in two steps.  The
+// Gaussian weight factor * exp(-|x - c|^2 / (2 r^2)) is separable, so
+// k_localize_axes evaluates, per axis j and local index i,
+// exp(-0.5 (loc_j(i) - center_j)^2 / r^2) with loc by indicesToCoords
+// (fieldtraits.hh:461-469) into one small table (cells[0] + cells[1] +
+// cells[2] doubles; factor folded into axis 0), and k_localize multiplies the
+// field with the product of the three entries: a pure HBM sweep.  Against the
+// reference's single exp() of the summed distance this differs by a few ulp
+// (tests: 1e-14 relative to the max norm).
 __global__ void
-k_localize(FieldGeom g, size_t total, double factor, double radius,
-           double* __restrict__ data)
+k_localize_axes(FieldGeom g, double factor, double rr, double* __restrict__ table)
 {
-  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (size_t)gridDim.x * blockDim.x) {
-    size_t rest = t;
-    double dist = 0.;
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      if (j < g.dim) {
-        const unsigned i = (unsigned)(rest % g.cells[j]);
-        rest /= g.cells[j];
-        const double loc =
-          __ddiv_rn(__dmul_rn((double)(i + g.offset[j]) + 0.5, g.ext[j]),
-                    (double)g.gcells[j]);
-        const double d = __dadd_rn(loc, -g.center[j]);
-        dist = __dadd_rn(dist, __dmul_rn(d, d));
+  const unsigned total = g.cells[0] + (g.dim > 1 ? g.cells[1] : 0) +
+                         (g.dim > 2 ? g.cells[2] : 0);
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += gridDim.x * blockDim.x) {
+    int j = 0;
+    unsigned i = t;
+    if (i >= g.cells[0]) {
+      i -= g.cells[0];
+      j = 1;
+      if (i >= g.cells[1]) {
+        i -= g.cells[1];
+        j = 2;
       }
     }
-    const double w = __dmul_rn(
-      factor, exp(__ddiv_rn(__dmul_rn(-0.5, dist), __dmul_rn(radius, radius))));
-    data[t] = __dmul_rn(data[t], w);
+    const double loc = __ddiv_rn(
+      __dmul_rn((double)(i + g.offset[j]) + 0.5, g.ext[j]), (double)g.gcells[j]);
+    const double d = __dadd_rn(loc, -g.center[j]);
+    const double w = exp(__ddiv_rn(__dmul_rn(-0.5, __dmul_rn(d, d)), rr));
+    table[t] = j == 0 ? __dmul_rn(factor, w) : w;
   }
+}
+
+template <int DIM>
+__global__ void
+k_localize(unsigned c0, unsigned c1, unsigned c2,
+           const double* __restrict__ table, double* __restrict__ data)
+{
+  constexpr unsigned ROWS = 4; // rows per block step: t0 is loaded once for them
+  const double* __restrict__ t0 = table;
+  const double* __restrict__ t1 = table + c0;
+  const double* __restrict__ t2 = t1 + c1;
+  for (unsigned i2 = blockIdx.z; i2 < c2; i2 += gridDim.z)
+    for (unsigned b1 = blockIdx.y * ROWS; b1 < c1; b1 += gridDim.y * ROWS) {
+      const double w2 = DIM > 2 ? t2[i2] : 1.;
+      for (unsigned i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < c0;
+           i0 += gridDim.x * blockDim.x) {
+        const double w0 = t0[i0];
+        double v[ROWS];
+#pragma unroll
+        for (unsigned r = 0; r < ROWS; r++)
+          if (b1 + r < c1)
+            v[r] = data[(size_t)c0 * (b1 + r + (size_t)c1 * i2) + i0];
+#pragma unroll
+        for (unsigned r = 0; r < ROWS; r++)
+          if (b1 + r < c1) {
+            double w = w0;
+            if (DIM > 1)
+              w = __dmul_rn(w, t1[b1 + r]);
+            if (DIM > 2)
+              w = __dmul_rn(w, w2);
+            data[(size_t)c0 * (b1 + r + (size_t)c1 * i2) + i0] =
+              __dmul_rn(v[r], w);
+          }
+      }
+    }
 }
 
 // StochasticPart::evaluate (stochastic.hh:480-574) for a batch of locations
@@ -377,23 +425,44 @@ k_localize(FieldGeom g, size_t total, double factor, double radius,
 // upper face of exactly one dimension reads the (zero-filled) overlap, on an
 // edge or corner it steps back into the last cell; anything outside the
 // closed box raises *bad.
+template <int DIM>
 __global__ void
 k_evaluate(FieldGeom g, const double* __restrict__ field, size_t npoints,
            const double* __restrict__ loc, int kind, double lambda,
            double* __restrict__ out, int* __restrict__ bad)
 {
-  for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npoints;
-       p += (size_t)gridDim.x * blockDim.x) {
-    unsigned idx[3] = { 0, 0, 0 };
-    int outside = 0;
-    bool invalid = false;
+  // U points per thread and step: all coordinate loads are issued before the
+  // first dependent gather, which keeps enough bytes in flight per SM
+  constexpr int U = 4;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t p0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p0 < npoints;
+       p0 += U * stride) {
+    double x[U][DIM];
 #pragma unroll
-    for (int i = 0; i < 3; i++) {
-      if (i < g.dim) {
-        const double x = loc[p * g.dim + i];
-        const double q =
-          __ddiv_rn(__dmul_rn(x, (double)g.cells[i] + 1e-6), g.ext[i]);
-        if (!(x >= 0.) || !(q < 4294967295.))
+    for (int u = 0; u < U; u++) {
+      const size_t p = p0 + u * stride;
+#pragma unroll
+      for (int i = 0; i < DIM; i++)
+        x[u][i] = p < npoints ? loc[p * DIM + i] : 0.;
+    }
+    size_t index[U];
+    int state[U]; // 0 inside, 1 overlap (zero), 2 invalid
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      unsigned idx[DIM];
+      int outside = 0;
+      bool invalid = false;
+#pragma unroll
+      for (int i = 0; i < DIM; i++) {
+        // Index(x * (cells + 1e-6) / ext): the product with the reciprocal
+        // is within 2 ulp of the quotient, so both truncate alike unless the
+        // value sits next to an integer -- only then the division is done
+        const double num = __dmul_rn(x[u][i], (double)g.cells[i] + 1e-6);
+        double q = __dmul_rn(num, g.center[i]); // center[] holds 1 / ext here
+        if (fabs(q - rint(q)) <= 1e-9 * (1. + fabs(q)))
+          q = __ddiv_rn(num, g.ext[i]);
+        idx[i] = 0;
+        if (!(x[u][i] >= 0.) || !(q < 4294967295.))
           invalid = true;
         else {
           idx[i] = (unsigned)q; // truncation, like the reference's Index(...)
@@ -403,26 +472,31 @@ k_evaluate(FieldGeom g, const double* __restrict__ field, size_t npoints,
             outside++;
         }
       }
-    }
-    double v;
-    if (invalid) {
-      *bad = 1;
-      v = nan("");
-    } else if (outside == 1) {
-      v = 0.;
-    } else {
-      size_t index = 0, stride = 1;
+      size_t lin = 0, step = 1;
 #pragma unroll
-      for (int i = 0; i < 3; i++) {
-        if (i < g.dim) {
-          const unsigned k = idx[i] == g.cells[i] ? idx[i] - 1 : idx[i];
-          index += stride * k;
-          stride *= g.cells[i];
-        }
+      for (int i = 0; i < DIM; i++) {
+        const unsigned k = idx[i] == g.cells[i] ? idx[i] - 1 : idx[i];
+        lin += step * k;
+        step *= g.cells[i];
       }
-      v = field[index];
+      index[u] = lin;
+      state[u] = invalid ? 2 : (outside == 1 ? 1 : 0);
     }
-    out[p] = invalid ? v : transform_value(v, kind, lambda);
+    double v[U];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      v[u] = (state[u] == 0 && p0 + u * stride < npoints) ? field[index[u]] : 0.;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t p = p0 + u * stride;
+      if (p < npoints) {
+        if (state[u] == 2) {
+          *bad = 1;
+          out[p] = nan("");
+        } else
+          out[p] = transform_value(v[u], kind, lambda);
+      }
+    }
   }
 }
 
@@ -686,6 +760,9 @@ struct pf_plan
   double* spare = nullptr;
   bool spare_valid = false;
   double* dev_io[2] = { nullptr, nullptr }; // staging for host fields
+  double* axis_tab = nullptr; // pf_field_localize: per-axis squared distances
+  size_t axis_cap = 0;
+  int* eval_flag = nullptr;   // pf_field_evaluate: "location outside" flag
   double* dev_in = nullptr;
   double* cg[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
   double* red_partial = nullptr; // RED_BLOCKS + 8 doubles
@@ -2627,6 +2704,8 @@ pf_plan_destroy(pf_plan* pl)
     cudaFree(kv.second);
   dev_free(&pl->dev_io[0]);
   dev_free(&pl->dev_io[1]);
+  dev_free(&pl->axis_tab);
+  dev_free(&pl->eval_flag);
   dev_free(&pl->dev_in);
   for (int i = 0; i < 6; i++)
     dev_free(&pl->cg[i]);
@@ -3308,6 +3387,15 @@ pf_vec_norminf(pf_plan* pl, size_t nn, const double* x, double* result)
 // resolution transfer, localisation, point evaluation
 // ---------------------------------------------------------------------------
 namespace {
+// one block row per field row: x covers the cells of a row, y / z the rows
+// and planes (grid-strided beyond the launch limits)
+dim3
+row_grid(unsigned c0, unsigned c1, unsigned c2)
+{
+  return dim3(std::min<unsigned>((c0 + 255) / 256, 1024),
+              std::min<unsigned>(c1, 65535), std::min<unsigned>(c2, 65535));
+}
+
 int
 field_dims(const char* who, int dim, const unsigned* cells, int min_dim,
            size_t* count)
@@ -3344,9 +3432,13 @@ pf_field_refine(pf_plan* pl, int dim, const unsigned* cells, const double* in,
   if (reinterpret_cast<uintptr_t>(so.dev) & 15)
     return fail(PF_ERR_INVALID, "pf_field_refine: out must be 16-byte aligned");
   const unsigned o2 = dim == 3 ? cells[2] : 1;
-  const size_t rows = 2 * (size_t)cells[1] * (dim == 3 ? 2 * (size_t)o2 : 1);
-  k_refine<<<grid_for(rows * cells[0]), 256, 0, pl->stream>>>(
-    cells[0], cells[1], rows, si.dev, reinterpret_cast<double2*>(so.dev));
+  const dim3 grid = row_grid(cells[0], cells[1], o2);
+  if (dim == 3)
+    k_refine<3><<<grid, 256, 0, pl->stream>>>(
+      cells[0], cells[1], o2, si.dev, reinterpret_cast<double2*>(so.dev));
+  else
+    k_refine<2><<<grid, 256, 0, pl->stream>>>(
+      cells[0], cells[1], o2, si.dev, reinterpret_cast<double2*>(so.dev));
   PF_CUDA(cudaGetLastError());
   pl->launches++;
   return so.finish();
@@ -3404,9 +3496,28 @@ pf_field_localize(pf_plan* pl, int dim, const unsigned* cells,
   StagedOut sd;
   PF_TRY(stage_out(pl, data, n, true, sd));
   const double factor = std::pow(2. * 3.14159, -(dim / 2.));
-  k_localize<<<grid_for(n), 256, 0, pl->stream>>>(g, n, factor, radius, sd.dev);
+  const unsigned c1 = dim > 1 ? cells[1] : 1, c2 = dim > 2 ? cells[2] : 1;
+  const size_t entries = (size_t)cells[0] + (dim > 1 ? c1 : 0) + (dim > 2 ? c2 : 0);
+  if (entries > pl->axis_cap) {
+    PF_CUDA(cudaStreamSynchronize(pl->stream));
+    dev_free(&pl->axis_tab);
+    PF_TRY(dev_alloc(&pl->axis_tab, entries));
+    pl->axis_cap = entries;
+  }
+  k_localize_axes<<<grid_for(entries), 256, 0, pl->stream>>>(g, factor, radius * radius,
+                                                              pl->axis_tab);
+  const dim3 grid = row_grid(cells[0], (c1 + 3) / 4, c2);
+  if (dim == 3)
+    k_localize<3><<<grid, 256, 0, pl->stream>>>(cells[0], c1, c2, pl->axis_tab,
+                                                sd.dev);
+  else if (dim == 2)
+    k_localize<2><<<grid, 256, 0, pl->stream>>>(cells[0], c1, c2, pl->axis_tab,
+                                                sd.dev);
+  else
+    k_localize<1><<<grid, 256, 0, pl->stream>>>(cells[0], c1, c2, pl->axis_tab,
+                                                sd.dev);
   PF_CUDA(cudaGetLastError());
-  pl->launches++;
+  pl->launches += 2;
   return sd.finish();
 }
 
@@ -3429,32 +3540,32 @@ pf_field_evaluate(pf_plan* pl, int dim, const unsigned* cells,
     g.cells[i] = cells[i];
     g.gcells[i] = cells[i];
     g.ext[i] = extensions[i];
+    g.center[i] = 1. / extensions[i]; // reciprocal for the index fast path
   }
   Staged sf, sl;
   StagedOut so;
   PF_TRY(stage_in(pl, field, n, sf));
   PF_TRY(stage_in(pl, locations, npoints * dim, sl));
   PF_TRY(stage_out(pl, out, npoints, false, so));
-  int* bad = nullptr;
-  PF_TRY(dev_alloc(&bad, 1));
-  cudaError_t e = cudaMemsetAsync(bad, 0, sizeof(int), pl->stream);
-  if (e == cudaSuccess) {
-    k_evaluate<<<grid_for(npoints), 256, 0, pl->stream>>>(
-      g, sf.dev, npoints, sl.dev, apply_transform ? pl->d.transform : 0,
-      pl->d.boxcox_lambda, so.dev, bad);
-    e = cudaGetLastError();
-    pl->launches++;
-  }
+  PF_TRY(dev_alloc(&pl->eval_flag, 1));
+  PF_CUDA(cudaMemsetAsync(pl->eval_flag, 0, sizeof(int), pl->stream));
+  const int kind = apply_transform ? pl->d.transform : 0;
+  const unsigned blocks = grid_for((npoints + 3) / 4);
+  if (dim == 3)
+    k_evaluate<3><<<blocks, 256, 0, pl->stream>>>(
+      g, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev, pl->eval_flag);
+  else if (dim == 2)
+    k_evaluate<2><<<blocks, 256, 0, pl->stream>>>(
+      g, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev, pl->eval_flag);
+  else
+    k_evaluate<1><<<blocks, 256, 0, pl->stream>>>(
+      g, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev, pl->eval_flag);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
   int flag = 0;
-  if (e == cudaSuccess)
-    e = cudaMemcpyAsync(&flag, bad, sizeof(int), cudaMemcpyDeviceToHost,
-                        pl->stream);
-  int rc = e == cudaSuccess ? so.finish() : 0;
-  cudaFree(bad);
-  if (e != cudaSuccess)
-    return fail(PF_ERR_CUDA, cudaGetErrorString(e));
-  if (rc)
-    return rc;
+  PF_CUDA(cudaMemcpyAsync(&flag, pl->eval_flag, sizeof(int),
+                          cudaMemcpyDeviceToHost, pl->stream));
+  PF_TRY(so.finish());
   if (flag)
     return fail(PF_ERR_INVALID, "pf_field_evaluate: location outside the domain");
   return 0;

@@ -206,6 +206,30 @@ def test_cuda_localize_and_evaluate_match_oracle(m, cells, ext):
 
 
 @pytest.mark.gpu
+def test_cuda_evaluate_on_cell_boundaries(m):
+    """coordsToIndices truncates x * (cells + 1e-6) / ext (fieldtraits.hh:445):
+    locations on cell boundaries and their floating-point neighbours must land
+    in the reference's cell (the kernel's reciprocal fast path falls back to
+    the division there)."""
+    cells, ext = [48, 37], [0.7, 3.0]
+    rng = np.random.default_rng(3)
+    f = rng.standard_normal(tuple(reversed(cells)))
+    pts = []
+    for i in range(2):
+        edges = np.arange(cells[i]) * ext[i] / cells[i]
+        scaled = np.arange(1, cells[i]) * ext[i] / (cells[i] + 1e-6)
+        for e in (edges, scaled):
+            for v in (e, np.nextafter(e, np.inf), np.nextafter(e, -np.inf)[1:]):
+                loc = rng.random((v.size, 2)) * np.asarray(ext)
+                loc[:, i] = v
+                pts.append(loc)
+    loc = np.concatenate(pts)
+    with plan_for(m) as p:
+        got = p.field_evaluate(cells, ext, f, loc, apply_transform=False)
+    assert np.array_equal(got, ol.field_evaluate(cells, ext, f, loc))
+
+
+@pytest.mark.gpu
 def test_cuda_error_behaviour(m):
     with plan_for(m) as p:
         with pytest.raises(m.PfError, match="not implemented"):
