@@ -86,10 +86,34 @@ ABI_SYMBOLS = [
     "pf_field_coarsen",
     "pf_field_localize",
     "pf_field_evaluate",
+    "pf_field_evaluate_trend",
+    "pf_field_bulk_evaluate",
     "pf_device_alloc",
     "pf_device_free",
     "pf_memcpy",
 ]
+
+
+TREND_KINDS = {"mean": 0, "slope": 1, "disk": 2, "block": 3}
+
+
+class PfTrendComponent(C.Structure):
+    """pf_trend_component: kind + (meanVector + shiftVector), trend.hh:601-634"""
+
+    _fields_ = [("kind", C.c_int), ("coeff", C.c_double * 7)]
+
+
+def _trend_array(trend):
+    """[(kind name, [coefficients...]), ...] -> (count, ctypes array or None)"""
+    trend = list(trend or ())
+    if not trend:
+        return 0, None
+    arr = (PfTrendComponent * len(trend))()
+    for a, (kind, coeff) in zip(arr, trend):
+        a.kind = TREND_KINDS[kind]
+        for i, c in enumerate(coeff):
+            a.coeff[i] = float(c)
+    return len(trend), arr
 
 
 class PfDesc(C.Structure):
@@ -202,6 +226,9 @@ def lib():
     L.pf_field_coarsen.argtypes = [vp, C.c_int, up, dp, dp]
     L.pf_field_localize.argtypes = [vp, C.c_int, up, up, up, dp, dp, C.c_double, dp]
     L.pf_field_evaluate.argtypes = [vp, C.c_int, up, dp, dp, sz, dp, C.c_int, dp]
+    tp = C.POINTER(PfTrendComponent)
+    L.pf_field_evaluate_trend.argtypes = [vp, C.c_int, up, dp, dp, sz, dp, C.c_int, tp, C.c_int, dp]
+    L.pf_field_bulk_evaluate.argtypes = [vp, C.c_int, up, dp, dp, C.c_int, tp, C.c_int, dp]
     L.pf_device_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.pf_device_free.argtypes = [vp, vp]
     L.pf_memcpy.argtypes = [vp, vp, vp, sz]
@@ -525,8 +552,9 @@ class Plan:
         _check(lib().pf_field_localize(self._h, d, self._cells(cells), off, gc, ext, cen, radius, _ptr(x)))
         return x
 
-    def field_evaluate(self, cells, extensions, field, locations, apply_transform=True, out=None):
-        """StochasticPart::evaluate + RandomField::evaluate's transform for n x dim locations."""
+    def field_evaluate(self, cells, extensions, field, locations, apply_transform=True, out=None, trend=None):
+        """RandomField::evaluate = T(stochastic + trend) for n x dim locations
+        (stochastic.hh:480-574, trend.hh:601-634,1491-1505, randomfield.hh:585-595)."""
         d = len(cells)
         ext = (C.c_double * 3)(*(list(extensions) + [1.0] * (3 - d)))
         if isinstance(locations, np.ndarray):
@@ -538,7 +566,20 @@ class Plan:
             npts = locations.numel() // d
         if isinstance(field, np.ndarray):
             field = np.ascontiguousarray(field, dtype=np.float64)
-        _check(lib().pf_field_evaluate(self._h, d, self._cells(cells), ext, _ptr(field), npts, _ptr(locations), int(bool(apply_transform)), _ptr(out)))
+        nt, tr = _trend_array(trend)
+        _check(lib().pf_field_evaluate_trend(self._h, d, self._cells(cells), ext, _ptr(field), npts, _ptr(locations), nt, tr, int(bool(apply_transform)), _ptr(out)))
+        return out
+
+    def field_bulk_evaluate(self, cells, extensions, field, trend=None, apply_transform=True, out=None):
+        """RandomField::bulkEvaluate (randomfield.hh:597-631) in one fused sweep."""
+        d = len(cells)
+        ext = (C.c_double * 3)(*(list(extensions) + [1.0] * (3 - d)))
+        if isinstance(field, np.ndarray):
+            field = np.ascontiguousarray(field, dtype=np.float64)
+            if out is None:
+                out = np.empty(tuple(reversed(cells)), dtype=np.float64)
+        nt, tr = _trend_array(trend)
+        _check(lib().pf_field_bulk_evaluate(self._h, d, self._cells(cells), ext, _ptr(field), nt, tr, int(bool(apply_transform)), _ptr(out)))
         return out
 
     # -- vector space -----------------------------------------------------------

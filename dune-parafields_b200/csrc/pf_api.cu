@@ -419,17 +419,112 @@ k_localize(unsigned c0, unsigned c1, unsigned c2,
     }
 }
 
+// TrendPart::evaluate (trend.hh:1491-1505) over TrendComponent::evaluate
+// (trend.hh:601-634); coeff = meanVector + shiftVector.  Explicit _rn
+// operations reproduce the reference's evaluation order without contractions;
+// the disk's exp() may differ from libm by an ulp.
+struct TrendSet
+{
+  int n;
+  int kind[PF_MAX_TREND_COMPONENTS];
+  double coeff[PF_MAX_TREND_COMPONENTS][7];
+};
+
+template <int DIM>
+__device__ __forceinline__ double
+trend_value(const TrendSet& tr, const double* ext, const double* x)
+{
+  double output = 0.;
+  for (int t = 0; t < tr.n; t++) {
+    const double* c = tr.coeff[t];
+    double comp = 0.;
+    switch (tr.kind[t]) {
+      case PF_TREND_MEAN:
+        comp = c[0];
+        break;
+      case PF_TREND_SLOPE:
+#pragma unroll
+        for (int i = 0; i < DIM; i++)
+          comp = __dadd_rn(
+            comp, __dmul_rn(c[i], __dadd_rn(x[i], -__dmul_rn(ext[i], 0.5))));
+        break;
+      case PF_TREND_DISK: {
+        double dist = 0.;
+#pragma unroll
+        for (int i = 0; i < DIM; i++) {
+          const double d = __dadd_rn(x[i], -c[i]);
+          dist = __dadd_rn(dist, __dmul_rn(d, d));
+        }
+        comp = exp(__dmul_rn(__ddiv_rn(-dist, __dmul_rn(c[DIM], c[DIM])),
+                             c[DIM + 1]));
+        break;
+      }
+      default: { // PF_TREND_BLOCK
+        bool inside = true;
+#pragma unroll
+        for (int i = 0; i < DIM; i++)
+          if (fabs(__dadd_rn(x[i], -c[i])) > __dmul_rn(0.5, c[DIM + i]))
+            inside = false;
+        comp = inside ? c[2 * DIM] : 0.;
+      }
+    }
+    output = __dadd_rn(output, comp);
+  }
+  return output;
+}
+
+// RandomField::bulkEvaluate (randomfield.hh:597-631): one fused sweep
+// out = T(field + trend(centre)), centre_j = (i_j + 0.5) * mesh_j with
+// mesh_j = extensions_j / cells_j.  The reference sends every centre through
+// coordsToIndices again; (i + 0.5) (1 + 1e-6 / cells) lies strictly inside
+// (i, i + 1), so that lookup returns cell i itself and is skipped here.
+template <int DIM, bool TREND>
+__global__ void
+k_bulk_evaluate(FieldGeom g, TrendSet tr, const double* __restrict__ field,
+                int kind, double lambda, double* __restrict__ out)
+{
+  constexpr unsigned ROWS = 4; // rows per block step: loads of all rows first
+  const unsigned c0 = g.cells[0], c1 = DIM > 1 ? g.cells[1] : 1,
+                 c2 = DIM > 2 ? g.cells[2] : 1;
+  for (unsigned i2 = blockIdx.z; i2 < c2; i2 += gridDim.z)
+    for (unsigned b1 = blockIdx.y * ROWS; b1 < c1; b1 += gridDim.y * ROWS) {
+      double x[3];
+      x[2] = __dmul_rn((double)i2 + 0.5, g.center[2]); // center[] = mesh here
+      for (unsigned i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < c0;
+           i0 += gridDim.x * blockDim.x) {
+        double v[ROWS];
+#pragma unroll
+        for (unsigned r = 0; r < ROWS; r++)
+          if (b1 + r < c1)
+            v[r] = field[(size_t)c0 * (b1 + r + (size_t)c1 * i2) + i0];
+        if (TREND)
+          x[0] = __dmul_rn((double)i0 + 0.5, g.center[0]);
+#pragma unroll
+        for (unsigned r = 0; r < ROWS; r++)
+          if (b1 + r < c1) {
+            double w = v[r];
+            if (TREND) {
+              x[1] = __dmul_rn((double)(b1 + r) + 0.5, g.center[1]);
+              w = __dadd_rn(w, trend_value<DIM>(tr, g.ext, x));
+            }
+            out[(size_t)c0 * (b1 + r + (size_t)c1 * i2) + i0] =
+              transform_value(w, kind, lambda);
+          }
+      }
+    }
+}
+
 // StochasticPart::evaluate (stochastic.hh:480-574) for a batch of locations
 // on one rank + RandomField::evaluate's value transform (randomfield.hh:
 // 585-595).  coordsToIndices: fieldtraits.hh:440-448.  A location on the
 // upper face of exactly one dimension reads the (zero-filled) overlap, on an
 // edge or corner it steps back into the last cell; anything outside the
 // closed box raises *bad.
-template <int DIM>
+template <int DIM, bool TREND>
 __global__ void
-k_evaluate(FieldGeom g, const double* __restrict__ field, size_t npoints,
-           const double* __restrict__ loc, int kind, double lambda,
-           double* __restrict__ out, int* __restrict__ bad)
+k_evaluate(FieldGeom g, TrendSet tr, const double* __restrict__ field,
+           size_t npoints, const double* __restrict__ loc, int kind,
+           double lambda, double* __restrict__ out, int* __restrict__ bad)
 {
   // U points per thread and step: all coordinate loads are issued before the
   // first dependent gather, which keeps enough bytes in flight per SM
@@ -493,8 +588,12 @@ k_evaluate(FieldGeom g, const double* __restrict__ field, size_t npoints,
         if (state[u] == 2) {
           *bad = 1;
           out[p] = nan("");
-        } else
-          out[p] = transform_value(v[u], kind, lambda);
+        } else {
+          // RandomField::evaluate: T(stochastic + trend)
+          const double w =
+            TREND ? __dadd_rn(v[u], trend_value<DIM>(tr, g.ext, x[u])) : v[u];
+          out[p] = transform_value(w, kind, lambda);
+        }
       }
     }
   }
@@ -3521,17 +3620,44 @@ pf_field_localize(pf_plan* pl, int dim, const unsigned* cells,
   return sd.finish();
 }
 
+namespace {
 int
-pf_field_evaluate(pf_plan* pl, int dim, const unsigned* cells,
-                  const double* extensions, const double* field,
-                  size_t npoints, const double* locations,
-                  int apply_transform, double* out)
+make_trend(const char* who, int dim, int ntrend,
+           const pf_trend_component* trend, TrendSet& tr)
+{
+  tr.n = 0;
+  if (ntrend < 0 || ntrend > PF_MAX_TREND_COMPONENTS)
+    return fail(PF_ERR_INVALID, std::string(who) + ": at most " +
+                                  std::to_string(PF_MAX_TREND_COMPONENTS) +
+                                  " trend components");
+  if (ntrend > 0 && !trend)
+    return fail(PF_ERR_INVALID, std::string(who) + ": null trend");
+  for (int t = 0; t < ntrend; t++) {
+    if (trend[t].kind < PF_TREND_MEAN || trend[t].kind > PF_TREND_BLOCK)
+      return fail(PF_ERR_INVALID, "Trend component type not found!"); // trend.hh:633
+    tr.kind[t] = trend[t].kind;
+    for (int i = 0; i < 7; i++)
+      tr.coeff[t][i] = i < 2 * dim + 1 ? trend[t].coeff[i] : 0.;
+  }
+  tr.n = ntrend;
+  return 0;
+}
+} // namespace
+
+int
+pf_field_evaluate_trend(pf_plan* pl, int dim, const unsigned* cells,
+                        const double* extensions, const double* field,
+                        size_t npoints, const double* locations, int ntrend,
+                        const pf_trend_component* trend, int apply_transform,
+                        double* out)
 {
   PF_TRY(check_plan(pl));
   size_t n = 0;
   PF_TRY(field_dims("pf_field_evaluate", dim, cells, 1, &n));
   if (!extensions)
     return fail(PF_ERR_INVALID, "pf_field_evaluate: null extensions");
+  TrendSet tr;
+  PF_TRY(make_trend("pf_field_evaluate", dim, ntrend, trend, tr));
   if (npoints == 0)
     return 0;
   FieldGeom g{};
@@ -3551,15 +3677,18 @@ pf_field_evaluate(pf_plan* pl, int dim, const unsigned* cells,
   PF_CUDA(cudaMemsetAsync(pl->eval_flag, 0, sizeof(int), pl->stream));
   const int kind = apply_transform ? pl->d.transform : 0;
   const unsigned blocks = grid_for((npoints + 3) / 4);
-  if (dim == 3)
-    k_evaluate<3><<<blocks, 256, 0, pl->stream>>>(
-      g, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev, pl->eval_flag);
-  else if (dim == 2)
-    k_evaluate<2><<<blocks, 256, 0, pl->stream>>>(
-      g, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev, pl->eval_flag);
-  else
-    k_evaluate<1><<<blocks, 256, 0, pl->stream>>>(
-      g, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev, pl->eval_flag);
+#define PF_EVAL(D, T)                                                          \
+  k_evaluate<D, T><<<blocks, 256, 0, pl->stream>>>(                            \
+    g, tr, sf.dev, npoints, sl.dev, kind, pl->d.boxcox_lambda, so.dev,         \
+    pl->eval_flag)
+  if (dim == 3) {
+    if (tr.n) PF_EVAL(3, true); else PF_EVAL(3, false);
+  } else if (dim == 2) {
+    if (tr.n) PF_EVAL(2, true); else PF_EVAL(2, false);
+  } else {
+    if (tr.n) PF_EVAL(1, true); else PF_EVAL(1, false);
+  }
+#undef PF_EVAL
   PF_CUDA(cudaGetLastError());
   pl->launches++;
   int flag = 0;
@@ -3569,6 +3698,60 @@ pf_field_evaluate(pf_plan* pl, int dim, const unsigned* cells,
   if (flag)
     return fail(PF_ERR_INVALID, "pf_field_evaluate: location outside the domain");
   return 0;
+}
+
+int
+pf_field_evaluate(pf_plan* pl, int dim, const unsigned* cells,
+                  const double* extensions, const double* field,
+                  size_t npoints, const double* locations,
+                  int apply_transform, double* out)
+{
+  return pf_field_evaluate_trend(pl, dim, cells, extensions, field, npoints,
+                                 locations, 0, nullptr, apply_transform, out);
+}
+
+int
+pf_field_bulk_evaluate(pf_plan* pl, int dim, const unsigned* cells,
+                       const double* extensions, const double* field,
+                       int ntrend, const pf_trend_component* trend,
+                       int apply_transform, double* out)
+{
+  PF_TRY(check_plan(pl));
+  size_t n = 0;
+  PF_TRY(field_dims("pf_field_bulk_evaluate", dim, cells, 1, &n));
+  if (!extensions)
+    return fail(PF_ERR_INVALID, "pf_field_bulk_evaluate: null extensions");
+  TrendSet tr;
+  PF_TRY(make_trend("pf_field_bulk_evaluate", dim, ntrend, trend, tr));
+  FieldGeom g{};
+  g.dim = dim;
+  for (int i = 0; i < 3; i++) {
+    g.cells[i] = i < dim ? cells[i] : 1;
+    g.gcells[i] = g.cells[i];
+    g.ext[i] = i < dim ? extensions[i] : 1.;
+    // meshsize of bulkEvaluate, randomfield.hh:622
+    g.center[i] = g.ext[i] / static_cast<double>(g.cells[i]);
+  }
+  Staged sf;
+  StagedOut so;
+  PF_TRY(stage_in(pl, field, n, sf));
+  PF_TRY(stage_out(pl, out, n, false, so));
+  const int kind = apply_transform ? pl->d.transform : 0;
+  const dim3 grid = row_grid(g.cells[0], (g.cells[1] + 3) / 4, g.cells[2]);
+#define PF_BULK(D, T)                                                          \
+  k_bulk_evaluate<D, T><<<grid, 256, 0, pl->stream>>>(                         \
+    g, tr, sf.dev, kind, pl->d.boxcox_lambda, so.dev)
+  if (dim == 3) {
+    if (tr.n) PF_BULK(3, true); else PF_BULK(3, false);
+  } else if (dim == 2) {
+    if (tr.n) PF_BULK(2, true); else PF_BULK(2, false);
+  } else {
+    if (tr.n) PF_BULK(1, true); else PF_BULK(1, false);
+  }
+#undef PF_BULK
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return so.finish();
 }
 
 int

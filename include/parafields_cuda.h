@@ -276,6 +276,43 @@ int pf_field_evaluate(pf_plan* plan, int dim, const unsigned* cells,
                       size_t npoints, const double* locations,
                       int apply_transform, double* out);
 
+/* One TrendComponent (trend.hh:601-634): coeff = meanVector + shiftVector.
+ * mean: {m}; slope: {s_0..s_dim-1}, value sum s_i (x_i - ext_i/2);
+ * disk: {c_0..c_dim-1, radius, height}, value exp(-|x-c|^2 / radius^2 * height);
+ * block: {c_0..c_dim-1, w_0..w_dim-1, value} inside |x_i - c_i| <= w_i/2.
+ * The image component (libpng) is not supported. */
+typedef enum pf_trend_kind
+{
+  PF_TREND_MEAN = 0,
+  PF_TREND_SLOPE = 1,
+  PF_TREND_DISK = 2,
+  PF_TREND_BLOCK = 3
+} pf_trend_kind;
+typedef struct pf_trend_component
+{
+  int kind;        /* pf_trend_kind */
+  double coeff[7]; /* up to 2*dim+1 coefficients */
+} pf_trend_component;
+#define PF_MAX_TREND_COMPONENTS 16
+
+/* RandomField::evaluate (randomfield.hh:585-595) for npoints locations:
+ * out = T(stochastic + trend), the trend summed over ntrend components in
+ * order (TrendPart::evaluate, trend.hh:1491-1505).  ntrend = 0 equals
+ * pf_field_evaluate. */
+int pf_field_evaluate_trend(pf_plan* plan, int dim, const unsigned* cells,
+                            const double* extensions, const double* field,
+                            size_t npoints, const double* locations,
+                            int ntrend, const pf_trend_component* trend,
+                            int apply_transform, double* out);
+/* RandomField::bulkEvaluate (randomfield.hh:597-631): the same at the centre
+ * of every cell, (i + 0.5) * (extensions / cells), in one fused sweep
+ * (field read once, no location array); out holds prod(cells) doubles and
+ * may alias field. */
+int pf_field_bulk_evaluate(pf_plan* plan, int dim, const unsigned* cells,
+                           const double* extensions, const double* field,
+                           int ntrend, const pf_trend_component* trend,
+                           int apply_transform, double* out);
+
 /* device memory helpers so that a host-only caller (C++, cgo, ctypes) can
  * keep fields resident in HBM */
 int pf_device_alloc(pf_plan* plan, size_t bytes, void** ptr);

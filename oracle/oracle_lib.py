@@ -31,6 +31,27 @@ ANISO = {"none": 0, "axiparallel": 1, "geometric": 2}
 TRANSFORM = {"none": 0, "logNormal": 1, "foldedNormal": 2, "sign": 3, "boxCox": 4}
 
 
+TREND = {"mean": 0, "slope": 1, "disk": 2, "block": 3}
+
+
+class OrcTrend(C.Structure):
+    """one TrendComponent: kind + (meanVector + shiftVector), trend.hh:601-634"""
+
+    _fields_ = [("kind", C.c_int), ("coeff", C.c_double * 7)]
+
+
+def trend_array(trend, cls=None):
+    """[(kind name, [coefficients...]), ...] -> ctypes array"""
+    cls = cls or OrcTrend
+    arr = (cls * max(len(trend), 1))()
+    for a, (kind, coeff) in zip(arr, trend):
+        a.kind = TREND[kind]
+        assert len(coeff) <= 7
+        for i, c in enumerate(coeff):
+            a.coeff[i] = float(c)
+    return arr
+
+
 class OrcCfg(C.Structure):
     _fields_ = [
         ("dim", C.c_int),
@@ -93,6 +114,9 @@ def lib():
         L.orc_field_coarsen.argtypes = [C.c_int, up, dp, dp]
         L.orc_field_localize.argtypes = [C.c_int, up, up, up, dp, dp, C.c_double, dp]
         L.orc_field_evaluate.argtypes = [C.c_int, up, dp, dp, C.c_size_t, dp, C.c_int, C.c_double, dp]
+        tp = C.POINTER(OrcTrend)
+        L.orc_field_evaluate_trend.argtypes = [C.c_int, up, dp, dp, C.c_size_t, dp, C.c_int, tp, C.c_int, C.c_double, dp]
+        L.orc_field_bulk_evaluate.argtypes = [C.c_int, up, dp, dp, C.c_int, tp, C.c_int, C.c_double, dp]
         _lib = L
     return _lib
 
@@ -325,3 +349,24 @@ def field_evaluate(cells, extensions, field, locations, transform="none", boxcox
     out = np.empty(loc.shape[0])
     _check(lib().orc_field_evaluate(d, _up(cells), _dp(ext), _dp(f), loc.shape[0], _dp(loc), TRANSFORM[transform], boxcox_lambda, _dp(out)))
     return out
+
+
+def field_evaluate_trend(cells, extensions, field, locations, trend, transform="none", boxcox_lambda=0.0):
+    """RandomField::evaluate = T(stochastic + trend), randomfield.hh:585-595."""
+    d = len(cells)
+    f = np.ascontiguousarray(field, dtype=np.float64).ravel()
+    loc = np.ascontiguousarray(locations, dtype=np.float64).reshape(-1, d)
+    ext = np.asarray(extensions, dtype=np.float64)
+    out = np.empty(loc.shape[0])
+    _check(lib().orc_field_evaluate_trend(d, _up(cells), _dp(ext), _dp(f), loc.shape[0], _dp(loc), len(trend), trend_array(trend), TRANSFORM[transform], boxcox_lambda, _dp(out)))
+    return out
+
+
+def field_bulk_evaluate(cells, extensions, field, trend=(), transform="none", boxcox_lambda=0.0):
+    """RandomField::bulkEvaluate, randomfield.hh:597-631."""
+    d = len(cells)
+    f = np.ascontiguousarray(field, dtype=np.float64).ravel()
+    ext = np.asarray(extensions, dtype=np.float64)
+    out = np.empty(f.size)
+    _check(lib().orc_field_bulk_evaluate(d, _up(cells), _dp(ext), _dp(f), len(trend), trend_array(list(trend)), TRANSFORM[transform], boxcox_lambda, _dp(out)))
+    return out.reshape(tuple(reversed(cells)))

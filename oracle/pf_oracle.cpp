@@ -1273,6 +1273,104 @@ orc_field_evaluate(int dim, const unsigned* cells, const double* extensions,
   ORC_CATCH
 }
 
+// TrendComponent::evaluate (trend.hh:601-634) summed by TrendPart::evaluate
+// (trend.hh:1491-1505).  A component is (kind, coeff[7]) with coeff =
+// meanVector + shiftVector; kinds 0 mean, 1 slope, 2 disk, 3 block.  The image
+// component (libpng) is out of scope.
+struct OrcTrend
+{
+  int kind;
+  double coeff[7];
+};
+
+static double
+trend_value(int dim, const double* extensions, int ntrend,
+            const OrcTrend* trend, const double* x)
+{
+  double output = 0.;
+  for (int t = 0; t < ntrend; t++) {
+    const double* c = trend[t].coeff;
+    double comp = 0.;
+    switch (trend[t].kind) {
+      case 0:
+        comp = c[0];
+        break;
+      case 1:
+        for (int i = 0; i < dim; i++)
+          comp += c[i] * (x[i] - extensions[i] / 2.);
+        break;
+      case 2: {
+        double distSquared = 0.;
+        for (int i = 0; i < dim; i++)
+          distSquared += std::pow(x[i] - c[i], 2);
+        comp = std::exp(-distSquared / std::pow(c[dim], 2) * c[dim + 1]);
+        break;
+      }
+      case 3: {
+        bool inside = true;
+        for (int i = 0; i < dim; i++)
+          if (std::abs(x[i] - c[i]) > 0.5 * c[dim + i])
+            inside = false;
+        comp = inside ? c[2 * dim] : 0.;
+        break;
+      }
+      default:
+        throw std::runtime_error{ "Trend component type not found!" };
+    }
+    output += comp;
+  }
+  return output;
+}
+
+// RandomField::evaluate (randomfield.hh:585-595): T(stochastic + trend)
+int
+orc_field_evaluate_trend(int dim, const unsigned* cells,
+                         const double* extensions, const double* field,
+                         size_t npoints, const double* loc, int ntrend,
+                         const OrcTrend* trend, int transform,
+                         double boxcox_lambda, double* out)
+{
+  int rc = orc_field_evaluate(dim, cells, extensions, field, npoints, loc, 0,
+                              0., out);
+  if (rc != 0)
+    return rc;
+  ORC_TRY
+  for (size_t p = 0; p < npoints; p++)
+    out[p] = out[p] + trend_value(dim, extensions, ntrend, trend, loc + p * dim);
+  if (transform != 0)
+    return orc_transform(transform, boxcox_lambda, npoints, out);
+  ORC_CATCH
+}
+
+// RandomField::bulkEvaluate (randomfield.hh:597-631): evaluate at the centre
+// of every cell, locations built as (i + 0.5) * (extensions / cells)
+int
+orc_field_bulk_evaluate(int dim, const unsigned* cells,
+                        const double* extensions, const double* field,
+                        int ntrend, const OrcTrend* trend, int transform,
+                        double boxcox_lambda, double* out)
+{
+  ORC_TRY
+  size_t bound[3] = { 1, 1, 1 };
+  size_t n = 1;
+  for (int i = 0; i < dim; i++) {
+    bound[i] = cells[i];
+    n *= cells[i];
+  }
+  std::vector<double> loc(n * dim);
+  for (size_t index = 0; index < n; index++) {
+    size_t idx[3] = { 0, 0, 0 };
+    indexToIndices(index, idx, bound, dim);
+    for (int j = 0; j < dim; j++) {
+      const double meshsize = extensions[j] / static_cast<double>(cells[j]);
+      loc[index * dim + j] = (static_cast<double>(idx[j]) + 0.5) * meshsize;
+    }
+  }
+  return orc_field_evaluate_trend(dim, cells, extensions, field, n, loc.data(),
+                                  ntrend, trend, transform, boxcox_lambda, out);
+  ORC_CATCH
+}
+
 int
 orc_max_threads()
 {

@@ -46,7 +46,7 @@ def lib():
     return _lib
 
 
-def ini_text(cells, covariance="exponential", corr_length=0.05, extensions=None, variance=1.0, anisotropy="none", factor=None, approximate=False, periodic=False, transform=None, boxcox_lambda=None, cg_iterations=None, cov_params=None, cache_inv=False, cache_inv_root=False, threshold=None):
+def ini_text(cells, covariance="exponential", corr_length=0.05, extensions=None, variance=1.0, anisotropy="none", factor=None, approximate=False, periodic=False, transform=None, boxcox_lambda=None, cg_iterations=None, cov_params=None, cache_inv=False, cache_inv_root=False, threshold=None, extra=None):
     """ini file contents in the reference's own keys."""
     dim = len(cells)
     ext = extensions or [1.0] * dim
@@ -77,6 +77,8 @@ def ini_text(cells, covariance="exponential", corr_length=0.05, extensions=None,
         lines.append("cacheInvRootMatvec = 1")
     if boxcox_lambda is not None:
         lines += ["[transform]", "boxCoxLambda = %r" % float(boxcox_lambda)]
+    if extra:
+        lines.append(extra.strip())
     return "\n".join(lines) + "\n"
 
 

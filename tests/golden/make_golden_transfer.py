@@ -31,6 +31,53 @@ CASES = {
 }
 SEED = 20240611
 
+# trend part (trend.hh): ini sections of the reference with zero variance, so
+# that meanVector + shiftVector = mean; the same components as
+# (kind, coefficients) for the C ABI
+TREND_CASES = {
+    "2d": dict(
+        case=dict(cells=[16, 12], covariance="exponential", corr_length=0.2, extensions=[1.0, 2.0]),
+        ini="[mean]\nmean = 0.7\nvariance = 0\n[slope]\nmean = 0.3 -0.2\nvariance = 0 0\n[disk0]\nmean = 0.4 1.1 0.2 1.5\nvariance = 0 0 0 0\n[block0]\nmean = 0.7 0.3 0.3 0.2 -2.0\nvariance = 0 0 0 0 0\n[block1]\nmean = 0.1 1.7 0.15 0.35 4.0\nvariance = 0 0 0 0 0\n",
+        trend=[("mean", [0.7]), ("slope", [0.3, -0.2]), ("disk", [0.4, 1.1, 0.2, 1.5]), ("block", [0.7, 0.3, 0.3, 0.2, -2.0]), ("block", [0.1, 1.7, 0.15, 0.35, 4.0])],
+    ),
+    "3d_lognormal": dict(
+        case=dict(cells=[8, 6, 10], covariance="exponential", corr_length=0.2, transform="logNormal"),
+        ini="[mean]\nmean = -0.5\nvariance = 0\n[slope]\nmean = 0.3 -0.2 0.9\nvariance = 0 0 0\n[disk0]\nmean = 0.4 0.6 0.5 0.3 0.8\nvariance = 0 0 0 0 0\n[disk1]\nmean = 0.9 0.1 0.2 0.15 0.4\nvariance = 0 0 0 0 0\n[block0]\nmean = 0.5 0.5 0.5 0.4 0.6 0.2 1.25\nvariance = 0 0 0 0 0 0 0\n",
+        trend=[("mean", [-0.5]), ("slope", [0.3, -0.2, 0.9]), ("disk", [0.4, 0.6, 0.5, 0.3, 0.8]), ("disk", [0.9, 0.1, 0.2, 0.15, 0.4]), ("block", [0.5, 0.5, 0.5, 0.4, 0.6, 0.2, 1.25])],
+    ),
+    "1d": dict(
+        case=dict(cells=[64], covariance="exponential", corr_length=0.1, extensions=[3.0]),
+        ini="[mean]\nmean = 2.0\nvariance = 0\n[slope]\nmean = -0.75\nvariance = 0\n[disk0]\nmean = 1.0 0.5 2.0\nvariance = 0 0 0\n[block0]\nmean = 2.5 0.5 3.0\nvariance = 0 0 0\n",
+        trend=[("mean", [2.0]), ("slope", [-0.75]), ("disk", [1.0, 0.5, 2.0]), ("block", [2.5, 0.5, 3.0])],
+    ),
+}
+
+
+def trend_fixtures():
+    import json
+
+    for name, t in TREND_CASES.items():
+        rng = np.random.default_rng(100 + len(name))
+        case = t["case"]
+        cells = case["cells"]
+        ext = case.get("extensions", [1.0] * len(cells))
+        r = rl.Reference(cells, extra=t["ini"], **case_kw(case))
+        field = r.generate(SEED)
+        loc = locations(cells, ext, rng)
+        np.savez(
+            os.path.join(HERE, "trend_%s.npz" % name),
+            ini=r.text,
+            cells=np.array(cells),
+            extensions=np.array(ext),
+            transform=case.get("transform", "none"),
+            trend=json.dumps(t["trend"]),
+            field=field,
+            bulk=r.bulk_evaluate(),
+            locations=loc,
+            values=r.evaluate(loc),
+        )
+        print("trend", name, field.shape)
+
 
 def locations(cells, ext, rng):
     d = len(cells)
@@ -84,6 +131,7 @@ def main():
             rough_coarsened=coarse,
         )
         print(name, field.shape, "->", refined.shape, "->", back.shape, "| rough ->", coarse.shape)
+    trend_fixtures()
 
 
 def case_kw(case):

@@ -282,3 +282,92 @@ def test_cuda_full_size_properties(m):
         p.field_evaluate([k, k, k], [1.0, 1.0, 1.0], fine, loc, apply_transform=False, out=out)
         p.synchronize()
         assert torch.equal(out.reshape(k, k), fine[37])
+
+
+# ---------------------------------------------------------------------------
+# trend part + bulkEvaluate (trend.hh:601-634,1491-1505; randomfield.hh:585-631)
+# ---------------------------------------------------------------------------
+TREND_FIXTURES = sorted(glob.glob(os.path.join(HERE, "golden", "trend_*.npz")))
+
+
+def load_trend(f):
+    import json
+
+    g, cells, ext, transform = load(f)
+    trend = [(k, c) for k, c in json.loads(str(g["trend"]))]
+    return g, cells, ext, transform, trend
+
+
+def close(a, b):
+    """exp() of the disk component / logNormal: libm against the device."""
+    return rel(a, b) < EXP_TOL
+
+
+def test_trend_fixtures_present():
+    assert len(TREND_FIXTURES) == 3
+
+
+@pytest.mark.parametrize("fixture", TREND_FIXTURES, ids=lambda f: os.path.basename(f)[:-4])
+def test_oracle_trend_matches_reference_fixtures(fixture):
+    g, cells, ext, transform, trend = load_trend(fixture)
+    bulk = ol.field_bulk_evaluate(cells, ext, g["field"], trend, transform)
+    assert np.array_equal(bulk, g["bulk"])
+    v = ol.field_evaluate_trend(cells, ext, g["field"], g["locations"], trend, transform)
+    assert np.array_equal(v, g["values"])
+    # the trend really contributes
+    assert rel(ol.field_bulk_evaluate(cells, ext, g["field"], [], transform), g["bulk"]) > 1e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fixture", TREND_FIXTURES, ids=lambda f: os.path.basename(f)[:-4])
+def test_cuda_trend_matches_reference_fixtures(m, fixture):
+    g, cells, ext, transform, trend = load_trend(fixture)
+    with plan_for(m, transform) as p:
+        assert close(p.field_bulk_evaluate(cells, ext, g["field"], trend), g["bulk"])
+        assert close(p.field_evaluate(cells, ext, g["field"], g["locations"], trend=trend), g["values"])
+        # components without exp() are bit-exact
+        plain = [t for t in trend if t[0] != "disk"]
+        got = p.field_bulk_evaluate(cells, ext, g["field"], plain, apply_transform=False)
+        assert np.array_equal(got, ol.field_bulk_evaluate(cells, ext, g["field"], plain))
+        got = p.field_evaluate(cells, ext, g["field"], g["locations"], apply_transform=False, trend=plain)
+        assert np.array_equal(got, ol.field_evaluate_trend(cells, ext, g["field"], g["locations"], plain))
+        # in place
+        buf = g["field"].copy()
+        p.field_bulk_evaluate(cells, ext, buf, trend, out=buf)
+        assert close(buf, g["bulk"])
+
+
+@pytest.mark.gpu
+def test_cuda_trend_errors(m):
+    with plan_for(m) as p:
+        f = np.zeros((4, 4))
+        with pytest.raises(m.PfError, match="at most 16 trend components"):
+            p.field_bulk_evaluate([4, 4], [1.0, 1.0], f, [("mean", [1.0])] * 17)
+        d = m.PfTrendComponent()
+        d.kind = 9
+        import ctypes as C
+
+        rc = m.lib().pf_field_bulk_evaluate(p._h, 2, p._cells([4, 4]), (C.c_double * 3)(1, 1, 1), f.ctypes.data, 1, C.byref(d), 0, f.ctypes.data)
+        assert rc == m.PF_ERR_INVALID and m.lib().pf_last_error() == b"Trend component type not found!"
+
+
+@pytest.mark.gpu
+def test_cuda_bulk_evaluate_full_size(m):
+    """512^3 (K3's cells): the fused sweep against torch on the same buffer."""
+    import torch
+
+    n = 512
+    dev = torch.device("cuda")
+    gen = torch.Generator(device=dev).manual_seed(11)
+    f = torch.randn((n, n, n), dtype=torch.float64, device=dev, generator=gen)
+    out = torch.empty_like(f)
+    with plan_for(m, "logNormal") as p:
+        p.field_bulk_evaluate([n] * 3, [1.0] * 3, f, out=out)
+        p.synchronize()
+        assert float(((out - torch.exp(f)).abs() / torch.exp(f)).max()) < 1e-15
+        trend = [("mean", [0.25]), ("slope", [1.0, 2.0, -3.0])]
+        p.field_bulk_evaluate([n] * 3, [1.0] * 3, f, trend, apply_transform=False, out=out)
+        p.synchronize()
+        c = (torch.arange(n, dtype=torch.float64, device=dev) + 0.5) * (1.0 / n) - 0.5
+        want = f + (0.25 + ((1.0 * c)[None, None, :] + (2.0 * c)[None, :, None] + (-3.0 * c)[:, None, None]))
+        assert float((out - want).abs().max()) < 1e-14
