@@ -140,6 +140,12 @@ class PfDesc(C.Structure):
         ("device", C.c_int),
         ("n_ranks", C.c_int),
         ("rank", C.c_int),
+        ("periodization", C.c_int),
+        ("sigmoid", C.c_int),
+        ("sigmoid_combine", C.c_int),
+        ("sigmoid_start", C.c_double),
+        ("sigmoid_end", C.c_double),
+        ("merge_recursions", C.c_uint),
     ]
 
 
@@ -278,6 +284,12 @@ def make_desc(
     cov_param=(0.0, 0.0),
     n_ranks=1,
     rank=0,
+    periodization="classical",
+    sigmoid="smoothstep",
+    sigmoid_combine="radialPlus",
+    sigmoid_start=1.0,
+    sigmoid_end=None,
+    merge_recursions=99,
 ):
     d = PfDesc()
     lib().pf_desc_default(C.byref(d))
@@ -312,6 +324,13 @@ def make_desc(
     d.device = device
     d.n_ranks = int(n_ranks)
     d.rank = int(rank)
+    # embedding.periodization / sigmoid, stochastic.sigmoidCombine (matrix.hh:530-590,662-719)
+    d.periodization = {"classical": 0, "merge": 1}[periodization]
+    d.sigmoid = {"smoothstep": 0, "smooth": 1}[sigmoid]
+    d.sigmoid_combine = {"radialPlus": 0, "radial": 1, "tensor": 2}[sigmoid_combine]
+    d.sigmoid_start = sigmoid_start
+    d.sigmoid_end = -1.0 if sigmoid_end is None else sigmoid_end
+    d.merge_recursions = merge_recursions
     return d
 
 

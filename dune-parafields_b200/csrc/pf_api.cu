@@ -825,6 +825,34 @@ grid_for(size_t n, int threads = 256)
 
 } // namespace
 
+// embedding.mergeRecursions with the magic value 99 (matrix.hh:691-719);
+// ~0u = "magic recursions value 99 not implemented for choice of covariance"
+static unsigned
+merge_recursions(const pf_desc& d, int dim)
+{
+  if (d.periodization != 1)
+    return 0;
+  if (d.merge_recursions != 99)
+    return d.merge_recursions;
+  switch (d.covariance) {
+    case PF_COV_MATERN:
+      return (unsigned)std::floor(d.cov_param[0] * 2. + double(dim) / 2.);
+    case PF_COV_GAMMA_EXPONENTIAL:
+    case PF_COV_GENERALIZED_CAUCHY:
+      return (unsigned)std::floor(d.cov_param[0] + double(dim) / 2.);
+    case PF_COV_EXPONENTIAL:
+      return 2;
+    case PF_COV_MATERN32:
+      return 4;
+    case PF_COV_MATERN52:
+      return 6;
+    case PF_COV_CAUCHY:
+      return 3;
+    default:
+      return ~0u;
+  }
+}
+
 // ===========================================================================
 // plan
 // ===========================================================================
@@ -1084,7 +1112,16 @@ plan_resize(pf_plan* pl)
     cv.h[i] = d.extensions[i] / d.cells[i];
     cv.half[i] = 0.5 * d.extensions[i] * pl->factor;
     cv.period[i] = d.extensions[i] * pl->factor;
+    cv.ext[i] = d.extensions[i];
   }
+  // embedding.periodization = merge, matrix.hh:662-719
+  cv.periodization = d.periodization;
+  cv.sigmoid = d.sigmoid;
+  cv.combine = d.sigmoid_combine;
+  cv.factor = pl->factor;
+  cv.s_start = d.sigmoid_start;
+  cv.s_end = d.sigmoid_end < 0. ? pl->factor - 1. : d.sigmoid_end;
+  cv.recursions = merge_recursions(d, pl->dim);
   const int dim = pl->dim;
   if (d.anisotropy == PF_ANISO_NONE) {
     cv.g[0] = 1. / d.corr_length[0];
@@ -2645,6 +2682,9 @@ pf_desc_default(pf_desc* d)
   d->threshold = 1e-14;        // matrix.hh:284
   d->cg_iterations = 100;      // fieldtraits.hh:178
   d->device = -1;
+  d->sigmoid_start = 1.;       // matrix.hh:687-688
+  d->sigmoid_end = -1.;        // factor - 1, matrix.hh:689-690
+  d->merge_recursions = 99;    // matrix.hh:691-692
 }
 
 int
@@ -2666,6 +2706,22 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
                 "\"geometric\"");
   if (desc->transform < 0 || desc->transform > 4)
     return fail(PF_ERR_INVALID, "transform type not known");
+  // matrix.hh:530-590, 671-680, 715-718
+  if (desc->periodization < 0 || desc->periodization > 1)
+    return fail(PF_ERR_INVALID,
+                "embedding.periodization must be \"classical\" or \"merge\" "
+                "(fold and cofold need GSL quadrature and are not built)");
+  if (desc->periodization == 1) {
+    if (desc->sigmoid < 0 || desc->sigmoid > 1)
+      return fail(PF_ERR_INVALID,
+                  "embedding.sigmoid must be \"smooth\" or \"smoothstep\"");
+    if (desc->sigmoid_combine < 0 || desc->sigmoid_combine > 2)
+      return fail(PF_ERR_INVALID,
+                  "sigmoidCombine must be tensor, radial or radialPlus");
+    if (merge_recursions(*desc, desc->dim) == ~0u)
+      return fail(PF_ERR_INVALID, "magic recursions value 99 not implemented "
+                                  "for choice of covariance");
+  }
   // covariance.hh argument checks
   if (desc->covariance == PF_COV_CUBIC && desc->dim == 3)
     return fail(PF_ERR_INVALID, "cubic covariance only applicable in 1D or 2D");

@@ -38,6 +38,14 @@ struct CovParams
   double half[3];    // 0.5 * ext * factor  (mirror threshold, matrix.hh:640)
   double period[3];  // ext * factor
   double g[9];       // geometry matrix already inverted (covariance.hh:17-136)
+  // merge periodisation (matrix.hh:662-787)
+  int periodization; // 0 classical, 1 merge
+  int sigmoid;       // 0 smoothstep, 1 smooth
+  int combine;       // 0 radialPlus, 1 radial, 2 tensor
+  unsigned recursions;
+  unsigned factor;
+  double s_start, s_end;
+  double ext[3];
 };
 
 // kernel kinds (dispatch ids of pf_launch)

@@ -251,10 +251,118 @@ cov_function(const CovParams& c, const double* x)
   return 0.;
 }
 
+// geometry transform h' = A h (covariance.hh:17-136), A already inverted
+__device__ __forceinline__ void
+geo_transform(const CovParams& c, const double* coord, double* tc)
+{
+  if (c.aniso == 0) {
+    for (int i = 0; i < c.dim; i++)
+      tc[i] = c.g[0] * coord[i];
+  } else if (c.aniso == 1) {
+    for (int i = 0; i < c.dim; i++)
+      tc[i] = c.g[i] * coord[i];
+  } else {
+    for (int i = 0; i < c.dim; i++) {
+      tc[i] = 0.;
+      for (int j = 0; j < c.dim; j++)
+        tc[i] += c.g[i * c.dim + j] * coord[j];
+    }
+  }
+}
+
+// SmoothSigmoid (covariance.hh:145-176) / SmoothstepSigmoid on
+// ClampingSigmoid (covariance.hh:202-275)
+static __device__ __noinline__ double
+sigmoid_value(const CovParams& c, double oneEdge, double zeroEdge, double x)
+{
+  const double ax = fabs(x);
+  if (c.sigmoid == 1) {
+    if (ax < oneEdge)
+      return 1.;
+    if (ax > zeroEdge)
+      return 0.;
+    const double x1 = (zeroEdge - ax) / (zeroEdge - oneEdge);
+    const double x2 = (ax - oneEdge) / (zeroEdge - oneEdge);
+    const double t1 = x1 > 0. ? exp(-1. / x1) : 0.;
+    const double t2 = x2 > 0. ? exp(-1. / x2) : 0.;
+    return t1 / (t1 + t2);
+  }
+  double x1;
+  if (ax < oneEdge)
+    x1 = 1.;
+  else if (ax > zeroEdge)
+    x1 = 0.;
+  else
+    x1 = (zeroEdge - ax) / (zeroEdge - oneEdge);
+  const double x2 = 2. * x1 - 1.;
+  double normalization = 1., addition = 1., output = 1.;
+  for (unsigned i = 1; i <= c.recursions; i++) {
+    output *= 2. * i;
+    addition *= 1 - x2 * x2;
+    output += addition;
+    output /= 2. * i + 1.;
+    normalization *= 2. * i / (2. * i + 1.);
+  }
+  output *= x2 / normalization;
+  output += 1.;
+  output /= 2.;
+  return output;
+}
+
+// Matrix::computeMatrixEntriesWithMerge (matrix.hh:662-787): 2^dim mirrored
+// copies of the covariance, each tapered by a sigmoid; what the tapers leave
+// is filled with the covariance of the far corner (radialPlus)
+static __device__ __noinline__ double
+cov_torus_merge(const CovParams& c, unsigned i0, unsigned i1, unsigned i2)
+{
+  const unsigned idx[3] = { i0, i1, i2 };
+  double trueCoord[3], mirrorCoord[3], tc[3];
+  double constValue = 0.;
+  if (c.combine == 0) {
+    for (int i = 0; i < c.dim; i++)
+      trueCoord[i] = c.ext[i] * c.factor / 2.;
+    geo_transform(c, trueCoord, tc);
+    constValue = cov_function(c, tc);
+  }
+  for (int i = 0; i < c.dim; i++)
+    trueCoord[i] = idx[i] * c.h[i];
+  const double eps = 1e-10;
+  const double sqrtDim = sqrt((double)c.dim);
+  const bool radial = c.combine != 2 && sqrtDim < c.factor / 2.;
+  double value = 0., remainder = 1.;
+  for (unsigned j = 0; j < (1u << c.dim); j++) {
+    for (int i = 0; i < c.dim; i++)
+      mirrorCoord[i] =
+        (j & (1u << i)) ? c.ext[i] * c.factor - trueCoord[i] : trueCoord[i];
+    double dampening = 1.;
+    if (radial) {
+      double radius = 0.;
+      for (int i = 0; i < c.dim; i++)
+        radius += (mirrorCoord[i] * mirrorCoord[i]) / (c.ext[i] * c.ext[i]);
+      radius = sqrt(radius);
+      dampening = sigmoid_value(c, c.s_start * sqrtDim - eps,
+                                c.factor - (c.factor - c.s_end) * sqrtDim + eps,
+                                radius);
+    } else {
+      for (int i = 0; i < c.dim; i++)
+        dampening *= sigmoid_value(c, c.ext[i] * c.s_start - eps,
+                                   c.ext[i] * c.s_end + eps, mirrorCoord[i]);
+    }
+    if (dampening < eps)
+      continue;
+    remainder -= dampening;
+    geo_transform(c, mirrorCoord, tc);
+    value += cov_function(c, tc) * dampening;
+  }
+  return value + constValue * remainder;
+}
+
 // torus cell (i0,i1,i2) -> covariance value
 __device__ __forceinline__ double
 cov_torus(const CovParams& c, unsigned i0, unsigned i1, unsigned i2)
 {
+  if (c.periodization == 1)
+    return cov_torus_merge(c, i0, i1, i2);
   double coord[3], tc[3];
   const unsigned idx[3] = { i0, i1, i2 };
   for (int i = 0; i < c.dim; i++) {

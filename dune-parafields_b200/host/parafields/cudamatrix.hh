@@ -208,6 +208,54 @@ public:
         : 0;
     d.max_factor = config.template get<unsigned int>("cuda.maxFactor", 0);
     d.device = config.template get<int>("cuda.device", -1);
+
+    // embedding.periodization / embedding.sigmoid / stochastic.sigmoidCombine
+    // (matrix.hh:530-590, 669-692); fold and cofold need GSL quadrature
+    const std::string periodization =
+      config.template get<std::string>("embedding.periodization", "classical");
+    if (periodization == "classical")
+      d.periodization = 0;
+    else if (periodization == "merge")
+      d.periodization = 1;
+    else if (periodization == "fold" || periodization == "cofold")
+      throw std::runtime_error{
+        "CudaMatrix: embedding.periodization fold / cofold is not built "
+        "(GSL quadrature); use classical or merge"
+      };
+    else
+      throw std::runtime_error{
+        "stochastic.periodization must be \"classical\", \"merge\", \"fold\", "
+        "or \"cofold\""
+      }; // matrix.hh:588-591
+    if (d.periodization == 1) {
+      const std::string sigmoid =
+        config.template get<std::string>("embedding.sigmoid", "smoothstep");
+      if (sigmoid == "smooth")
+        d.sigmoid = 1;
+      else if (sigmoid == "smoothstep")
+        d.sigmoid = 0;
+      else
+        throw std::runtime_error{
+          "embedding.sigmoid must be \"smooth\" or \"smoothstep\""
+        };
+      const std::string combine = config.template get<std::string>(
+        "stochastic.sigmoidCombine", "radialPlus");
+      if (combine == "radialPlus")
+        d.sigmoid_combine = 0;
+      else if (combine == "radial")
+        d.sigmoid_combine = 1;
+      else if (combine == "tensor")
+        d.sigmoid_combine = 2;
+      else
+        throw std::runtime_error{
+          "sigmoidCombine must be tensor, radial or radialPlus"
+        };
+      d.sigmoid_start = config.template get<RF>("embedding.sigmoidStart", 1.);
+      d.sigmoid_end = config.template get<RF>(
+        "embedding.sigmoidEnd", (*traits).embeddingFactor - 1.);
+      d.merge_recursions =
+        config.template get<unsigned int>("embedding.mergeRecursions", 99);
+    }
     // the reference's R2C-matrix census quirk is
     // kept so that the clamp pattern matches the reference
     d.census_quirk = (d.anisotropy == PF_ANISO_GEOMETRIC) ? 1 : 0;

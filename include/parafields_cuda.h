@@ -132,6 +132,20 @@ typedef struct pf_desc
      layers; 0 or 1 = single GPU */
   int n_ranks;
   int rank;
+  /* embedding.periodization (matrix.hh:530-572): 0 classical circulant
+     embedding (mirroring, matrix.hh:624-648), 1 merge = 2^dim mirrored copies
+     tapered by sigmoids (computeMatrixEntriesWithMerge, matrix.hh:662-787).
+     fold / cofold need GSL quadrature and are not built. */
+  int periodization;
+  int sigmoid;              /* embedding.sigmoid: 0 smoothstep (default),
+                               1 smooth (covariance.hh:145-275)              */
+  int sigmoid_combine;      /* stochastic.sigmoidCombine: 0 radialPlus
+                               (default), 1 radial, 2 tensor                  */
+  double sigmoid_start;     /* embedding.sigmoidStart (1)                     */
+  double sigmoid_end;       /* embedding.sigmoidEnd; < 0 = factor - 1         */
+  unsigned merge_recursions; /* embedding.mergeRecursions; 99 = the
+                               reference's per-covariance heuristic
+                               (matrix.hh:693-719)                            */
 } pf_desc;
 
 /* eigenvalue census, matrix.hh:283-320 */

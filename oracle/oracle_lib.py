@@ -52,6 +52,27 @@ def trend_array(trend, cls=None):
     return arr
 
 
+PERIODIZATION = {"classical": 0, "merge": 1}
+SIGMOID = {"smoothstep": 0, "smooth": 1}
+SIGMOID_COMBINE = {"radialPlus": 0, "radial": 1, "tensor": 2}
+
+
+def merge_recursions_for(covariance, dim, recursions=99, p0=0.0):
+    """embedding.mergeRecursions with the magic value 99, matrix.hh:693-719"""
+    import math
+
+    if recursions != 99:
+        return recursions
+    if covariance == "matern":
+        return int(math.floor(p0 * 2.0 + dim / 2.0))
+    if covariance in ("gammaExponential", "generalizedCauchy"):
+        return int(math.floor(p0 + dim / 2.0))
+    table = {"exponential": 2, "matern32": 4, "matern52": 6, "cauchy": 3}
+    if covariance not in table:
+        raise RuntimeError("magic recursions value 99 not implemented for choice of covariance")
+    return table[covariance]
+
+
 class OrcCfg(C.Structure):
     _fields_ = [
         ("dim", C.c_int),
@@ -71,6 +92,12 @@ class OrcCfg(C.Structure):
         ("transposed", C.c_int),
         ("cg_iterations", C.c_uint),
         ("threads", C.c_int),
+        ("periodization", C.c_int),
+        ("sigmoid", C.c_int),
+        ("sigmoid_combine", C.c_int),
+        ("sigmoid_start", C.c_double),
+        ("sigmoid_end", C.c_double),
+        ("recursions", C.c_uint),
     ]
 
 
@@ -159,6 +186,12 @@ class Oracle:
         p0=0.0,
         p1=0.0,
         periodic=False,
+        periodization="classical",
+        sigmoid="smoothstep",
+        sigmoid_combine="radialPlus",
+        sigmoid_start=1.0,
+        sigmoid_end=None,
+        merge_recursions=99,
     ):
         if periodic:
             factor = 1  # fieldtraits.hh:196-202
@@ -196,6 +229,12 @@ class Oracle:
         cfg.transposed = int(dim == 3) if transposed is None else int(transposed)
         cfg.cg_iterations = cg_iterations
         cfg.threads = threads
+        cfg.periodization = PERIODIZATION[periodization]
+        cfg.sigmoid = SIGMOID[sigmoid]
+        cfg.sigmoid_combine = SIGMOID_COMBINE[sigmoid_combine]
+        cfg.sigmoid_start = sigmoid_start
+        cfg.sigmoid_end = factor - 1.0 if sigmoid_end is None else sigmoid_end
+        cfg.recursions = merge_recursions_for(covariance, dim, merge_recursions, p0) if periodization == "merge" else 0
         self.cfg = cfg
         self.matrix_backend = matrix_backend
         self.field_backend = field_backend

@@ -69,6 +69,13 @@ struct OrcCfg
                         // (fieldtraits.hh:226-264): 3D -> 1, else 0
   unsigned cg_iterations;
   int threads;          // OpenMP threads for the FFT loops (1 = reference)
+  // embedding.periodization = merge (matrix.hh:530-572,662-787)
+  int periodization;    // 0 classical, 1 merge
+  int sigmoid;          // embedding.sigmoid: 0 smoothstep, 1 smooth
+  int sigmoid_combine;  // stochastic.sigmoidCombine: 0 radialPlus, 1 radial, 2 tensor
+  double sigmoid_start; // embedding.sigmoidStart (1)
+  double sigmoid_end;   // embedding.sigmoidEnd (factor - 1)
+  unsigned recursions;  // embedding.mergeRecursions after the 99 heuristic
 };
 
 enum
@@ -431,11 +438,106 @@ struct Sizes
   }
 };
 
+// SmoothSigmoid (covariance.hh:145-176), ClampingSigmoid (:202-218),
+// SmoothstepSigmoid (:244-275)
+static inline double
+sigmoid_value(int kind, double oneEdge, double zeroEdge, double x,
+              unsigned recursions)
+{
+  if (kind == 1) {
+    if (std::abs(x) < oneEdge)
+      return 1.;
+    if (std::abs(x) > zeroEdge)
+      return 0.;
+    const double x1 = (zeroEdge - std::abs(x)) / (zeroEdge - oneEdge);
+    const double x2 = (std::abs(x) - oneEdge) / (zeroEdge - oneEdge);
+    const double t1 = x1 > 0. ? std::exp(-1. / x1) : 0.;
+    const double t2 = x2 > 0. ? std::exp(-1. / x2) : 0.;
+    return t1 / (t1 + t2);
+  }
+  double x1;
+  if (std::abs(x) < oneEdge)
+    x1 = 1.;
+  else if (std::abs(x) > zeroEdge)
+    x1 = 0.;
+  else
+    x1 = (zeroEdge - std::abs(x)) / (zeroEdge - oneEdge);
+  const double x2 = 2. * x1 - 1.;
+  double normalization = 1.;
+  double addition = 1.;
+  double output = 1.;
+  for (unsigned int i = 1; i <= recursions; i++) {
+    output *= 2. * i;
+    addition *= 1 - x2 * x2;
+    output += addition;
+    output /= 2. * i + 1.;
+    normalization *= 2. * i / (2. * i + 1.);
+  }
+  output *= x2 / normalization;
+  output += 1.;
+  output /= 2.;
+  return output;
+}
+
+// Matrix::computeMatrixEntriesWithMerge, matrix.hh:662-787: 2^dim mirrored
+// copies of the covariance, each tapered by a sigmoid, the rest filled with
+// the value at the far corner (radialPlus)
+static inline double
+torus_cov_merge(const OrcCfg& cfg, const Sizes& s, const Geometry& g,
+                const size_t* idx)
+{
+  const int dim = s.dim;
+  const bool radial = cfg.sigmoid_combine != 2;
+  double trueCoord[3], mirrorCoord[3], transCoord[3];
+  double constValue = 0.;
+  if (cfg.sigmoid_combine == 0) {
+    for (int i = 0; i < dim; i++)
+      trueCoord[i] = cfg.ext[i] * cfg.factor / 2.;
+    g.transform(trueCoord, transCoord);
+    constValue = covariance(cfg, transCoord);
+  }
+  for (int i = 0; i < dim; i++)
+    trueCoord[i] = (unsigned)idx[i] * s.h[i];
+  double value = 0.;
+  double remainder = 1.;
+  for (unsigned int j = 0; j < (1u << dim); j++) {
+    for (int i = 0; i < dim; i++)
+      mirrorCoord[i] =
+        (j & (1u << i)) ? cfg.ext[i] * cfg.factor - trueCoord[i] : trueCoord[i];
+    double dampening = 1.;
+    const double eps = 1e-10;
+    const double sqrtDim = std::sqrt(double(dim));
+    const unsigned int factor = cfg.factor;
+    if (radial && sqrtDim < factor / 2.) {
+      double radius = 0.;
+      for (int i = 0; i < dim; i++)
+        radius += (mirrorCoord[i] * mirrorCoord[i]) / (cfg.ext[i] * cfg.ext[i]);
+      radius = std::sqrt(radius);
+      dampening = sigmoid_value(cfg.sigmoid, cfg.sigmoid_start * sqrtDim - eps,
+                                factor - (factor - cfg.sigmoid_end) * sqrtDim + eps,
+                                radius, cfg.recursions);
+    } else {
+      for (int i = 0; i < dim; i++)
+        dampening *= sigmoid_value(cfg.sigmoid, cfg.ext[i] * cfg.sigmoid_start - eps,
+                                   cfg.ext[i] * cfg.sigmoid_end + eps,
+                                   mirrorCoord[i], cfg.recursions);
+    }
+    if (dampening < eps)
+      continue;
+    remainder -= dampening;
+    g.transform(mirrorCoord, transCoord);
+    value = value + covariance(cfg, transCoord) * dampening;
+  }
+  return value + constValue * remainder;
+}
+
 // torus covariance value at torus cell idx (matrix.hh:637-646)
 static inline double
 torus_cov(const OrcCfg& cfg, const Sizes& s, const Geometry& g,
           const size_t* idx)
 {
+  if (cfg.periodization == 1)
+    return torus_cov_merge(cfg, s, g, idx);
   double coord[3], tc[3];
   for (int i = 0; i < s.dim; i++) {
     coord[i] = (unsigned)idx[i] * s.h[i];
