@@ -478,35 +478,109 @@ trend_value(const TrendSet& tr, const double* ext, const double* x)
 // mesh_j = extensions_j / cells_j.  The reference sends every centre through
 // coordsToIndices again; (i + 0.5) (1 + 1e-6 / cells) lies strictly inside
 // (i, i + 1), so that lookup returns cell i itself and is skipped here.
+// Per-axis parts of the trend components at the cell centres (the terms of
+// TrendComponent::evaluate, trend.hh:601-634, that depend on one coordinate
+// only): slope c_j (x_j - ext_j / 2), disk (x_j - c_j)^2, block 1 / 0 for
+// |x_j - c_j| <= w_j / 2.  Layout [component][c0 + c1 + c2].  Summing them in
+// k_bulk_evaluate in the reference's order gives the per-cell values bit for
+// bit (same operations, same order) without recomputing them per cell.
+__global__ void
+k_trend_axes(FieldGeom g, TrendSet tr, double* __restrict__ table)
+{
+  const unsigned L = g.cells[0] + g.cells[1] + g.cells[2];
+  const unsigned total = L * (unsigned)tr.n;
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += gridDim.x * blockDim.x) {
+    const unsigned t = e / L;
+    unsigned i = e - t * L;
+    int j = 0;
+    if (i >= g.cells[0]) {
+      i -= g.cells[0];
+      j = 1;
+      if (i >= g.cells[1]) {
+        i -= g.cells[1];
+        j = 2;
+      }
+    }
+    const double* c = tr.coeff[t];
+    const double x = __dmul_rn((double)i + 0.5, g.center[j]); // center[] = mesh
+    double v = 0.;
+    if (j < g.dim) {
+      if (tr.kind[t] == PF_TREND_SLOPE)
+        v = __dmul_rn(c[j], __dadd_rn(x, -__dmul_rn(g.ext[j], 0.5)));
+      else if (tr.kind[t] == PF_TREND_DISK) {
+        const double d = __dadd_rn(x, -c[j]);
+        v = __dmul_rn(d, d);
+      } else if (tr.kind[t] == PF_TREND_BLOCK)
+        v = fabs(__dadd_rn(x, -c[j])) > __dmul_rn(0.5, c[g.dim + j]) ? 0. : 1.;
+    } else if (tr.kind[t] == PF_TREND_BLOCK)
+      v = 1.;
+    table[e] = v;
+  }
+}
+
 template <int DIM, bool TREND>
 __global__ void
-k_bulk_evaluate(FieldGeom g, TrendSet tr, const double* __restrict__ field,
-                int kind, double lambda, double* __restrict__ out)
+k_bulk_evaluate(FieldGeom g, TrendSet tr, const double* __restrict__ table,
+                const double* __restrict__ field, int kind, double lambda,
+                double* __restrict__ out)
 {
   constexpr unsigned ROWS = 4; // rows per block step: loads of all rows first
   const unsigned c0 = g.cells[0], c1 = DIM > 1 ? g.cells[1] : 1,
                  c2 = DIM > 2 ? g.cells[2] : 1;
+  const unsigned L = g.cells[0] + g.cells[1] + g.cells[2];
   for (unsigned i2 = blockIdx.z; i2 < c2; i2 += gridDim.z)
     for (unsigned b1 = blockIdx.y * ROWS; b1 < c1; b1 += gridDim.y * ROWS) {
-      double x[3];
-      x[2] = __dmul_rn((double)i2 + 0.5, g.center[2]); // center[] = mesh here
       for (unsigned i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < c0;
            i0 += gridDim.x * blockDim.x) {
-        double v[ROWS];
+        double v[ROWS], tsum[ROWS];
 #pragma unroll
-        for (unsigned r = 0; r < ROWS; r++)
+        for (unsigned r = 0; r < ROWS; r++) {
+          tsum[r] = 0.;
           if (b1 + r < c1)
             v[r] = field[(size_t)c0 * (b1 + r + (size_t)c1 * i2) + i0];
-        if (TREND)
-          x[0] = __dmul_rn((double)i0 + 0.5, g.center[0]);
+        }
+        if (TREND) {
+          for (int t = 0; t < tr.n; t++) {
+            const double* __restrict__ tab = table + (size_t)t * L;
+            const double* c = tr.coeff[t];
+            const int k = tr.kind[t];
+            const double a0 = tab[i0];
+            const double a2 = DIM > 2 ? tab[g.cells[0] + g.cells[1] + i2] : 0.;
+#pragma unroll
+            for (unsigned r = 0; r < ROWS; r++) {
+              const unsigned i1 = min(b1 + r, c1 - 1);
+              const double a1 = DIM > 1 ? tab[g.cells[0] + i1] : 0.;
+              double comp;
+              if (k == PF_TREND_MEAN)
+                comp = c[0];
+              else if (k == PF_TREND_BLOCK) {
+                bool inside = a0 != 0.;
+                if (DIM > 1)
+                  inside = inside && a1 != 0.;
+                if (DIM > 2)
+                  inside = inside && a2 != 0.;
+                comp = inside ? c[2 * DIM] : 0.;
+              } else {
+                double sum = a0; // 0 + a0
+                if (DIM > 1)
+                  sum = __dadd_rn(sum, a1);
+                if (DIM > 2)
+                  sum = __dadd_rn(sum, a2);
+                comp = k == PF_TREND_SLOPE
+                         ? sum
+                         : exp(__dmul_rn(
+                             __ddiv_rn(-sum, __dmul_rn(c[DIM], c[DIM])),
+                             c[DIM + 1]));
+              }
+              tsum[r] = __dadd_rn(tsum[r], comp);
+            }
+          }
+        }
 #pragma unroll
         for (unsigned r = 0; r < ROWS; r++)
           if (b1 + r < c1) {
-            double w = v[r];
-            if (TREND) {
-              x[1] = __dmul_rn((double)(b1 + r) + 0.5, g.center[1]);
-              w = __dadd_rn(w, trend_value<DIM>(tr, g.ext, x));
-            }
+            const double w = TREND ? __dadd_rn(v[r], tsum[r]) : v[r];
             out[(size_t)c0 * (b1 + r + (size_t)c1 * i2) + i0] =
               transform_value(w, kind, lambda);
           }
@@ -3794,9 +3868,21 @@ pf_field_bulk_evaluate(pf_plan* pl, int dim, const unsigned* cells,
   PF_TRY(stage_out(pl, out, n, false, so));
   const int kind = apply_transform ? pl->d.transform : 0;
   const dim3 grid = row_grid(g.cells[0], (g.cells[1] + 3) / 4, g.cells[2]);
+  if (tr.n) {
+    const size_t entries =
+      (size_t)tr.n * ((size_t)g.cells[0] + g.cells[1] + g.cells[2]);
+    if (entries > pl->axis_cap) {
+      PF_CUDA(cudaStreamSynchronize(pl->stream));
+      dev_free(&pl->axis_tab);
+      PF_TRY(dev_alloc(&pl->axis_tab, entries));
+      pl->axis_cap = entries;
+    }
+    k_trend_axes<<<grid_for(entries), 256, 0, pl->stream>>>(g, tr, pl->axis_tab);
+    pl->launches++;
+  }
 #define PF_BULK(D, T)                                                          \
   k_bulk_evaluate<D, T><<<grid, 256, 0, pl->stream>>>(                         \
-    g, tr, sf.dev, kind, pl->d.boxcox_lambda, so.dev)
+    g, tr, pl->axis_tab, sf.dev, kind, pl->d.boxcox_lambda, so.dev)
   if (dim == 3) {
     if (tr.n) PF_BULK(3, true); else PF_BULK(3, false);
   } else if (dim == 2) {
