@@ -131,6 +131,10 @@ def lib():
         L.orc_reference_noise.argtypes = [C.c_uint, C.c_size_t, dp]
         L.orc_reference_noise_ranks.argtypes = [C.c_uint, C.c_size_t, C.c_int, dp]
         L.orc_max_threads.restype = C.c_int
+        u32 = C.POINTER(C.c_uint32)
+        L.orc_philox4x32.argtypes = [C.c_int, u32, u32, u32]
+        L.orc_philox_noise.argtypes = [C.POINTER(OrcCfg), C.c_uint64, C.c_uint64, C.c_int, dp]
+        L.orc_philox_uncorrelated.argtypes = [C.c_uint64, C.c_size_t, C.c_uint64, dp]
         L.orc_generate_uncorrelated.argtypes = [C.c_uint, C.c_size_t, dp]
         L.orc_multiply.argtypes = [C.POINTER(OrcCfg), dp, C.c_int, dp, dp]
         L.orc_multiply_inverse.argtypes = [C.POINTER(OrcCfg), dp, dp, dp, C.POINTER(C.c_uint)]
@@ -299,6 +303,13 @@ class Oracle:
         _check(lib().orc_reference_noise_ranks(C.c_uint(seed), self.noise_entries, ranks, _dp(noise)))
         return noise
 
+    def philox_noise(self, seed, realization=0, mode="fp64"):
+        """the CUDA path's device noise (Philox4x32 counter stream + Box-Muller)
+        for (seed, realization), restated on the CPU, in reference stream order"""
+        noise = np.empty(2 * self.noise_entries, dtype=np.float64)
+        _check(lib().orc_philox_noise(C.byref(self.cfg), seed, realization, {"fast": 0, "fp64": 1}[mode], _dp(noise)))
+        return noise
+
     def generate_from_noise(self, noise, want_spare=False):
         lam = self.lambda_stored()
         noise = np.ascontiguousarray(noise, dtype=np.float64)
@@ -340,6 +351,22 @@ class Oracle:
 def generate_uncorrelated(seed, n):
     out = np.empty(n, dtype=np.float64)
     _check(lib().orc_generate_uncorrelated(C.c_uint(seed), n, _dp(out)))
+    return out
+
+
+def philox4x32(rounds, ctr, key):
+    """one Philox4x32-R block of the oracle's restatement (Salmon et al., SC'11)"""
+    c = (C.c_uint32 * 4)(*ctr)
+    k = (C.c_uint32 * 2)(*key)
+    o = (C.c_uint32 * 4)()
+    _check(lib().orc_philox4x32(rounds, c, k, o))
+    return tuple(int(x) for x in o)
+
+
+def philox_uncorrelated(seed, n, q0=0):
+    """pf_generate_uncorrelated's specification restated (device Philox, fp64)"""
+    out = np.empty(n, dtype=np.float64)
+    _check(lib().orc_philox_uncorrelated(seed, n, q0, _dp(out)))
     return out
 
 

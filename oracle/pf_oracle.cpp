@@ -1473,6 +1473,167 @@ orc_field_bulk_evaluate(int dim, const unsigned* cells,
   ORC_CATCH
 }
 
+} // extern "C"
+
+// --------------------------------------------------------------------------
+// Device white noise of the CUDA product path, restated on the CPU so that the
+// benchmarked variant (counter -> Philox -> Box-Muller -> sigma rule -> c2r)
+// has an oracle of its own.  The reference has no counterpart (its
+// RNGBackend::sample, backends/cpprngbackend.hh:49-58, is a sequential
+// stream); what is restated here is the SPECIFICATION the library documents
+// (include/parafields_cuda.h, "device noise"), written from the published
+// algorithm -- Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy
+// as 1, 2, 3", SC'11, Philox4x32-R with the Random123 multipliers and Weyl
+// key increments -- and not from the CUDA source:
+//   counter = (c lo, c hi, realization lo, realization hi), key = (seed lo,
+//   seed hi); c = k0 + m0 * (e mod L/2) [+ m0 * (L/2) * k1 in 3D], where e is
+//   the index along the LAST frequency axis (length L) and one Philox block of
+//   four words serves the two entries e and e + L/2: words (0,1) -> entry
+//   e < L/2, words (2,3) -> entry e + L/2.  Box-Muller on a word pair (w0,w1):
+//   u = (w0 + 1/2) 2^-32, radius sqrt(-2 ln u), angle pi (w1 2^-31 - 1);
+//   r1 = radius cos, r2 = radius sin.  mode 1: fp64, 10 rounds; mode 0
+//   ("fast"): 7 rounds, the same formula in fp32 (the device uses the MUFU
+//   approximations of lg2 / sqrt / sin / cos there, so agreement is ~1e-6).
+// The normals are written in the reference's stream order, so
+// that generate_from_noise() above finishes the job.
+// --------------------------------------------------------------------------
+static void
+philox4x32(int rounds, const uint32_t ctr[4], const uint32_t key[2],
+           uint32_t out[4])
+{
+  const uint64_t M0 = 0xD2511F53ull, M1 = 0xCD9E8D57ull;
+  const uint32_t W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+  uint32_t c[4] = { ctr[0], ctr[1], ctr[2], ctr[3] };
+  uint32_t k[2] = { key[0], key[1] };
+  for (int r = 0; r < rounds; r++) {
+    if (r > 0) { // bump the key between rounds
+      k[0] += W0;
+      k[1] += W1;
+    }
+    const uint64_t p0 = M0 * c[0], p1 = M1 * c[2];
+    const uint32_t n[4] = { (uint32_t)(p1 >> 32) ^ c[1] ^ k[0], (uint32_t)p1,
+                            (uint32_t)(p0 >> 32) ^ c[3] ^ k[1], (uint32_t)p0 };
+    for (int i = 0; i < 4; i++)
+      c[i] = n[i];
+  }
+  for (int i = 0; i < 4; i++)
+    out[i] = c[i];
+}
+
+static void
+box_muller(int mode, uint32_t w0, uint32_t w1, double* r1, double* r2)
+{
+  if (mode == 1) {
+    const double u = ((double)w0 + 0.5) * 2.3283064365386963e-10; // 2^-32
+    const double radius = std::sqrt(-2.0 * std::log(u));
+    const double turn = (double)w1 * 4.6566128730773926e-10 - 1.0; // angle/pi
+    const double ang = 3.14159265358979323846264338327950288 * turn;
+    *r1 = radius * std::cos(ang);
+    *r2 = radius * std::sin(ang);
+  } else {
+    const float u = std::fmaf((float)w0, 2.3283064365386963e-10f,
+                              1.1641532182693481e-10f);
+    const float radius = std::sqrt(-1.3862943611198906f * std::log2(u));
+    const float ang =
+      std::fmaf((float)w1, 1.4629180792671596e-09f, -3.14159265358979f);
+    *r1 = (double)(radius * std::cos(ang));
+    *r2 = (double)(radius * std::sin(ang));
+  }
+}
+
+static void
+philox_noise(const OrcCfg& cfg, uint64_t seed, uint64_t realization, int mode,
+             double* noise)
+{
+  Sizes s(cfg);
+  const int d = s.dim;
+  const int rounds = mode == 1 ? 10 : 7;
+  const uint32_t key[2] = { (uint32_t)seed, (uint32_t)(seed >> 32) };
+  const bool dft = cfg.field_backend == 1;
+  const size_t b0 = dft ? s.n[0] : s.m0;
+  const size_t L = s.n[d - 1], half = L / 2;
+  const bool tr = cfg.transposed && d == 3;
+  const size_t S = b0 * (d > 1 ? s.n[1] : 1) * (d > 2 ? s.n[2] : 1);
+  for (size_t idx = 0; idx < S; idx++) {
+    size_t k[3] = { 0, 0, 0 };
+    if (tr) {
+      size_t b[3] = { b0, s.n[2], s.n[1] }, t[3];
+      indexToIndices(idx, t, b, 3);
+      k[0] = t[0];
+      k[1] = t[2];
+      k[2] = t[1];
+    } else {
+      size_t b[3] = { b0, s.n[1], s.n[2] };
+      indexToIndices(idx, k, b, d);
+    }
+    const size_t e = k[d - 1];
+    uint64_t c;
+    if (d == 1)
+      c = e % half;
+    else if (d == 2)
+      c = k[0] + (uint64_t)b0 * (e % half);
+    else
+      c = k[0] + (uint64_t)b0 * (e % half) + (uint64_t)b0 * half * k[1];
+    const uint32_t ctr[4] = { (uint32_t)c, (uint32_t)(c >> 32),
+                              (uint32_t)realization,
+                              (uint32_t)(realization >> 32) };
+    uint32_t w[4];
+    philox4x32(rounds, ctr, key, w);
+    const int o = e >= half ? 2 : 0;
+    box_muller(mode, w[o], w[o + 1], &noise[2 * idx], &noise[2 * idx + 1]);
+  }
+}
+
+extern "C" {
+
+// one Philox4x32-R block (known-answer tests against the Random123 vectors)
+int
+orc_philox4x32(int rounds, const uint32_t* ctr, const uint32_t* key,
+               uint32_t* out)
+{
+  ORC_TRY
+  philox4x32(rounds, ctr, key, out);
+  ORC_CATCH
+}
+
+// the product path's device noise for (seed, realization) in the reference's
+// stream order: 2 * orc_noise_entries(cfg) doubles; mode 0 fast, 1 fp64
+int
+orc_philox_noise(const OrcCfg* cfg, uint64_t seed, uint64_t realization,
+                 int mode, double* noise)
+{
+  ORC_TRY
+  philox_noise(*cfg, seed, realization, mode, noise);
+  ORC_CATCH
+}
+
+// pf_generate_uncorrelated's specification: block q (counter q0 + q,
+// realization word = 2^64 - 1, 10 rounds, fp64 Box-Muller) fills cells
+// 4q .. 4q+3 with (r1, r2) of words (0,1) and (r1, r2) of words (2,3)
+int
+orc_philox_uncorrelated(uint64_t seed, size_t n, uint64_t q0, double* out)
+{
+  ORC_TRY
+  const uint32_t key[2] = { (uint32_t)seed, (uint32_t)(seed >> 32) };
+  for (size_t q = 0; 4 * q < n; q++) {
+    const uint64_t c = q0 + q;
+    const uint32_t ctr[4] = { (uint32_t)c, (uint32_t)(c >> 32), 0xFFFFFFFFu,
+                              0xFFFFFFFFu };
+    uint32_t w[4];
+    philox4x32(10, ctr, key, w);
+    double v[4];
+    box_muller(1, w[0], w[1], &v[0], &v[1]);
+    box_muller(1, w[2], w[3], &v[2], &v[3]);
+    for (size_t j = 0; j < 4 && 4 * q + j < n; j++)
+      out[4 * q + j] = v[j];
+  }
+  ORC_CATCH
+}
+
+} // extern "C"
+
+extern "C" {
+
 int
 orc_max_threads()
 {

@@ -49,6 +49,17 @@ CASES = {
     "geometric_3d": dict(cells=[16, 32, 8], covariance="exponential", corr_length=[0.02, 0.004, 0.0, 0.004, 0.032, 0.002, 0.0, 0.002, 0.024], anisotropy="geometric"),
     "factor4_3d": dict(cells=[8, 16, 4], covariance="exponential", corr_length=[0.05, 0.01, 0.0, 0.01, 0.08, 0.005, 0.0, 0.005, 0.06], anisotropy="geometric", factor=4),
     "periodic_2d": dict(cells=[32, 32], covariance="exponential", corr_length=0.1, periodic=True, approximate=True),
+    # the remaining covariance functors (covariance.hh:294-890), one fixture each
+    "cov_separableExponential_2d": dict(cells=[32, 16], covariance="separableExponential", corr_length=0.07, variance=1.7, approximate=True),
+    "cov_separableExponential_3d": dict(cells=[8, 16, 8], covariance="separableExponential", corr_length=[0.1, 0.05, 0.2], anisotropy="axiparallel", approximate=True),
+    "cov_dampedOscillation_2d": dict(cells=[32, 32], covariance="dampedOscillation", corr_length=0.07, approximate=True),
+    "cov_dampedOscillation_3d": dict(cells=[8, 8, 16], covariance="dampedOscillation", corr_length=0.07, variance=0.6, approximate=True),
+    "cov_gammaExponential_2d": dict(cells=[32, 16], covariance="gammaExponential", corr_length=0.07, cov_params={"expGamma": 1.5}, approximate=True),
+    "cov_generalizedCauchy_3d": dict(cells=[8, 16, 8], covariance="generalizedCauchy", corr_length=0.07, cov_params={"cauchyAlpha": 1.2, "cauchyBeta": 0.8}, approximate=True),
+    "cov_whiteNoise_2d": dict(cells=[16, 32], covariance="whiteNoise", corr_length=0.07, variance=2.5),
+    "cov_whiteNoise_1d": dict(cells=[64], covariance="whiteNoise", corr_length=0.07),
+    "cov_cauchy_2d": dict(cells=[32, 32], covariance="cauchy", corr_length=0.05, approximate=True),
+    "cov_matern52_3d": dict(cells=[8, 8, 8], covariance="matern52", corr_length=0.1, approximate=True),
 }
 SEED = 20240611
 
@@ -56,9 +67,12 @@ SEED = 20240611
 def main():
     if not rl.available():
         raise SystemExit("oracle/_ref/libpf_ref.so missing: run `make -C oracle` where /root/reference exists")
+    only = sys.argv[1:]  # optional name prefixes: regenerate a subset
     kat = rl.rng(42, 6)
     np.savez(os.path.join(HERE, "ref_rng_kat.npz"), seed=42, values=kat)
     for name, case in CASES.items():
+        if only and not any(name.startswith(o) for o in only):
+            continue
         # the CG stopping rule (1e-16 energy stagnation, matrix.hh:1438-1441)
         # is rounding sensitive: pin the iteration count so that both sides
         # stop on the count ("CG stopping rule")
@@ -66,8 +80,9 @@ def main():
         if not name.startswith("t1d"):  # tiny 1D systems converge exactly
             case.setdefault("cg_iterations", 4)
         r = rl.Reference(**case)
-        okw = {k: v for k, v in case.items() if k not in ("transform",)}
-        o = ol.Oracle(**okw)
+        okw = {k: v for k, v in case.items() if k not in ("transform", "cov_params")}
+        pv = list(case.get("cov_params", {}).values()) + [0.0, 0.0]
+        o = ol.Oracle(p0=pv[0], p1=pv[1], **okw)
         field = r.generate(SEED)
         data = dict(
             ini=np.array(r.text),
@@ -94,6 +109,8 @@ def main():
         data["uncorrelated"] = r.generate_uncorrelated(7)
         np.savez_compressed(os.path.join(HERE, "ref_%s.npz" % name), **data)
         print(name, "ok", field.shape, "lambda min %.3e" % data["lambda_stored"].min())
+    if only:
+        return
     # value transforms at evaluation time (mutators.hh) on one field
     base = dict(cells=[16, 16], covariance="exponential", corr_length=0.1)
     tr = {}
