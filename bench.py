@@ -3,8 +3,8 @@
 
 Contract (see the task statement): `python bench.py --gpus N --steps K
 --warmup W` prints ONE JSON line from rank 0.  A "step" is one realization of
-the workload per GPU (K3 of SURVEY.md section 8: 3D 512^3 cells, spherical
-covariance, corrLength 0.1, embedding factor 2 -> 1024^3 fp64 torus).
+the workload (K3 of SURVEY.md section 8: 3D 512^3 cells, spherical covariance,
+corrLength 0.1, embedding factor 2 -> 1024^3 fp64 torus).
 
   value        whole-job realizations/s, fields stay in HBM, timed with CUDA
                events on the launching stream, max over ranks
@@ -12,19 +12,30 @@ covariance, corrLength 0.1, embedding factor 2 -> 1024^3 fp64 torus).
                buffer: the device->host copy of every field is inside the
                timed region (the only per-step input is the (seed,
                realization) pair passed by value)
-  roofline     dominant kernel (pass A: Philox noise * sqrt(lambda) + inverse
-               FFT along the last axis), algorithmic bytes / measured launch
-               duration against MEASURED_PEAKS.json
+  roofline     N = 1: dominant kernel, algorithmic bytes / measured launch
+               duration against MEASURED_PEAKS.json (HBM);  N > 1 (slab mode):
+               bytes every GPU must send over NVLink per realization / step
+               time against the measured 770 GB/s peer-copy figure, the HBM
+               view nested below it
+  rng_fp64     the same K3 step with rng_mode fp64 (10 Philox rounds + fp64
+               Box-Muller, the reference's precision of the normals); the
+               headline uses rng_mode fast (7 rounds + fp32 Box-Muller)
+  other_workloads  K1, K2, K4 (one by one and as a batch of 64), K5 matvec and
+               one PCG iteration: a few steps each with their roofline fraction
   cpu_baseline the CPU oracle (single thread = one MPI rank of the reference)
                on a bounded sample of the same workload
+  parity       N > 1: one 64^3 slab-vs-single comparison per rank before the
+               timed region; the run fails (exit 1) unless it is exactly 0.0
 
-Multi-GPU (N>1, launched by torch.distributed.run): realizations are
-independent given (seed, realization), so ranks generate disjoint realization
-indices with no data-path collective ("replicas", weak scaling).
+Multi-GPU (N > 1, launched by torch.distributed.run): `--mode slab` (default)
+shards ONE realization over the GPUs (BASELINE.json's configuration, strong
+scaling); `--mode replicas` gives every GPU its own realizations (weak).
 
-`--impl reference` times the CPU restatement of the reference path
-(oracle/, all host threads) -- the reference itself cannot be built in this
-image (needs FFTW3-MPI, MPI, dune-common).
+`--impl reference` times the CPU restatement of the reference path (oracle/,
+every host thread, the FULL workload: same config as the GPU arm) and, next to
+it, a best-effort all-core variant on a real FFT library (scipy / pocketfft).
+The reference itself cannot be built with its own FFT (needs FFTW3-MPI, MPI,
+dune-common).
 """
 import argparse
 import importlib
@@ -49,11 +60,17 @@ WORKLOADS = {
     "K5": dict(cells=[256, 256, 256], covariance="exponential", corr_length=0.05, label="3D 256^3 exponential (512^3 torus)"),
     "S3": dict(cells=[128, 128, 128], covariance="spherical", corr_length=0.1, label="3D 128^3 spherical (256^3 torus)"),
 }
+SEED = 20240611
 
 
-def algorithmic_bytes(cells, factor=2, compact=True):
+def plan_kwargs(name):
+    return {k: v for k, v in WORKLOADS[name].items() if k != "label"}
+
+
+def algorithmic_bytes(cells, factor=2, compact=True, batch=1):
     """bytes per realization of the pruned pass pipeline and
-    of its dominant kernel (pass A)."""
+    of its passes (pass A = noise + first inverse axis, the dominant kernel).
+    batch > 1: the sigma table is read once per batch."""
     c = list(cells)
     n = [factor * x for x in c]
     m0 = n[0] // 2 + 1
@@ -62,14 +79,26 @@ def algorithmic_bytes(cells, factor=2, compact=True):
         a_w = 16 * m0 * n[1] * c[2]
         b_w = 16 * m0 * c[1] * c[2]
         c_w = 8 * c[0] * c[1] * c[2]
-        total = lam + 2 * a_w + 2 * b_w + c_w
-        return dict(total=total, pass_a=lam + a_w, pass_b=a_w + b_w, pass_c=b_w + c_w)
+        total = lam // batch + 2 * a_w + 2 * b_w + c_w
+        return dict(total=total, pass_a=lam // batch + a_w, pass_b=a_w + b_w, pass_c=b_w + c_w)
     if len(c) == 2:
         lam = 8 * ((n[0] // 2 + 1) * (n[1] // 2 + 1) if compact else m0 * n[1])
         a_w = 16 * m0 * c[1]
         c_w = 8 * c[0] * c[1]
-        return dict(total=lam + 2 * a_w + c_w, pass_a=lam + a_w, pass_b=0, pass_c=a_w + c_w)
+        return dict(total=lam // batch + 2 * a_w + c_w, pass_a=lam // batch + a_w, pass_b=0, pass_c=a_w + c_w)
     return dict(total=8 * n[0] + 16 * c[0], pass_a=8 * n[0] + 16 * c[0], pass_b=0, pass_c=0)
+
+
+def matvec_bytes(cells, factor=2):
+    """algorithmic bytes of one covariance matvec"""
+    c = list(cells)
+    n = [factor * x for x in c]
+    m0 = n[0] // 2 + 1
+    lam = 8 * (n[0] // 2 + 1) * (n[1] // 2 + 1) * (n[2] // 2 + 1)
+    f = 8 * c[0] * c[1] * c[2]
+    u = 16 * m0 * c[1] * c[2]
+    v = 16 * m0 * n[1] * c[2]
+    return 2 * f + 4 * u + 4 * v + lam
 
 
 class ClockSampler:
@@ -141,85 +170,314 @@ def measured_peaks():
     return dict(hbm_gbs=6650.0), "fallback"
 
 
-def cpu_sample_config(wl):
-    """Bounded CPU sample of a workload: same covariance, 1/4 of the cells per
-    dimension in 3D (1/64 of the work), 1/2 in 2D."""
+# ---------------------------------------------------------------------------
+# CPU legs (the only places that may execute oracle/)
+# ---------------------------------------------------------------------------
+def host_threads():
+    """threads this process may use: its CPU affinity, NOT OMP_NUM_THREADS
+    (torch.distributed.run exports OMP_NUM_THREADS=1 to every rank)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def host_mem_gb():
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable"):
+                return float(ln.split()[1]) / 1e6
+    except Exception:
+        pass
+    return 0.0
+
+
+def cpu_config(wl, div):
+    """the workload with every dimension divided by `div` (1 = full size)"""
     cfg = {k: v for k, v in WORKLOADS[wl].items() if k not in ("label", "transform")}
     cells = cfg["cells"]
-    if len(cells) == 3 and cells[0] >= 512:
-        div = 2
-    elif len(cells) == 3 and cells[0] >= 256:
-        div = 2
-    else:
-        div = 1
     cfg["cells"] = [c // div for c in cells]
     scale = float(np.prod(cells)) / float(np.prod(cfg["cells"]))
     return cfg, scale
 
 
-def time_oracle(wl, threads, reps):
-    """seconds per realization of the CPU oracle on the bounded sample."""
+def time_oracle(wl, threads, reps, div, warm=0):
+    """seconds per realization of the CPU port (oracle/pf_oracle.cpp) on the
+    workload with cells / div per dimension: RNG stream(s) + sqrt(lambda) loop
+    + c2r + restriction, eigenvalue setup timed separately"""
     from oracle import oracle_lib as ol
 
-    cfg, scale = cpu_sample_config(wl)
+    cfg, scale = cpu_config(wl, div)
     o = ol.Oracle(threads=threads, **cfg)
     t0 = time.perf_counter()
     o.eigenvalues()
     t_eig = time.perf_counter() - t0
-    times = []
     # `threads` emulates an MPI run of the reference with that many ranks:
     # rank r draws its slab of the noise stream with seed + r
     ranks = threads
     while ranks > 1 and o.noise_entries % ranks:
         ranks -= 1
+    times = []
+    for r in range(warm + reps):
+        t0 = time.perf_counter()
+        noise = o.reference_noise_ranks(SEED + r, ranks)  # RNG stream(s)
+        o.generate_from_noise(noise)  # sqrt(lambda) loop + c2r + restrict
+        del noise
+        times.append(time.perf_counter() - t0)
+    times = times[warm:]
+    return dict(mean=float(np.mean(times)), best=float(np.min(times)), steps=len(times), scale=scale, cells=cfg["cells"], t_eig=t_eig, total=float(np.sum(times)))
+
+
+def time_fftlib(wl, threads, reps, div, lam_stream=None):
+    """Best-effort all-core CPU variant on a real FFT library:
+    numpy Generator normals drawn by `threads` workers, sigma scaling with the
+    Hermitian rule of r2cfieldbackend.hh:305-325, scipy.fft.irfftn (pocketfft,
+    workers = threads), restriction.  Same arithmetic as the reference's
+    generateField, not its RNG stream.  Returns seconds per realization."""
+    import concurrent.futures as cf
+
+    import scipy.fft
+
+    cfg, scale = cpu_config(wl, div)
+    c = cfg["cells"]
+    n = [2 * x for x in c]
+    dim = len(c)
+    m0 = n[0] // 2 + 1
+    # sigma on the half spectrum (k_last, ..., k0): the spectrum's values do not
+    # matter for the timing, its shape and the arithmetic do.  Use the analytic
+    # torus covariance -> rfftn once (setup, untimed).
+    t0 = time.perf_counter()
+    ax = [np.minimum(np.arange(k), k - np.arange(k)) / (k / 2.0) for k in n]
+    if dim == 3:
+        h = np.sqrt(ax[2][:, None, None] ** 2 + ax[1][None, :, None] ** 2 + ax[0][None, None, :] ** 2)
+    else:
+        h = np.sqrt(ax[1][:, None] ** 2 + ax[0][None, :] ** 2)
+    ell = np.ravel(cfg["corr_length"])[0]
+    h /= ell
+    cov = np.where(h < 1.0, 1.0 - 1.5 * h + 0.5 * h**3, 0.0) if cfg["covariance"] == "spherical" else np.exp(-h)
+    del h
+    lam = scipy.fft.rfftn(cov, workers=threads).real / cov.size
+    del cov
+    np.maximum(lam, 0.0, out=lam)
+    sig = np.sqrt(lam) * np.sqrt(0.5)
+    del lam
+    t_eig = time.perf_counter() - t0
+    shape = sig.shape
+    X = np.empty(shape, dtype=np.complex128)
+    Xr = X.view(np.float64).reshape(-1)
+    sigr = sig.reshape(-1)
+    bounds = sorted(set(int(b) for b in np.linspace(0, sigr.size, 8 * threads + 1)))
+    pool = cf.ThreadPoolExecutor(threads)
+
+    def fill(args):
+        i, lo, hi, seed = args
+        g = np.random.Generator(np.random.SFC64([seed, i]))
+        v = Xr[2 * lo : 2 * hi]
+        g.standard_normal(out=v)
+        v.reshape(-1, 2)[:] *= sigr[lo:hi, None]
+
+    times = []
     for r in range(reps):
         t0 = time.perf_counter()
-        noise = o.reference_noise_ranks(20240611 + r, ranks)  # RNG stream(s)
-        o.generate_from_noise(noise)  # sqrt(lambda) loop + c2r + restrict
+        list(pool.map(fill, [(i, bounds[i], bounds[i + 1], SEED + r) for i in range(len(bounds) - 1)]))
+        # self-conjugate entries: real, full weight (r2cfieldbackend.hh:318-321)
+        idx = [(0, n[d] // 2) for d in range(dim)]
+        for sel in np.array(np.meshgrid(*idx[::-1], indexing="ij")).reshape(dim, -1).T:
+            X[tuple(sel)] = X[tuple(sel)].real * np.sqrt(2.0)
+        y = scipy.fft.irfftn(X, s=tuple(n[::-1]), workers=threads, overwrite_x=True)
+        y *= float(y.size)  # FFTW's backward transform is unnormalised
+        field = np.ascontiguousarray(y[tuple(slice(0, k) for k in c[::-1])])
         times.append(time.perf_counter() - t0)
-    return min(times), scale, cfg, t_eig
+        del y, field
+    pool.shutdown()
+    return dict(mean=float(np.mean(times)), best=float(np.min(times)), steps=len(times), scale=scale, cells=c, t_eig=t_eig)
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the CPU restatement with all host threads."""
+    """--impl reference: the CPU restatement of the reference path, every host
+    thread, the FULL workload (same config as the GPU arm) when the host has
+    the memory for it, rank 0 only."""
     if rank != 0:
         return
-    from oracle import oracle_lib as ol
-
-    threads = max(1, os.cpu_count() or 1)
-    threads = min(threads, ol.lib().orc_max_threads()) if hasattr(ol.lib(), "orc_max_threads") else threads
-    steps = max(1, args.steps)
-    # warm-up + timed steps on the bounded sample
-    t_warm, scale, cfg, t_eig = time_oracle(args.workload, threads, max(1, min(args.warmup, 1)))
+    threads = host_threads()
+    cells = WORKLOADS[args.workload]["cells"]
+    torus = float(np.prod([2 * c for c in cells]))
+    need_gb = torus * 8 * (4.6 if len(cells) == 3 else 4.0) / 1e9  # noise + X + real + eigen scratch
+    div = 1
+    if host_mem_gb() < need_gb:
+        div = 2
+    steps = max(1, min(args.steps, 3))
+    warm = 1 if args.warmup > 0 else 0
     t0 = time.perf_counter()
-    t_step, _, _, _ = time_oracle(args.workload, threads, min(steps, 3))
+    res = time_oracle(args.workload, threads, steps, div, warm=warm)
     wall = time.perf_counter() - t0
-    value = 1.0 / (t_step * scale)
-    sample = "one realization of %s cells (1/%d of the workload's cells), linear scaling to the full size; eigenvalue setup %.1fs excluded" % (
-        "x".join(map(str, cfg["cells"])),
-        int(scale),
-        t_eig,
+    same = div == 1
+    t_step = res["mean"] * res["scale"]
+    value = 1.0 / t_step
+    sample = "%d timed realization(s) (+%d warm-up) of %s cells%s; eigenvalue setup %.1f s excluded (one-time)" % (
+        res["steps"],
+        warm,
+        "x".join(map(str, res["cells"])),
+        " = the full workload" if same else " (1/%d of the workload's cells, host memory %.0f GB < %.0f GB needed; linear scaling)" % (int(res["scale"]), host_mem_gb(), need_gb),
+        res["t_eig"],
     )
+    fftlib = None
+    if not args.no_fftlib:
+        try:
+            fr = time_fftlib(args.workload, threads, max(1, min(steps, 2)), div)
+            fftlib = dict(
+                value=1.0 / (fr["mean"] * fr["scale"]),
+                unit="realizations/s",
+                cores=threads,
+                kind="port",
+                library="scipy.fft (pocketfft), numpy Generator normals",
+                ms_per_step=1e3 * fr["mean"] * fr["scale"],
+                sample="%d realization(s) of %s cells%s; spectrum setup %.1f s excluded" % (fr["steps"], "x".join(map(str, fr["cells"])), " = the full workload" if same else " (scaled)", fr["t_eig"]),
+            )
+        except Exception as e:  # never lose the main figure to the extra one
+            fftlib = dict(unavailable="%s: %s" % (type(e).__name__, e))
     line = dict(
         impl="reference",
         metric="realizations/sec",
         value=value,
         unit="realizations/s",
         n_gpus=args.gpus,
-        steps=args.steps,
-        warmup=args.warmup,
-        ms_per_step=1e3 * t_step * scale,
+        steps=res["steps"],
+        steps_requested=args.steps,
+        warmup=warm,
+        ms_per_step=1e3 * t_step,
         higher_is_better=True,
-        scaling="weak",
+        scaling="strong" if args.gpus > 1 else "weak",
         vs_baseline=None,
         dtype="f64",
         data="synthetic",
-        config=dict(workload=WORKLOADS[args.workload]["label"], name=args.workload),
+        config=dict(workload=WORKLOADS[args.workload]["label"], name=args.workload, same_config=same, timed_wall_s=res["total"], run_wall_s=wall),
         cpu_baseline=dict(value=value, unit="realizations/s", cores=threads, kind="port", sample=sample),
+        cpu_baseline_fftlib=fftlib,
         e2e=dict(value=value, unit="realizations/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
-        note="reference = CPU restatement of parafields-core (oracle/pf_oracle.cpp, OpenMP over FFT lines); the real reference needs FFTW3-MPI/MPI/dune-common, absent here",
+        note="reference arm = CPU restatement of parafields-core's generateField (oracle/pf_oracle.cpp: reference RNG streams of `cores` MPI ranks, sqrt(lambda) loop, c2r, restriction; own plain FFT, OpenMP over FFT lines); cpu_baseline_fftlib = the same arithmetic on scipy/pocketfft with all cores.  The reference's own FFT (FFTW3-MPI) is absent from this image.",
     )
     print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------
+# GPU legs
+# ---------------------------------------------------------------------------
+def timed_generate(torch, plan, stream, K, W, apply_tr, first=0, batch=None):
+    """K realizations after W warm-ups, CUDA events on the plan's stream"""
+    D = plan.local_domain_size
+    field = torch.empty(D if batch is None else (batch, D), dtype=torch.float64, device="cuda")
+    for s in range(W):
+        if batch is None:
+            plan.generate(SEED, first + s, out=field, apply_transform=apply_tr)
+        else:
+            plan.generate_batch(SEED, first + s * batch, batch, out=field, apply_transform=apply_tr)
+    plan.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for s in range(K):
+        if batch is None:
+            plan.generate(SEED, first + W + s, out=field, apply_transform=apply_tr)
+        else:
+            plan.generate_batch(SEED, first + (W + s) * batch, batch, out=field, apply_transform=apply_tr)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (K * (batch or 1))
+
+
+def other_workloads(torch, pfb, stream, peak):
+    """K1, K2, K4 (single and batch 64), K5 matvec / PCG iteration: a few steps
+    each, fields resident in HBM, roofline fraction against the same peak"""
+    out = []
+
+    def entry(name, what, ms, nbytes, **kw):
+        d = dict(workload=name, what=what, ms=ms, per_s=1e3 / ms, algorithmic_bytes=nbytes, achieved_gbs=nbytes / ms / 1e6, frac=nbytes / ms / 1e6 / peak)
+        d.update(kw)
+        out.append(d)
+
+    for name in ("K1", "K2", "K4"):
+        try:
+            wl = plan_kwargs(name)
+            compact = wl.get("anisotropy", "none") != "geometric"
+            tr = wl.get("transform", "none") != "none"
+            with pfb.Plan(device=torch.cuda.current_device(), **wl) as p:
+                p.set_stream(stream)
+                p.compute_eigenvalues()
+                ms = timed_generate(torch, p, stream, 20 if name != "K4" else 10, 3, tr)
+                entry(name, "generate, one call per realization", ms, algorithmic_bytes(wl["cells"], compact=compact)["total"], label=WORKLOADS[name]["label"], note="K1 is L2-resident (12.6 MB): informational" if name == "K1" else None)
+                nb = 64 if name != "K2" else 16
+                msb = timed_generate(torch, p, stream, 2, 1, tr, first=1000, batch=nb if name != "K4" else 16)
+                entry(name, "generate_batch (%d realizations per call; bytes of a batch of 64: sigma read once per batch)" % (nb if name != "K4" else 16), msb, algorithmic_bytes(wl["cells"], compact=compact, batch=64)["total"])
+        except Exception as e:
+            out.append(dict(workload=name, error="%s: %s" % (type(e).__name__, e)))
+    try:
+        wl = plan_kwargs("K5")
+        nbytes = matvec_bytes(wl["cells"])
+        with pfb.Plan(device=torch.cuda.current_device(), **wl) as p:
+            p.set_stream(stream)
+            p.compute_eigenvalues()
+            x = torch.empty(p.domain_size, dtype=torch.float64, device="cuda")
+            y = torch.empty_like(x)
+            p.generate(1, 0, out=x)
+            for op in ("matrix", "root", "inverse_ext"):
+                for _ in range(3):
+                    p.apply(op, x, out=y)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(20):
+                    p.apply(op, x, out=y)
+                e1.record(stream)
+                torch.cuda.synchronize()
+                entry("K5", "times%s (one matvec)" % {"matrix": "Matrix", "root": "MatrixRoot", "inverse_ext": "InverseExtended"}[op], e0.elapsed_time(e1) / 20, nbytes)
+        # one PCG iteration of timesInverseMatrix: difference of two pinned counts
+        t = {}
+        for its in (2, 12):
+            with pfb.Plan(device=torch.cuda.current_device(), cg_iterations=its, **wl) as p:
+                p.set_stream(stream)
+                p.compute_eigenvalues()
+                x = torch.empty(p.domain_size, dtype=torch.float64, device="cuda")
+                y = torch.empty_like(x)
+                p.generate(1, 0, out=x)
+                p.solve(x, out=y)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                p.solve(x, out=y)
+                torch.cuda.synchronize()
+                t[its] = (time.perf_counter() - t0, p.cg_iterations_used)
+        if t[12][1] > t[2][1]:
+            ms_it = 1e3 * (t[12][0] - t[2][0]) / (t[12][1] - t[2][1])
+            D8 = 8 * int(np.prod(wl["cells"]))
+            entry("K5", "one PCG iteration of timesInverseMatrix (2 matvecs + 22 vector passes)", ms_it, 2 * nbytes + 22 * D8, label=WORKLOADS["K5"]["label"])
+    except Exception as e:
+        out.append(dict(workload="K5", error="%s: %s" % (type(e).__name__, e)))
+    return out
+
+
+def slab_parity(torch, dist, pfb, local_rank, rank, world):
+    """one 64^3 slab-vs-single comparison on this rank (device noise, single
+    calls and a pipelined batch); max over ranks of max|diff| / max|field|"""
+    case = dict(cells=[64, 64, 64], covariance="exponential", corr_length=0.1)
+    worst = 0.0
+    with pfb.Plan(device=local_rank, **case) as single, pfb.Plan(device=local_rank, n_ranks=world, rank=rank, **case) as slab:
+        slab.connect()
+        layers = 64 // world
+        for r in range(3):
+            full = single.generate(SEED, r)
+            mine = slab.generate(SEED, r)
+            ref = full[rank * layers : (rank + 1) * layers]
+            worst = max(worst, float(np.max(np.abs(mine - ref)) / np.max(np.abs(full))))
+        dev = torch.empty((3, slab.local_domain_size), dtype=torch.float64, device="cuda")
+        slab.generate_batch(SEED, 10, 3, out=dev)
+        slab.synchronize()
+        for r in range(3):
+            full = single.generate(SEED, 10 + r)
+            ref = full[rank * layers : (rank + 1) * layers].ravel()
+            worst = max(worst, float(np.max(np.abs(dev[r].cpu().numpy() - ref)) / np.max(np.abs(full))))
+        dist.barrier()
+    t = torch.tensor([worst], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), "3D 64^3 exponential, 3 single calls + a pipelined batch of 3 per rank, device noise"
 
 
 def main():
@@ -233,6 +491,8 @@ def main():
     ap.add_argument("--mode", default="auto", choices=["auto", "slab", "replicas"], help="N>1: slab = one realization sharded over the GPUs (BASELINE config, default), replicas = independent realizations per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-others", action="store_true", help="skip the other_workloads array and the rng_fp64 figure")
+    ap.add_argument("--no-fftlib", action="store_true", help="reference arm: skip the scipy/pocketfft variant")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -256,8 +516,19 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     pfb = importlib.import_module("dune-parafields_b200")
-    wl = {k: v for k, v in WORKLOADS[args.workload].items() if k != "label"}
+    wl = plan_kwargs(args.workload)
     slab = distributed and args.mode in ("auto", "slab")
+
+    parity = None
+    if slab:
+        err, what = slab_parity(torch, dist, pfb, local_rank, rank, world)
+        parity = dict(slab_vs_single_max_rel=err, case=what, ranks=world)
+        if err != 0.0:
+            if rank == 0:
+                print(json.dumps(dict(metric="realizations/sec", value=None, n_gpus=world, parity=parity, error="slab mode does not reproduce the single-GPU field bit for bit")))
+            dist.destroy_process_group()
+            sys.exit(1)
+
     if slab:
         plan = pfb.Plan(device=local_rank, rng_mode=args.rng, n_ranks=world, rank=rank, **wl)
     else:
@@ -279,7 +550,6 @@ def main():
     per_step = 1 if slab else world  # realizations finished per step, whole job
     apply_tr = wl.get("transform", "none") != "none"
     field = torch.empty(D, dtype=torch.float64, device="cuda")
-    seed = 20240611
     K, W = args.steps, args.warmup
 
     def barrier():
@@ -289,7 +559,7 @@ def main():
 
     # ---- warm-up -----------------------------------------------------------
     for s in range(W):
-        plan.generate(seed, ridx(s), out=field, apply_transform=apply_tr)
+        plan.generate(SEED, ridx(s), out=field, apply_transform=apply_tr)
     plan.synchronize()
 
     # ---- timed region: K realizations per rank, fields resident in HBM -----
@@ -307,10 +577,10 @@ def main():
         barrier()
     ev0.record(stream)
     if slab:
-        plan.generate_batch(seed, W, K, out=fields, apply_transform=apply_tr)
+        plan.generate_batch(SEED, W, K, out=fields, apply_transform=apply_tr)
     else:
         for s in range(K):
-            plan.generate(seed, ridx(W + s), out=field, apply_transform=apply_tr)
+            plan.generate(SEED, ridx(W + s), out=field, apply_transform=apply_tr)
     ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -323,16 +593,18 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = per_step * K / (ms * 1e-3)
+    if slab:
+        del fields
 
     # ---- e2e: host (pinned) output, D2H copy inside the timed region -------
     e2e = None
     if not args.no_e2e:
         Ke = max(2, min(K, 8))
         host = torch.empty((Ke, D), dtype=torch.float64).pin_memory()
-        plan.generate_batch(seed, 0, 2, out=host[:2], apply_transform=apply_tr)  # warm-up
+        plan.generate_batch(SEED, 0, 2, out=host[:2], apply_transform=apply_tr)  # warm-up
         barrier()
         t0 = time.perf_counter()
-        plan.generate_batch(seed, 0 if slab else rank * Ke, Ke, out=host, apply_transform=apply_tr)
+        plan.generate_batch(SEED, 0 if slab else rank * Ke, Ke, out=host, apply_transform=apply_tr)
         torch.cuda.synchronize()
         te = time.perf_counter() - t0
         if distributed:
@@ -344,13 +616,26 @@ def main():
             unit="realizations/s",
             h2d_bytes_per_step=16,
             d2h_bytes_per_step=8 * D,
+            d2h_gbs_per_gpu=8 * D * Ke / te / 1e9,
             steps=Ke,
             api="pf_generate_batch with a pinned host output buffer",
         )
         del host
 
+    # ---- the same step with fp64 normals (N = 1) ----------------------------
+    rng_other = None
+    if world == 1 and not args.no_others:
+        other = "fp64" if args.rng == "fast" else "fast"
+        plan.close()
+        plan = pfb.Plan(device=local_rank, rng_mode=other, **wl)
+        plan.set_stream(stream)
+        plan.compute_eigenvalues()
+        ms_o = timed_generate(torch, plan, stream, max(3, min(K, 10)), 3, apply_tr)
+        rng_other = dict(rng=other, value=1e3 / ms_o, unit="realizations/s", ms_per_step=ms_o, note="10 Philox rounds + fp64 Box-Muller (log, sqrt, sincospi)" if other == "fp64" else "7 Philox rounds + fp32 MUFU Box-Muller")
+
     if rank == 0:
         peaks, peak_kind = measured_peaks()
+        peak = float(peaks["hbm_gbs"])
         ab = algorithmic_bytes(wl["cells"], compact=wl.get("anisotropy", "none") != "geometric")
         # dominant kernel = the pass with the largest share of the step
         names = {0: "pass_a", 2: "pass_b", 4: "pass_c", 1: "pass_a"}
@@ -364,7 +649,6 @@ def main():
             dom, dom_ms = "step", ms / K
             ab = dict(ab, step=ab["total"])
         achieved = ab[dom] / share / (dom_ms * 1e-3) / 1e9
-        peak = float(peaks["hbm_gbs"])
         traffic = None
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
@@ -373,7 +657,7 @@ def main():
         except Exception:
             pass
         step_s = ms / K * 1e-3
-        roofline = dict(
+        hbm = dict(
             bound="hbm",
             kernel=dom,
             achieved=achieved,
@@ -393,32 +677,41 @@ def main():
             ),
             passes_ms={k: v[0] / max(v[1], 1) for k, v in shares.items()},
         )
+        roofline = hbm
         if slab:
             lay = pfb.slab_layout(wl["cells"], 2, world, 0)
             c = wl["cells"]
             m0 = c[0] + 1
             row = 16 * lay["a_count"] * (m0 if len(c) == 3 else 1)  # bytes per layer written by rank 0
             sent = row * c[-1] * (world - 1) // world  # layers owned by other ranks
-            roofline["nvlink"] = dict(
-                sent_bytes_per_gpu_per_realization=sent,
+            roofline = dict(
+                bound="nvlink",
+                kernel="pass_a (tile rows stored to the layer owners) / exchange",
                 achieved=sent / step_s / 1e9,
                 peak=770.0,
                 unit="GB/s",
                 frac=sent / step_s / 1e9 / 770.0,
+                traffic=None,
+                sent_bytes_per_gpu_per_realization=sent,
                 peak_source="measured peer copy per direction per GPU (B200_PROFILING.md)",
-                note="pass A stores to peer memory overlap with its compute; passes B and C are local",
+                note="slab mode is NVLink-bound at every N (SURVEY 8(d)): roofline time = bytes each GPU must send / 770 GB/s, overlapped with the local passes",
+                hbm=hbm,
             )
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            t_step, scale, cfg, t_eig_cpu = time_oracle(args.workload, 1, 1)
+            r = time_oracle(args.workload, 1, 1, 2 if len(wl["cells"]) == 3 else 1)
             cpu = dict(
-                value=1.0 / (t_step * scale),
+                value=1.0 / (r["mean"] * r["scale"]),
                 unit="realizations/s",
                 cores=1,
                 kind="port",
-                sample="one realization of %s cells (1/%d of the workload's cells, %.1f s), linear scaling; single thread = one MPI rank of the reference"
-                % ("x".join(map(str, cfg["cells"])), int(scale), t_step),
+                sample="one realization of %s cells (1/%d of the workload's cells, %.1f s), linear scaling; single thread = one MPI rank of the reference; the all-core figures at full size are in the --impl reference line"
+                % ("x".join(map(str, r["cells"])), int(r["scale"]), r["mean"]),
             )
+        others = None
+        if world == 1 and not args.no_others:
+            plan.close()
+            others = other_workloads(torch, pfb, stream, peak)
         line = dict(
             metric="realizations/sec",
             value=value,
@@ -436,7 +729,7 @@ def main():
                 workload=WORKLOADS[args.workload]["label"],
                 name=args.workload,
                 parallelism=(
-                    "slab x%d: one realization sharded over the GPUs, pass A scatters tile rows to the layer owners by peer stores over NVLink (no NCCL on the data path)" % world
+                    "slab x%d: one realization sharded over the GPUs, pass A scatters tile rows to the layer owners by peer stores over NVLink (CUDA IPC; no NCCL on the data path)" % world
                     if slab
                     else "replicas x%d (independent realizations, no collective)" % world
                 ),
@@ -451,6 +744,12 @@ def main():
             roofline=roofline,
             cpu_baseline=cpu,
         )
+        if rng_other:
+            line["rng_" + rng_other["rng"]] = rng_other
+        if parity:
+            line["parity"] = parity
+        if others is not None:
+            line["other_workloads"] = others
         print(json.dumps(line))
     plan.close()
     if distributed:

@@ -1,14 +1,19 @@
-// oracle/fieldgenerator_cuda.cpp -- the reference's OWN command line
-// (src/fieldgenerator.cc, compiled unmodified from /root/reference) on top of
-// this repository's CUDA path.  TEST INFRASTRUCTURE / drop-in proof.
+// fieldgenerator_cuda.cpp -- the reference's OWN command line
+// (src/fieldgenerator.cc, compiled UNMODIFIED from the reference checkout named
+// by PF_REFERENCE_CLI) on top of this repository's CUDA path.
 //
 // The only change a maintainer makes to switch the CLI over is the default
 // matrix of RandomField; here that edit is applied
 // from the outside: the class templates are compiled under other names and
 // `RandomField<GridTraits>` / `RandomFieldList<GridTraits>` are re-introduced
 // as aliases that plug parafields::CudaMatrix in.  Everything else -- the ini
-// parser calls, -key value options, seed handling, refinement flags, writers
-// -- is the reference's code.
+// parser calls, -key value options, seed handling, refinement flags, list
+// mode, writers -- is the reference's code.
+//
+// Linked against standins/fftw_sizes.cpp: the reference's traits class asks
+// FFTW-MPI for the slab sizes (fieldtraits.hh:204,368-379); those calls are
+// answered, every transform entry point aborts.  So this binary PROVES that no
+// CPU FFT runs behind the CLI.
 #define RandomField RandomFieldTemplate
 #define RandomFieldList RandomFieldListTemplate
 #include <parafields/cudamatrix.hh>
@@ -24,4 +29,7 @@ using RandomFieldList =
   RandomFieldListTemplate<GridTraits, CudaMatrix, CudaMatrix, RandomFieldTemplate>;
 } // namespace parafields
 
-#include "../../reference/src/fieldgenerator.cc"
+#ifndef PF_REFERENCE_CLI
+#error "compile with -DPF_REFERENCE_CLI='\"<reference>/src/fieldgenerator.cc\"'"
+#endif
+#include PF_REFERENCE_CLI

@@ -832,18 +832,31 @@ k_slab_signal(unsigned long long* const* flags, int n, int me,
     __threadfence_system();
   }
 }
-// thread i waits until rank i has published at least `epoch` here; bounded
-// spin (about 4 s) so that a lost peer cannot hang the device
+// thread i waits until rank i has published at least `epoch` here.  The spin
+// is bounded (limit_ns of globaltimer, PF_SLAB_TIMEOUT_S, default 120 s) so
+// that a lost peer cannot hang the device for ever; a timeout is FATAL for the
+// plan: the flag (pinned host memory) is sticky, every entry point that
+// synchronises reports PF_ERR_CUDA once it is set, and nothing computed after
+// it may be used.
+__device__ __forceinline__ unsigned long long
+global_ns()
+{
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __global__ void
 k_slab_wait(const unsigned long long* mine, int n, unsigned long long epoch,
-            int* timeout_flag)
+            volatile int* timeout_flag, unsigned long long limit_ns)
 {
   const int i = threadIdx.x;
   if (i < n) {
     const volatile unsigned long long* f = mine + i;
-    const long long t0 = clock64();
+    const unsigned long long t0 = global_ns();
+    unsigned spins = 0;
     while (*f < epoch) {
-      if (clock64() - t0 > 8000000000ll) {
+      if ((++spins & 1023u) == 0 &&
+          (*timeout_flag || global_ns() - t0 > limit_ns)) {
         *timeout_flag = 1;
         break;
       }
@@ -859,7 +872,7 @@ k_slab_wait(const unsigned long long* mine, int n, unsigned long long epoch,
 __global__ void
 k_slab_reduce(unsigned long long* const* flags, unsigned long long* mine, int n,
               int me, unsigned long long seq, int mode, double* value,
-              int* timeout_flag)
+              volatile int* timeout_flag, unsigned long long limit_ns)
 {
   __shared__ double vals[8];
   const int i = threadIdx.x;
@@ -871,9 +884,11 @@ k_slab_reduce(unsigned long long* const* flags, unsigned long long* mine, int n,
     slot[0] = seq;
     __threadfence_system();
     const volatile unsigned long long* in = mine + 16 + 2 * (par * 8 + i);
-    const long long t0 = clock64();
+    const unsigned long long t0 = global_ns();
+    unsigned spins = 0;
     while (in[0] < seq) {
-      if (clock64() - t0 > 8000000000ll) {
+      if ((++spins & 1023u) == 0 &&
+          (*timeout_flag || global_ns() - t0 > limit_ns)) {
         *timeout_flag = 1;
         break;
       }
@@ -959,7 +974,10 @@ struct pf_plan
   cplx* Z = nullptr;
   cplx* V = nullptr;
   double* spare = nullptr;
+  // 1D: pl->spare holds the imaginary part of transform (spare_seed, spare_t)
   bool spare_valid = false;
+  uint64_t spare_seed = 0, spare_t = 0;
+  int spare_rng = 0;
   double* dev_io[2] = { nullptr, nullptr }; // staging for host fields
   double* axis_tab = nullptr; // pf_field_localize: per-axis squared distances
   size_t axis_cap = 0;
@@ -972,6 +990,7 @@ struct pf_plan
   bool eig_valid = false;
   cudaStream_t stream = nullptr;
   cudaStream_t copy_stream = nullptr;
+  cudaStream_t d2h_stream = nullptr; // slab mode, host output: field copies
   // slab exchange by DMA: one stream per destination so that several copy
   // engines drive NVLink at once (PF_SLAB_STREAMS limits the fan-out)
   cudaStream_t peer_stream[8] = {};
@@ -1020,7 +1039,12 @@ struct pf_plan
   void* peer_block[8] = { nullptr };
   unsigned long long** d_flagsA = nullptr; // device arrays of peer pointers
   unsigned long long** d_flagsB = nullptr;
+  // sticky "a wait on a peer timed out" flag in pinned, device-mapped host
+  // memory: the kernels set it, slab_timed_out() reads it after a stream
+  // synchronisation without another copy
+  int* h_timeout = nullptr;
   int* d_timeout = nullptr;
+  unsigned long long slab_limit_ns = 120ull * 1000000000ull;
   bool connected = false;
   unsigned long long epoch = 0;
   // exchange by DMA (default): pass A writes the rows of other ranks into
@@ -1043,6 +1067,18 @@ struct pf_plan
 };
 
 namespace {
+
+// slab mode: call after the plan's stream has been synchronised
+int
+slab_check(const pf_plan* pl)
+{
+  if (pl->h_timeout && *(volatile int*)pl->h_timeout)
+    return fail(PF_ERR_CUDA,
+                "slab mode: timed out waiting for a peer rank (all ranks must "
+                "issue the same calls within PF_SLAB_TIMEOUT_S seconds of each "
+                "other); the plan is unusable");
+  return 0;
+}
 
 template <class T>
 int
@@ -1094,6 +1130,15 @@ supported_n(long long n)
   return launcher_for(n) != nullptr;
 }
 
+// extended sizes this build has kernels for
+bool
+size_supported(const pf_plan* pl, long long n)
+{
+  const bool long_ok = pl->dim == 2 && pl->nranks <= 1 && n > 1024 &&
+                       n <= 16384 && (n & (n - 1)) == 0;
+  return supported_n(n) || long_ok;
+}
+
 // sizes, fieldtraits.hh:214-311 (single device = single rank)
 int
 plan_resize(pf_plan* pl)
@@ -1108,10 +1153,7 @@ plan_resize(pf_plan* pl)
   for (int i = 0; i < pl->dim; i++) {
     pl->c[i] = d.cells[i];
     pl->n[i] = (long long)pl->factor * d.cells[i];
-    const bool long_ok = pl->dim == 2 && pl->nranks <= 1 &&
-                         pl->n[i] > 1024 && pl->n[i] <= 16384 &&
-                         (pl->n[i] & (pl->n[i] - 1)) == 0;
-    if (!supported_n(pl->n[i]) && !long_ok)
+    if (!size_supported(pl, pl->n[i]))
       return fail(PF_ERR_INVALID,
                   "unsupported extended size " + std::to_string(pl->n[i]) +
                     " in dimension " + std::to_string(i) +
@@ -1811,6 +1853,20 @@ eigen_once(pf_plan* pl)
   return 0;
 }
 
+// would plan_resize accept this embedding factor?  (checked BEFORE the retry
+// touches the plan, so that an unsupported doubled size leaves the plan
+// intact and the caller sees the negative-eigenvalue error with its census)
+bool
+factor_supported(const pf_plan* pl, unsigned factor)
+{
+  for (int i = 0; i < pl->dim; i++) {
+    const long long n = (long long)factor * pl->d.cells[i];
+    if (!size_supported(pl, n))
+      return false;
+  }
+  return true;
+}
+
 int
 ensure_eigen(pf_plan* pl)
 {
@@ -1820,7 +1876,7 @@ ensure_eigen(pf_plan* pl)
     PF_TRY(eigen_once(pl));
     if (pl->stats.negative_count > 0 && !pl->d.approximate) {
       if (pl->d.max_factor && pl->factor * 2 <= pl->d.max_factor &&
-          !pl->d.periodic) {
+          !pl->d.periodic && factor_supported(pl, pl->factor * 2)) {
         pl->factor *= 2; // embedding-factor retry (new behaviour, off by
                          // default; the reference only throws)
         PF_TRY(plan_resize(pl));
@@ -2185,7 +2241,7 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
   } else if (e > 2) {
     // peers must have consumed what we stored into their buffer s
     k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
-                                          e - 2, pl->d_timeout);
+                                          e - 2, pl->d_timeout, pl->slab_limit_ns);
     pl->launches++;
   }
   PassArgs a = blank_args();
@@ -2267,7 +2323,7 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
     PF_CUDA(cudaStreamWaitEvent(pl->copy_stream, pl->ev_a[s], 0));
     if (e > 2) {
       k_slab_wait<<<1, 32, 0, pl->copy_stream>>>(
-        slab_flags(pl, pl->slab_block, 1), P, e - 2, pl->d_timeout);
+        slab_flags(pl, pl->slab_block, 1), P, e - 2, pl->d_timeout, pl->slab_limit_ns);
       pl->launches++;
     }
     if (pl->a_count > 0) {
@@ -2313,7 +2369,7 @@ slab_issue_tail(pf_plan* pl, unsigned long long e, double* out_dev,
   const int P = pl->nranks;
   const int s = (int)(e & 1);
   k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e,
-                                        pl->d_timeout);
+                                        pl->d_timeout, pl->slab_limit_ns);
   pl->launches++;
   PF_TRY(inverse_tail(pl, slab_buffer(pl, pl->slab_block, s), pl->cl, out_dev,
                       transform, pl->dim == 3 && pl->n[1] % 8 == 0));
@@ -2410,7 +2466,7 @@ apply_slab_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
   const unsigned long long e1 = ++pl->epoch;
   if (e1 > 2) {
     k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
-                                          e1 - 2, pl->d_timeout);
+                                          e1 - 2, pl->d_timeout, pl->slab_limit_ns);
     pl->launches++;
   }
   for (int i = 0; i < P; i++) {
@@ -2428,14 +2484,14 @@ apply_slab_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
   }
   k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e1);
   k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e1,
-                                        pl->d_timeout);
+                                        pl->d_timeout, pl->slab_limit_ns);
   pl->launches += 2;
   // ---- fused spectral pass, tiles stored into the owners' buffers, epoch e2 ---
   const unsigned long long e2 = ++pl->epoch;
   const int s2 = (int)(e2 & 1);
   if (e2 > 2) {
     k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
-                                          e2 - 2, pl->d_timeout);
+                                          e2 - 2, pl->d_timeout, pl->slab_limit_ns);
     pl->launches++;
   }
   PassArgs s = blank_args();
@@ -2601,7 +2657,8 @@ reduce_dev(pf_plan* pl, size_t nn, const double* x, const double* y,
   if (pl->nranks > 1) {
     k_slab_reduce<<<1, 32, 0, pl->stream>>>(
       pl->d_flagsA, slab_flags(pl, pl->slab_block, 0), pl->nranks, pl->rank,
-      ++pl->red_seq, mode, pl->red_partial + RED_BLOCKS, pl->d_timeout);
+      ++pl->red_seq, mode, pl->red_partial + RED_BLOCKS, pl->d_timeout,
+      pl->slab_limit_ns);
     pl->launches++;
   }
   PF_CUDA(cudaGetLastError());
@@ -2609,7 +2666,7 @@ reduce_dev(pf_plan* pl, size_t nn, const double* x, const double* y,
   PF_CUDA(cudaMemcpyAsync(result_host, pl->red_partial + RED_BLOCKS,
                           sizeof(double), cudaMemcpyDeviceToHost, pl->stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
-  return 0;
+  return slab_check(pl);
 }
 
 // staging of host arrays
@@ -2660,7 +2717,7 @@ struct StagedOut
       PF_CUDA(cudaMemcpyAsync(host, owned, count * sizeof(double),
                               cudaMemcpyDeviceToHost, pl->stream));
     PF_CUDA(cudaStreamSynchronize(pl->stream));
-    return 0;
+    return slab_check(pl);
   }
 };
 
@@ -2690,7 +2747,8 @@ check_plan(const pf_plan* pl)
   cudaError_t e = cudaSetDevice(pl->device);
   if (e != cudaSuccess)
     return fail(PF_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
-  return 0;
+  // a plan whose peer wait timed out stays failed (fatal)
+  return slab_check(pl);
 }
 
 } // namespace
@@ -2864,11 +2922,19 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
         cudaMemset(blk, 0, bytes) != cudaSuccess ||
         cudaMalloc((void**)&pl->d_flagsA, 8 * sizeof(void*)) != cudaSuccess ||
         cudaMalloc((void**)&pl->d_flagsB, 8 * sizeof(void*)) != cudaSuccess ||
-        cudaMalloc((void**)&pl->d_timeout, sizeof(int)) != cudaSuccess ||
-        cudaMemset(pl->d_timeout, 0, sizeof(int)) != cudaSuccess) {
+        cudaHostAlloc((void**)&pl->h_timeout, sizeof(int),
+                      cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer((void**)&pl->d_timeout, pl->h_timeout, 0) !=
+          cudaSuccess) {
       cudaGetLastError();
       delete pl;
       return fail(PF_ERR_NOMEM, "slab mode: allocating the exchange block failed");
+    }
+    *pl->h_timeout = 0;
+    if (const char* env = getenv("PF_SLAB_TIMEOUT_S")) {
+      const double sec = atof(env);
+      if (sec > 0.)
+        pl->slab_limit_ns = (unsigned long long)(sec * 1e9);
     }
     pl->slab_block = static_cast<unsigned char*>(blk);
     pl->peer_block[pl->rank] = blk;
@@ -2956,10 +3022,12 @@ pf_plan_destroy(pf_plan* pl)
     cudaFree(pl->d_flagsA);
   if (pl->d_flagsB)
     cudaFree(pl->d_flagsB);
-  if (pl->d_timeout)
-    cudaFree(pl->d_timeout);
+  if (pl->h_timeout)
+    cudaFreeHost(pl->h_timeout);
   if (pl->copy_stream)
     cudaStreamDestroy(pl->copy_stream);
+  if (pl->d2h_stream)
+    cudaStreamDestroy(pl->d2h_stream);
   if (pl->tail_stream)
     cudaStreamDestroy(pl->tail_stream);
   if (pl->ev_fork)
@@ -2997,13 +3065,7 @@ pf_plan_synchronize(pf_plan* pl)
 {
   PF_TRY(check_plan(pl));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
-  if (pl->d_timeout) {
-    int t = 0;
-    PF_CUDA(cudaMemcpy(&t, pl->d_timeout, sizeof(int), cudaMemcpyDeviceToHost));
-    if (t)
-      return fail(PF_ERR_CUDA, "slab mode: timed out waiting for a peer rank");
-  }
-  return 0;
+  return slab_check(pl);
 }
 
 unsigned long long
@@ -3206,13 +3268,37 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
   const int nk = pl->d.rng_mode == 1 ? pf::NOISE_PHILOX_F64 : pf::NOISE_PHILOX_FAST;
   const bool dev = is_device_ptr(out);
   if (pl->dim == 1) {
-    // DFT backend: one transform yields two fields (matrix.hh:428-437)
+    // DFT backend: one transform yields two fields (matrix.hh:428-437).  The
+    // C ABI is stateless: realization r is the real (r even) or imaginary
+    // (r odd) part of transform r / 2; the reference's "every second call
+    // returns the spare field" protocol lives in the host plugin
+    // (cudamatrix.hh).  The plan merely caches the other half of the last
+    // transform so that the pair (2t, 2t + 1) costs one FFT.
     PF_TRY(dev_alloc(&pl->spare, pl->Dl));
     PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
+    PF_TRY(dev_alloc(&pl->dev_io[1], pl->Dl));
     for (size_t r = 0; r < count; r++) {
+      const uint64_t idx = first + r, t = idx >> 1;
+      const bool imag = (idx & 1) != 0;
       double* o = out + r * pl->Dl;
       double* dst = dev ? o : pl->dev_io[0];
-      if (pl->spare_valid) {
+      const bool cached = pl->spare_valid && pl->spare_seed == seed &&
+                          pl->spare_t == t && pl->spare_rng == nk;
+      if (!imag) {
+        // the real part; the (untransformed) imaginary part goes to the cache
+        PF_TRY(generate_dev(pl, nk, seed, t, nullptr, dst, pl->spare, tr));
+        pl->spare_valid = true;
+        pl->spare_seed = seed;
+        pl->spare_t = t;
+        pl->spare_rng = nk;
+      } else {
+        if (!cached) {
+          PF_TRY(generate_dev(pl, nk, seed, t, nullptr, pl->dev_io[1], pl->spare, 0));
+          pl->spare_valid = true;
+          pl->spare_seed = seed;
+          pl->spare_t = t;
+          pl->spare_rng = nk;
+        }
         if (tr) {
           k_transform<<<grid_for(pl->Dl), 256, 0, pl->stream>>>(
             pl->Dl, pl->spare, dst, tr, pl->d.boxcox_lambda);
@@ -3220,10 +3306,6 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
         } else
           PF_CUDA(cudaMemcpyAsync(dst, pl->spare, pl->Dl * sizeof(double),
                                   cudaMemcpyDeviceToDevice, pl->stream));
-        pl->spare_valid = false;
-      } else {
-        PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, dst, pl->spare, tr));
-        pl->spare_valid = true;
       }
       if (!dev) {
         PF_CUDA(cudaMemcpyAsync(o, dst, pl->Dl * sizeof(double),
@@ -3233,20 +3315,34 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
     }
     return 0;
   }
-  if (dev && pl->nranks > 1) {
+  if (pl->nranks > 1) {
     // slab mode, software pipelined: pass A (and the start of the exchange)
     // of realization r+1 is issued before the tail of realization r, so the
-    // NVLink transfer overlaps compute
+    // NVLink transfer overlaps compute.  Host output: the tails write two
+    // device buffers in turn and a third stream copies them out, so the D2H
+    // transfer of realization r overlaps the kernels of realization r+1.
     unsigned long long e_prev = 0, e = 0;
     // kernel exchange with an SM split: pass A stays on the plan's stream,
     // the tails go to a second stream and both run on their share of the SMs
     const bool split = pl->split_a > 0 && !pl->slab_dma && count > 1;
     cudaStream_t main_stream = pl->stream;
+    if (!dev) {
+      PF_TRY(dev_alloc(&pl->dev_io[0], pl->Dl));
+      if (count > 1)
+        PF_TRY(dev_alloc(&pl->dev_io[1], pl->Dl));
+      if (!pl->d2h_stream)
+        PF_CUDA(cudaStreamCreateWithFlags(&pl->d2h_stream, cudaStreamNonBlocking));
+    }
     if (split) {
       PF_CUDA(cudaEventRecord(pl->ev_fork, main_stream));
       PF_CUDA(cudaStreamWaitEvent(pl->tail_stream, pl->ev_fork, 0));
     }
-    auto tail = [&](unsigned long long ep, double* o) -> int {
+    auto tail = [&](unsigned long long ep, size_t r) -> int {
+      cudaStream_t ts = split ? pl->tail_stream : main_stream;
+      const int b = (int)(r & 1);
+      double* o = dev ? out + r * pl->Dl : pl->dev_io[b];
+      if (!dev && r >= 2) // the copy of realization r-2 has left this buffer
+        PF_CUDA(cudaStreamWaitEvent(ts, pl->ev_copied[b], 0));
       if (split) {
         pl->stream = pl->tail_stream;
         pl->sm_cap = pl->sm_count - pl->split_a;
@@ -3254,7 +3350,15 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
       const int rc = slab_issue_tail(pl, ep, o, tr);
       pl->stream = main_stream;
       pl->sm_cap = 0;
-      return rc;
+      PF_TRY(rc);
+      if (!dev) {
+        PF_CUDA(cudaEventRecord(pl->ev_done[b], ts));
+        PF_CUDA(cudaStreamWaitEvent(pl->d2h_stream, pl->ev_done[b], 0));
+        PF_CUDA(cudaMemcpyAsync(out + r * pl->Dl, o, pl->Dl * sizeof(double),
+                                cudaMemcpyDeviceToHost, pl->d2h_stream));
+        PF_CUDA(cudaEventRecord(pl->ev_copied[b], pl->d2h_stream));
+      }
+      return 0;
     };
     for (size_t r = 0; r < count; r++) {
       pl->sm_cap = split ? pl->split_a : 0;
@@ -3262,14 +3366,19 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
       pl->sm_cap = 0;
       PF_TRY(rc);
       if (r > 0)
-        PF_TRY(tail(e_prev, out + (r - 1) * pl->Dl));
+        PF_TRY(tail(e_prev, r - 1));
       e_prev = e;
     }
     if (count > 0)
-      PF_TRY(tail(e_prev, out + (count - 1) * pl->Dl));
+      PF_TRY(tail(e_prev, count - 1));
     if (split) {
       PF_CUDA(cudaEventRecord(pl->ev_join, pl->tail_stream));
       PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_join, 0));
+    }
+    if (!dev) {
+      PF_CUDA(cudaStreamSynchronize(pl->d2h_stream));
+      PF_CUDA(cudaStreamSynchronize(main_stream));
+      return slab_check(pl);
     }
     return 0;
   }
@@ -3349,7 +3458,7 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
   }
   PF_CUDA(cudaStreamSynchronize(pl->copy_stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
-  return 0;
+  return slab_check(pl);
 }
 
 int
@@ -3377,6 +3486,7 @@ pf_generate_from_noise(pf_plan* pl, const double* noise, double* out,
   if (pl->dim == 1) {
     PF_TRY(dev_alloc(&pl->spare, pl->Dl));
     sp = (spare && sdev) ? spare : pl->spare;
+    pl->spare_valid = false; // the Philox cache no longer describes pl->spare
   }
   PF_TRY(generate_dev(pl, pf::NOISE_INJECTED, 0, 0,
                       reinterpret_cast<const double2*>(sn.dev), dst, sp, 0));
@@ -3387,7 +3497,7 @@ pf_generate_from_noise(pf_plan* pl, const double* noise, double* out,
     PF_CUDA(cudaMemcpyAsync(spare, sp, pl->Dl * sizeof(double),
                             cudaMemcpyDeviceToHost, pl->stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
-  return 0;
+  return slab_check(pl);
 }
 
 int
@@ -3443,7 +3553,7 @@ pf_apply(pf_plan* pl, int op, const double* in, double* out)
     PF_CUDA(cudaMemcpyAsync(out, dst, pl->Dl * sizeof(double),
                             cudaMemcpyDeviceToHost, pl->stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
-  return 0;
+  return slab_check(pl);
 }
 
 // Matrix::multiplyInverse + innerCG (matrix.hh:198-215,1331-1448).  All
@@ -3521,7 +3631,7 @@ pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
                                              : cudaMemcpyDeviceToHost,
                           pl->stream));
   PF_CUDA(cudaStreamSynchronize(pl->stream));
-  return 0;
+  return slab_check(pl);
 }
 
 int

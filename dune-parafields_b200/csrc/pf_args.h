@@ -69,7 +69,7 @@ enum
 // noise sources of K_GEN_*
 enum
 {
-  NOISE_PHILOX_FAST = 0, // Philox4x32-10 + fp32 (MUFU) Box-Muller
+  NOISE_PHILOX_FAST = 0, // Philox4x32-7 + fp32 (MUFU) Box-Muller
   NOISE_PHILOX_F64 = 1,  // Philox4x32-10 + fp64 Box-Muller
   NOISE_INJECTED = 2     // caller supplied (r1,r2) pairs, reference order
 };

@@ -1,8 +1,14 @@
 // pf_rng.cuh -- counter-based white noise for the product path.
 //
-// Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3",
+// Philox4x32 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3",
 // SC'11; constants of Random123) keyed by the user seed, counter =
-// (global frequency index, realization).  The counter is a pure function of
+// (global frequency index, realization).  Two modes (pf_desc.rng_mode):
+//   fp64 (1): 10 rounds (the Random123 / cuRAND default) + fp64 Box-Muller;
+//   fast (0):  7 rounds (the smallest count Salmon et al. report as passing
+//              BigCrush) + fp32 Box-Muller on the MUFU units (lg2 / sqrt / sin
+//              / cos .approx, ~1e-6 absolute error per normal, 24-bit angle).
+// Both are pinned by known-answer tests and by a CPU restatement of
+// counter -> normals -> field (tests/test_philox.py, tests/test_gpu_noise.py).  The counter is a pure function of
 // the frequency coordinates, so a field does not depend on the launch
 // geometry or on how the spectrum is sharded over GPUs.
 //

@@ -19,7 +19,10 @@
 //                     (std::default_random_engine + std::normal_distribution,
 //                     cpprngbackend.hh:49-58) drawn on the host and injected,
 //                     so generate(seed) reproduces the reference's field
-//   cuda.rng        fast (fp32 Box-Muller, default) | fp64
+//   cuda.rng        fp64 (default: 10 Philox rounds, fp64 Box-Muller -- normals
+//                   of the reference's precision) | fast (7 rounds, fp32
+//                   Box-Muller on the special-function units; what bench.py
+//                   times by default)
 //   cuda.sampler    reference (default) | corrected   
 //   cuda.maxFactor  embedding-factor retry bound (0 = off, the reference throws)
 //   cuda.device     CUDA device ordinal (-1 = current)
@@ -125,6 +128,8 @@ public:
       plan = nullptr;
     }
     filled = false;
+    spare.clear();
+    spareSeedValid = false;
     if (dim < 1 || dim > 3)
       throw std::runtime_error{ "CudaMatrix supports dim 1, 2, 3" };
     const auto& config = (*traits).config;
@@ -200,7 +205,7 @@ public:
       throw std::runtime_error{ "cuda.noise must be \"philox\" or \"reference\"" };
     referenceNoise = (noise == "reference");
     d.rng_mode =
-      config.template get<std::string>("cuda.rng", "fast") == "fp64" ? 1 : 0;
+      config.template get<std::string>("cuda.rng", "fp64") == "fast" ? 0 : 1;
     d.parity_mode =
       config.template get<std::string>("cuda.sampler", "reference") ==
           "corrected"
@@ -304,7 +309,7 @@ public:
         "custom covariance classes are host functors and cannot be evaluated "
         "by the CUDA path"
       };
-    pf_eig_stats stats;
+    pf_eig_stats stats{};
     const int rc = pf_compute_eigenvalues(plan, &stats);
     if ((*traits).verbose && (*traits).rank == 0)
       std::cout << stats.small_count << " small, " << stats.zero_count
@@ -344,6 +349,20 @@ public:
                                      stochasticPart.dataVector.data(),
                                      dim == 1 ? spare.data() : nullptr));
       }
+    } else if (dim == 1) {
+      // DFT field backend (matrix.hh:349,428-437): the first call returns the
+      // real part of one complex transform, the next call its imaginary part
+      // WHATEVER seed it is given.  The C ABI is stateless (realization 2t /
+      // 2t+1 = real / imaginary part of transform t), so the protocol is kept
+      // here.
+      if (spareSeedValid) {
+        check(pf_generate(plan, spareSeed, 1, stochasticPart.dataVector.data(), 0));
+        spareSeedValid = false;
+      } else {
+        check(pf_generate(plan, seed, 0, stochasticPart.dataVector.data(), 0));
+        spareSeed = seed;
+        spareSeedValid = true;
+      }
     } else
       check(
         pf_generate(plan, seed, 0, stochasticPart.dataVector.data(), 0));
@@ -380,6 +399,8 @@ public:
 
 private:
   mutable std::vector<RF> spare;
+  mutable unsigned int spareSeed = 0;
+  mutable bool spareSeedValid = false;
 
   void ensureFilled() const
   {

@@ -204,7 +204,13 @@ size_t pf_local_domain_size(const pf_plan* plan);
  * slab.  pf_apply and pf_solve work on the distributed field too (`in` / `out`
  * = this rank's layers; forward exchange by DMA, backward exchange by peer
  * stores, scalar products combined over the ranks in rank order).  All ranks
- * must issue the same sequence of pf_generate*, pf_apply and pf_solve calls. */
+ * must issue the same sequence of pf_generate*, pf_apply and pf_solve calls,
+ * and no rank may fall behind its peers by more than the wait bound
+ * (PF_SLAB_TIMEOUT_S in the environment, default 120 s: eigenvalue setup,
+ * allocation or I/O between calls count).  A wait that exceeds the bound is
+ * FATAL for the plan: the call that synchronises next (pf_plan_synchronize,
+ * pf_apply, pf_solve, pf_generate* with host buffers, every later call)
+ * returns PF_ERR_CUDA and nothing computed after the timeout may be used. */
 #define PF_SLAB_HANDLE_BYTES 64
 int pf_slab_handle(pf_plan* plan, void* handle_out);
 int pf_slab_connect(pf_plan* plan, const void* handles, int count);
@@ -217,10 +223,25 @@ size_t pf_eigenvalue_count(const pf_plan* plan, int layout);
 int pf_get_eigenvalues(pf_plan* plan, double* out, size_t count, int layout);
 
 /* Matrix::generateField, matrix.hh:343-438, with device Philox noise keyed by
- * (seed, realization).  apply_transform fuses ValueTransform::apply
- * (randomfield.hh:600) into the last pass.  In 1D the DFT backend's spare
- * field protocol (matrix.hh:349,428-437) is kept: every second call returns
- * the imaginary part of the previous transform. */
+ * (seed, realization): the result is a pure function of the plan's
+ * configuration, seed and realization (no hidden state; launch geometry and
+ * slab decomposition do not enter).  apply_transform fuses
+ * ValueTransform::apply (randomfield.hh:600) into the last pass.
+ *
+ * Device noise, specification (restated on the CPU in oracle/pf_oracle.cpp and
+ * checked by tests/test_gpu_noise.py): one Philox4x32 block per pair of
+ * frequency entries, counter = (c, realization), key = seed, with
+ * c = k0 + m0 (e mod L/2) [+ m0 (L/2) k1 in 3D], e = index along the LAST
+ * frequency axis of length L; words (0,1) serve entry e < L/2, words (2,3)
+ * entry e + L/2; Box-Muller: u = (w0 + 1/2) 2^-32, radius sqrt(-2 ln u),
+ * angle pi (w1 2^-31 - 1), (r1, r2) = radius (cos, sin).  rng_mode 1: 10
+ * rounds, fp64; rng_mode 0: 7 rounds, the same formula in fp32.
+ *
+ * 1D (DFT field backend, matrix.hh:349,428-437: one complex transform yields
+ * two fields): realization r is the real part (r even) or the imaginary part
+ * (r odd) of transform r / 2.  The reference's protocol "every second
+ * generate() returns the spare field and ignores its seed" is kept by the
+ * host plugin (cudamatrix.hh), not by hidden state in the plan. */
 int pf_generate(pf_plan* plan, uint64_t seed, uint64_t realization,
                 double* out, int apply_transform);
 /* `count` realizations first..first+count-1 into out[count][domain] */

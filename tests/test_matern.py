@@ -115,11 +115,11 @@ def test_matern_nu_must_be_positive():
     assert b"matern nu has to be positive" in m.lib().pf_last_error()
 
 
-CLI = os.path.join(ROOT, "oracle", "_ref", "fieldgenerator_cuda")
+CLI = os.path.join(ROOT, "dune-parafields_b200", "cli", "_build", "fieldgenerator_cuda")
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(not os.path.exists(CLI), reason="oracle/_ref/fieldgenerator_cuda not built (no /root/reference)")
+@pytest.mark.skipif(not os.path.exists(CLI), reason="dune-parafields_b200/cli/_build/fieldgenerator_cuda not built (no /root/reference)")
 def test_reference_cli_general_matern(tmp_path):
     """`covariance = matern` + `maternNu` through the reference's own CLI
     (src/fieldgenerator.cc, unmodified) on the CUDA path: same field as the
@@ -138,7 +138,7 @@ def test_reference_cli_general_matern(tmp_path):
         elif line.startswith("LOOKUP_TABLE"):
             started = True
     vals = np.array(vals)
-    with m.Plan([32, 32], covariance="matern32", corr_length=0.1) as p:
+    with m.Plan([32, 32], covariance="matern32", corr_length=0.1, rng_mode="fp64") as p:
         ref = p.generate(seed=5, realization=0).ravel()
     assert vals.size == ref.size
     assert np.max(np.abs(vals - ref)) < 1e-4 * np.max(np.abs(ref))
