@@ -638,7 +638,11 @@ def main():
         peak = float(peaks["hbm_gbs"])
         ab = algorithmic_bytes(wl["cells"], compact=wl.get("anisotropy", "none") != "geometric")
         # dominant kernel = the pass with the largest share of the step
-        names = {0: "pass_a", 2: "pass_b", 4: "pass_c", 1: "pass_a"}
+        # 12: the fused kernel of the streaming route (first two axes in one
+        # persistent kernel, pf_stream.cuh): its algorithmic bytes are those of
+        # pass A + pass B
+        names = {0: "pass_a", 2: "pass_b", 4: "pass_c", 1: "pass_a", 12: "pass_ab"}
+        ab["pass_ab"] = ab["pass_a"] + ab["pass_b"]
         shares = {names[k]: v for k, v in times.items() if k in names}
         dom = max(shares, key=lambda k: shares[k][0]) if shares else "pass_a"
         dom_ms = shares[dom][0] / max(shares[dom][1], 1) if shares else float("nan")

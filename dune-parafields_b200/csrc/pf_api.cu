@@ -43,6 +43,11 @@ PF_DECL(1024)
 PF_DECL_PIPE(256)
 PF_DECL_PIPE(512)
 PF_DECL_PIPE(1024)
+// streaming route for large cubic 3D tori (pf_stream.cuh), N = 512 / 1024
+extern "C" int pf_stream_launch_n512(int, const void*, const void*, const void*,
+                                     int, cudaStream_t);
+extern "C" int pf_stream_launch_n1024(int, const void*, const void*, const void*,
+                                      int, cudaStream_t);
 
 namespace {
 
@@ -794,6 +799,7 @@ k_uncorrelated(size_t n, unsigned long long seed, unsigned long long q0,
 
 #include "pf_rng.cuh"
 #include "pf_long.cuh"
+#include "pf_stream.cuh"
 
 namespace {
 
@@ -973,6 +979,16 @@ struct pf_plan
   cplx* Y = nullptr;
   cplx* Z = nullptr;
   cplx* V = nullptr;
+  // streaming route (pf_stream.cuh): ring of pass-A planes (L2-resident),
+  // ticket + per-plane completion counters
+  cplx* ring = nullptr;
+  unsigned* stream_sync = nullptr;
+  int stream_slots = 0, stream_lag = 0; // 0: chosen from the problem size
+  // layout of the pass-B output of the streaming route: 0 = Zt[k0][x2][x1]
+  // (contiguous line stores, transposing pass C kp_c2rt), 1 = Z[x2][x1][k0]
+  // (16-byte stores merged by L2, contiguous-line pass C kp_c2r); PF_ZT
+  int stream_zt = 0;
+  bool stream_on = true; // PF_STREAM=0 selects the three-pass route
   double* spare = nullptr;
   // 1D: pl->spare holds the imaginary part of transform (spare_seed, spare_t)
   bool spare_valid = false;
@@ -1114,6 +1130,8 @@ free_sized(pf_plan* pl)
   dev_free(&pl->sig);
   dev_free(&pl->inv);
   dev_free(&pl->Y);
+  dev_free(&pl->ring);
+  dev_free(&pl->stream_sync);
   dev_free(&pl->Y2);
   dev_free(&pl->Z);
   dev_free(&pl->V);
@@ -1923,10 +1941,11 @@ ensure_sig_gen(pf_plan* pl, int mode)
 }
 
 int
-ensure_work(pf_plan* pl)
+ensure_work(pf_plan* pl, bool need_y = true)
 {
   if (pl->dim == 3) {
-    PF_TRY(dev_alloc(&pl->Y, (size_t)pl->m0 * pl->c[2] * pl->n[1]));
+    if (need_y)
+      PF_TRY(dev_alloc(&pl->Y, (size_t)pl->m0 * pl->c[2] * pl->n[1]));
     PF_TRY(dev_alloc(&pl->Z, (size_t)pl->c[2] * pl->c[1] * pl->m0p));
   } else if (pl->dim == 2) {
     PF_TRY(dev_alloc(&pl->Z, (size_t)pl->c[1] * pl->m0p));
@@ -2103,6 +2122,167 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
                   unsigned long long realization, const double2* noise_dev,
                   double* out_dev, int transform);
 
+// ---------------------------------------------------------------------------
+// streaming route (pf_stream.cuh): large cubic 3D tori on one GPU
+// ---------------------------------------------------------------------------
+bool
+stream_route(const pf_plan* pl)
+{
+  if (!pl->stream_on || pl->dim != 3 || pl->nranks > 1 || pl->factor != 2)
+    return false;
+  const long long N = pl->n[0];
+  if ((N != 512 && N != 1024) || pl->n[1] != N || pl->n[2] != N)
+    return false;
+  if (pl->split_one || pl->gen3_force || !(pl->pipe_mask & (1u << pf::K_GEN3)))
+    return false; // experiments / tests that pin the three-pass kernels
+  return true;
+}
+
+int
+encode_map3(void* base, cuuint64_t d0, cuuint64_t d1, cuuint64_t d2,
+            cuuint64_t s1_bytes, cuuint64_t s2_bytes, cuuint32_t b0,
+            cuuint32_t b1, cuuint32_t b2, CUtensorMapSwizzle swz, CUtensorMap* tm)
+{
+  encode_tiled_fn enc = get_encode_tiled();
+  if (!enc)
+    return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
+  const cuuint64_t gdim[3] = { d0, d1, d2 };
+  const cuuint64_t gstr[2] = { s1_bytes, s2_bytes };
+  const cuuint32_t box[3] = { b0, b1, b2 };
+  const cuuint32_t estr[3] = { 1, 1, 1 };
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, gdim, gstr,
+                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(PF_ERR_CUDA, "cuTensorMapEncodeTiled (stream) failed with code " +
+                               std::to_string((int)r));
+  return 0;
+}
+
+// `a`: pass A as prepared by generate_dev (table, noise, counters, Hermitian
+// rule; lines a = k1, b = k0, elements k2)
+int
+generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
+{
+  const long long N = pl->n[0];
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  const int lpg = N == 1024 ? 4 : 8;
+  const int grid = pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count;
+  // B-items run `lag` planes behind the A-lines: the groups in flight hold
+  // 3 * grid consecutive tickets, i.e. that many / (items per plane) planes,
+  // and a plane's A-lines must be long finished when its B-items are drawn;
+  // the ring holds the planes in between plus slack
+  if (pl->stream_lag <= 0) {
+    const long long per_plane = N / lpg + c[2] / lpg;
+    pl->stream_lag = (int)((3LL * grid + per_plane - 1) / per_plane) + 2;
+  }
+  if (pl->stream_slots < pl->stream_lag + 3) {
+    dev_free(&pl->ring);
+    pl->stream_slots = pl->stream_lag + 3;
+  }
+  const int slots = pl->stream_slots;
+  PF_TRY(dev_alloc(&pl->ring, (size_t)slots * N * c[2]));
+  const size_t nsync = 16 + 2 * (size_t)m0;
+  PF_TRY(dev_alloc(&pl->stream_sync, nsync));
+  cplx* zt = pl->Z; // [m0][c2][c1] fits the Z buffer (c2 * c1 * m0p)
+  const cplx* tw = nullptr;
+  PF_TRY(twiddles(pl, N, &tw));
+  auto fn = N == 1024 ? pf_stream_launch_n1024 : pf_stream_launch_n512;
+  PF_CUDA(cudaMemsetAsync(pl->stream_sync, 0, nsync * sizeof(unsigned), pl->stream));
+  pf::StreamArgs sa;
+  memset(&sa, 0, sizeof(sa));
+  sa.a = a;
+  sa.a.keep = (int)c[2];
+  sa.ring = pl->ring;
+  sa.slots = slots;
+  sa.zt = zt;
+  if (pl->stream_zt == 1) { // Z[x2][x1][k0], row pitch m0p
+    sa.zs_k0 = 1;
+    sa.zs_x1 = pl->m0p;
+    sa.zs_x2 = c[1] * pl->m0p;
+  } else {                  // Zt[k0][x2][x1]
+    sa.zs_k0 = c[2] * c[1];
+    sa.zs_x2 = c[1];
+    sa.zs_x1 = 1;
+  }
+  sa.c1 = (int)c[1];
+  sa.c2 = (int)c[2];
+  sa.lag = pl->stream_lag;
+  sa.sync = pl->stream_sync;
+  CUtensorMap maps[2];
+  // ring[slot][k1][x2]: box = lpg x2 (64 / 128 bytes) x 256 k1
+  PF_TRY(encode_map3(pl->ring, 2 * (cuuint64_t)c[2], (cuuint64_t)N, (cuuint64_t)slots,
+                     (cuuint64_t)c[2] * 16, (cuuint64_t)N * c[2] * 16,
+                     (cuuint32_t)(2 * lpg), 256, 1,
+                     lpg == 4 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     &maps[0]));
+  cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+  if (pl->profiling) {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventCreate(&e2);
+    cudaEventRecord(e0, pl->stream);
+  }
+  int e = fn(0, &sa, tw, maps, grid, pl->stream);
+  if (e != 0)
+    return fail(PF_ERR_CUDA, std::string("kernel launch failed (kp_ab): ") +
+                               cudaGetErrorString((cudaError_t)e));
+  pl->launches++;
+  if (pl->profiling)
+    cudaEventRecord(e1, pl->stream);
+  if (pl->stream_zt == 1) {
+    if (pl->profiling) {
+      pl->prof_events.push_back({ 12, { e0, e1 } });
+      cudaEventDestroy(e2);
+    }
+    // contiguous-line pass C of the three-pass route on Z[x2][x1][k0]
+    PassArgs c3 = blank_args();
+    c3.A = (int)(c[1] * c[2]);
+    c3.B = 1;
+    c3.in = zt;
+    c3.isa = pl->m0p;
+    c3.out = out_dev;
+    c3.out_pitch = c[0];
+    c3.keep = (int)c[0];
+    c3.transform = transform;
+    c3.tparam = pl->d.boxcox_lambda;
+    return run_pass(pl, N, pf::K_C2R, c3);
+  }
+  cudaEvent_t e1b = nullptr;
+  if (pl->profiling) {
+    cudaEventCreate(&e1b); // prof_collect destroys both events of a pair
+    cudaEventRecord(e1b, pl->stream);
+  }
+  // last axis: Zt[k0][x2][x1] -> field
+  PassArgs cc = blank_args();
+  cc.A = (int)c[1];
+  cc.B = (int)c[2];
+  cc.out = out_dev;
+  cc.out_pitch = c[0];
+  cc.keep = (int)c[0];
+  cc.transform = transform;
+  cc.tparam = pl->d.boxcox_lambda;
+  PF_TRY(encode_map3(zt, 2 * (cuuint64_t)c[1], (cuuint64_t)c[2], (cuuint64_t)m0,
+                     (cuuint64_t)c[1] * 16, (cuuint64_t)c[2] * c[1] * 16, 16, 1, 256,
+                     CU_TENSOR_MAP_SWIZZLE_128B, &maps[0]));
+  PF_TRY(encode_map3(zt, 2 * (cuuint64_t)c[1], (cuuint64_t)c[2], (cuuint64_t)m0,
+                     (cuuint64_t)c[1] * 16, (cuuint64_t)c[2] * c[1] * 16, 16, 1, 8,
+                     CU_TENSOR_MAP_SWIZZLE_128B, &maps[1]));
+  e = fn(1, &cc, tw, maps, grid, pl->stream);
+  if (e != 0)
+    return fail(PF_ERR_CUDA, std::string("kernel launch failed (kp_c2rt): ") +
+                               cudaGetErrorString((cudaError_t)e));
+  pl->launches++;
+  if (pl->profiling) {
+    cudaEventRecord(e2, pl->stream);
+    pl->prof_events.push_back({ 12, { e0, e1 } });  // fused first two axes
+    pl->prof_events.push_back({ pf::K_C2R, { e1b, e2 } });
+  }
+  return 0;
+}
+
 // Matrix::generateField (matrix.hh:343-438) into device memory
 int
 generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
@@ -2113,7 +2293,9 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     return generate_slab_dev(pl, noise_kind, seed, realization, noise_dev,
                              out_dev, transform);
   PF_TRY(ensure_sig_gen(pl, pl->hermitian ? 0 : 1));
-  PF_TRY(ensure_work(pl));
+  const bool stream = stream_route(pl) && pl->gen_phase == 0 && !pl->y_override &&
+                      (pl->Pg % 2 == 0);
+  PF_TRY(ensure_work(pl, !stream));
   const long long* n = pl->n;
   const long long* c = pl->c;
   const long long m0 = pl->m0;
@@ -2138,6 +2320,8 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     a.na_self = (int)n[1];
     a.nb_self = (int)n[0];
     a.plane_axis = 1;
+    if (stream)
+      return generate_stream(pl, a, out_dev, transform);
     cplx* Yb = pl->y_override ? pl->y_override : pl->Y;
     a.out = Yb; // Y[k0][x2][k1]
     a.osb = c[2] * n[1];
@@ -2892,6 +3076,14 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     pl->gen3_force = std::string(env) == "force";
   if (const char* env = getenv("PF_SPLIT")) // SMs for pass A in the one-GPU pipeline
     pl->split_one = atoi(env);
+  if (const char* env = getenv("PF_STREAM")) // 0: three-pass route everywhere
+    pl->stream_on = atoi(env) != 0;
+  if (const char* env = getenv("PF_RING")) // planes in the L2-resident ring
+    pl->stream_slots = std::max(2, std::min(64, atoi(env)));
+  if (const char* env = getenv("PF_LAG")) // planes pass B runs behind pass A
+    pl->stream_lag = std::max(1, std::min(32, atoi(env)));
+  if (const char* env = getenv("PF_ZT"))
+    pl->stream_zt = atoi(env);
   pl->nranks = desc->n_ranks > 1 ? desc->n_ranks : 1;
   pl->rank = pl->nranks > 1 ? desc->rank : 0;
   if (pl->nranks > 8 || pl->rank < 0 || pl->rank >= pl->nranks) {

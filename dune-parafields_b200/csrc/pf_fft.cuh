@@ -286,7 +286,9 @@ line_fft_phase1(cplx (&v)[LineCfg<N>::E], cplx* s, int t)
   }
 }
 
-template <int N, int DIR>
+// TWS: the twiddle table lives in shared memory (plain loads) instead of
+// global memory read through the non-coherent path
+template <int N, int DIR, bool TWS = false>
 PF_HD void
 line_fft_phase2(cplx (&v)[LineCfg<N>::E], const cplx* s, int t,
                 const cplx* __restrict__ tw2)
@@ -303,7 +305,7 @@ line_fft_phase2(cplx (&v)[LineCfg<N>::E], const cplx* s, int t,
 #pragma unroll
       for (int r = 1; r < C::R2; r++) {
 #ifdef __CUDA_ARCH__
-        const cplx w = __ldg(&tw2[r * 32 + jb]);
+        const cplx w = TWS ? tw2[r * 32 + jb] : __ldg(&tw2[r * 32 + jb]);
 #else
         const cplx w = tw2[r * 32 + jb];
 #endif
@@ -334,7 +336,7 @@ line_fft_phase2_load(cplx (&v)[LineCfg<N>::E], const cplx* s, int t)
       v[i + C::NB2 * r] = s[pidx(t + C::TPL * i + 32 * r)];
 }
 
-template <int N, int DIR>
+template <int N, int DIR, bool TWS = false>
 PF_HD void
 line_fft_phase2_compute(cplx (&v)[LineCfg<N>::E], int t,
                         const cplx* __restrict__ tw2)
@@ -346,7 +348,7 @@ line_fft_phase2_compute(cplx (&v)[LineCfg<N>::E], int t,
 #pragma unroll
     for (int r = 1; r < C::R2; r++) {
 #ifdef __CUDA_ARCH__
-      const cplx w = __ldg(&tw2[r * 32 + jb]);
+      const cplx w = TWS ? tw2[r * 32 + jb] : __ldg(&tw2[r * 32 + jb]);
 #else
       const cplx w = tw2[r * 32 + jb];
 #endif
@@ -358,14 +360,14 @@ line_fft_phase2_compute(cplx (&v)[LineCfg<N>::E], int t,
 }
 
 #ifdef __CUDACC__
-template <int N, int DIR>
+template <int N, int DIR, bool TWS = false>
 __device__ __forceinline__ void
 line_fft(cplx (&v)[LineCfg<N>::E], cplx* s, int t, const cplx* __restrict__ tw2)
 {
   line_fft_phase1<N, DIR>(v, s, t);
   if constexpr (LineCfg<N>::R2 > 1) {
     __syncwarp();
-    line_fft_phase2<N, DIR>(v, s, t, tw2);
+    line_fft_phase2<N, DIR, TWS>(v, s, t, tw2);
     __syncwarp();
   }
 }

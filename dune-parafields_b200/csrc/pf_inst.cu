@@ -4,6 +4,9 @@
 #if PF_N >= 256
 #include "pf_pipe.cuh"
 #endif
+#if PF_N >= 512
+#include "pf_stream.cuh"
+#endif
 
 #ifndef PF_N
 #error "compile with -DPF_N=<line length>"
@@ -194,6 +197,57 @@ extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
       break;
     default:
       break;
+  }
+  return (int)e;
+}
+#endif
+
+#if PF_N >= 512
+namespace pf {
+template <class Kern, class... Args>
+static cudaError_t
+launch_stream(Kern kern, int threads, size_t smem, int grid, cudaStream_t st,
+              Args... args)
+{
+  cudaError_t e = cudaFuncSetAttribute(
+    kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess)
+    return e;
+  kern<<<grid, threads, smem, st>>>(args...);
+  return cudaGetLastError();
+}
+} // namespace pf
+
+// streaming route (pf_stream.cuh): which = 0 fused first two axes (kp_ab),
+// `maps` -> one CUtensorMap (ring tiles); which = 1 last axis (kp_c2rt),
+// `maps` -> two CUtensorMaps (256-row and 8-row boxes of Zt)
+extern "C" int PF_CAT(pf_stream_launch_n, PF_N)(int which, const void* args,
+                                                const void* tw2v,
+                                                const void* maps, int grid,
+                                                cudaStream_t st)
+{
+  constexpr int N = PF_N;
+  using S = SCfg<N>;
+  const cplx* tw2 = reinterpret_cast<const cplx*>(tw2v);
+  const CUtensorMap* tm = reinterpret_cast<const CUtensorMap*>(maps);
+  cudaError_t e = cudaErrorInvalidValue;
+  if (grid <= 0)
+    return (int)cudaSuccess;
+  if (which == 0) {
+    const StreamArgs& sa = *reinterpret_cast<const StreamArgs*>(args);
+    if (sa.a.noise_kind == NOISE_PHILOX_FAST)
+      e = launch_stream(kp_ab<N, NOISE_PHILOX_FAST>, S::THREADS, S::SMEM, grid, st,
+                      sa, tw2, tm[0]);
+    else if (sa.a.noise_kind == NOISE_PHILOX_F64)
+      e = launch_stream(kp_ab<N, NOISE_PHILOX_F64>, S::THREADS, S::SMEM, grid, st,
+                      sa, tw2, tm[0]);
+    else
+      e = launch_stream(kp_ab<N, NOISE_INJECTED>, S::THREADS, S::SMEM, grid, st, sa,
+                      tw2, tm[0]);
+  } else {
+    const PassArgs& a = *reinterpret_cast<const PassArgs*>(args);
+    e = launch_stream(kp_c2rt<N>, S::THREADS, S::SMEM, grid, st, a, tw2, tm[0],
+                    tm[1]);
   }
   return (int)e;
 }

@@ -28,7 +28,7 @@ def main():
 
     pfb = importlib.import_module("dune-parafields_b200")
     wl = {k: v for k, v in bench.WORKLOADS[args.workload].items() if k != "label"}
-    names = {0: "A", 1: "A1d", 2: "B", 4: "C"}
+    names = {0: "A", 1: "A1d", 2: "B", 4: "C", 12: "AB"}
     for mask in args.masks.split(","):
         if mask == "default":
             os.environ.pop("PF_PIPE", None)
