@@ -455,29 +455,33 @@ def other_workloads(torch, pfb, stream, peak):
 
 
 def slab_parity(torch, dist, pfb, local_rank, rank, world):
-    """one 64^3 slab-vs-single comparison on this rank (device noise, single
-    calls and a pipelined batch); max over ranks of max|diff| / max|field|"""
-    case = dict(cells=[64, 64, 64], covariance="exponential", corr_length=0.1)
+    """slab-vs-single comparisons on this rank before the timed region (device
+    noise, single calls and a pipelined batch): a 64^3 field (exchange route)
+    and a 256^3 field (512^3 torus: the streaming route the K3 run takes);
+    max over ranks of max|diff| / max|field|"""
     worst = 0.0
-    with pfb.Plan(device=local_rank, **case) as single, pfb.Plan(device=local_rank, n_ranks=world, rank=rank, **case) as slab:
-        slab.connect()
-        layers = 64 // world
-        for r in range(3):
-            full = single.generate(SEED, r)
-            mine = slab.generate(SEED, r)
-            ref = full[rank * layers : (rank + 1) * layers]
-            worst = max(worst, float(np.max(np.abs(mine - ref)) / np.max(np.abs(full))))
-        dev = torch.empty((3, slab.local_domain_size), dtype=torch.float64, device="cuda")
-        slab.generate_batch(SEED, 10, 3, out=dev)
-        slab.synchronize()
-        for r in range(3):
-            full = single.generate(SEED, 10 + r)
-            ref = full[rank * layers : (rank + 1) * layers].ravel()
-            worst = max(worst, float(np.max(np.abs(dev[r].cpu().numpy() - ref)) / np.max(np.abs(full))))
-        dist.barrier()
+    for n in (64, 256):
+        case = dict(cells=[n, n, n], covariance="exponential", corr_length=0.1)
+        with pfb.Plan(device=local_rank, **case) as single, pfb.Plan(device=local_rank, n_ranks=world, rank=rank, **case) as slab:
+            slab.connect()
+            layers = n // world
+            for r in range(3):
+                full = single.generate(SEED, r)
+                mine = slab.generate(SEED, r)
+                ref = full[rank * layers : (rank + 1) * layers]
+                worst = max(worst, float(np.max(np.abs(mine - ref)) / np.max(np.abs(full))))
+            dev = torch.empty((3, slab.local_domain_size), dtype=torch.float64, device="cuda")
+            slab.generate_batch(SEED, 10, 3, out=dev)
+            slab.synchronize()
+            for r in range(3):
+                full = single.generate(SEED, 10 + r)
+                ref = full[rank * layers : (rank + 1) * layers].ravel()
+                worst = max(worst, float(np.max(np.abs(dev[r].cpu().numpy() - ref)) / np.max(np.abs(full))))
+            del dev
+            dist.barrier()
     t = torch.tensor([worst], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item()), "3D 64^3 exponential, 3 single calls + a pipelined batch of 3 per rank, device noise"
+    return float(t.item()), "3D 64^3 (exchange route) and 256^3 (streaming route) exponential: 3 single calls + a pipelined batch of 3 per rank each, device noise"
 
 
 def main():
@@ -701,6 +705,12 @@ def main():
                 note="slab mode is NVLink-bound at every N (SURVEY 8(d)): roofline time = bytes each GPU must send / 770 GB/s, overlapped with the local passes",
                 hbm=hbm,
             )
+            st = pfb.stream_slab_layout(wl["cells"], 2, world, 0)
+            if st and os.environ.get("PF_STREAM", "1") != "0":
+                roofline["route"] = "streaming route: every rank takes its planes of k0 through both first axes (kp_ab) and stores the twice-pruned lines to the layer owners; no exchange pass"
+                roofline["actual_sent_bytes_per_gpu_per_realization"] = st["sent_bytes"]
+                roofline["actual_nvlink_gbs"] = st["sent_bytes"] / step_s / 1e9
+                roofline["note"] += "; the streaming route moves HALF of SURVEY's bytes (the exchange happens after both prunings), so `frac` -- kept on SURVEY's byte count -- can exceed what the links would allow the transposed transform"
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             r = time_oracle(args.workload, 1, 1, 2 if len(wl["cells"]) == 3 else 1)

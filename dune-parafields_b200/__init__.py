@@ -357,6 +357,33 @@ def slab_layout(cells, factor, n_ranks, rank):
     return dict(a_begin=b0, a_count=b1 - b0, layers=layers, layer_begin=rank * layers, lines=A, line_length=N)
 
 
+def stream_slab_layout(cells, factor, n_ranks, rank):
+    """Decomposition of the streaming multi-GPU route (pf_api.cu plan_resize,
+    pf_stream.cuh): rank r takes the planes [plane_begin, plane_begin + planes)
+    of k0 through BOTH first inverse axes and stores the twice-pruned lines
+    (k0, x2, x1 < c1) into the buffer of the rank owning layer x2; every rank
+    then finishes the last axis on its layers.  None if the shape is not
+    eligible (cubic torus of 512 / 1024 per axis, factor 2, whole B-items per
+    owner)."""
+    cells = list(cells)
+    if len(cells) != 3 or factor != 2 or cells[2] % n_ranks:
+        return None
+    n = [factor * c for c in cells]
+    if n[0] not in (512, 1024) or n[1] != n[0] or n[2] != n[0]:
+        return None
+    lpg = 4 if n[0] == 1024 else 8
+    layers = cells[2] // n_ranks
+    m0 = n[0] // 2 + 1
+    if layers % lpg or m0 < n_ranks:
+        return None
+    base, extra = divmod(m0, n_ranks)
+    planes = base + (1 if rank < extra else 0)
+    begin = base * rank + min(rank, extra)
+    # bytes this rank sends to its peers per realization
+    sent = 16 * planes * (cells[2] - layers) * cells[1]
+    return dict(plane_begin=begin, planes=planes, layers=layers, layer_begin=rank * layers, sent_bytes=sent)
+
+
 class Plan:
     """Owner of one pf_plan (the CUDA counterpart of parafields::Matrix)."""
 

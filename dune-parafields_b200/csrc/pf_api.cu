@@ -988,7 +988,12 @@ struct pf_plan
   // (contiguous line stores, transposing pass C kp_c2rt), 1 = Z[x2][x1][k0]
   // (16-byte stores merged by L2, contiguous-line pass C kp_c2r); PF_ZT
   int stream_zt = 0;
-  bool stream_on = true; // PF_STREAM=0 selects the three-pass route
+  // one GPU: off by default -- measured on B200 at K3 (profiles/r2c): the fused
+  // kernel takes 4.24 ms where passes A + B take 3.74 ms (one more barrier per
+  // item and a larger instruction footprint outweigh the saved HBM traffic);
+  // PF_STREAM=1 selects it.  It is the default of the multi-GPU route, where
+  // it removes the exchange pass.
+  bool stream_on = false;
   double* spare = nullptr;
   // 1D: pl->spare holds the imaginary part of transform (spare_seed, spare_t)
   bool spare_valid = false;
@@ -1050,6 +1055,13 @@ struct pf_plan
   size_t xbuf_elems = 0;     // complex elements of one exchange buffer
   long long a_chunk = 0, a_total = 0; // rank q owns lines [q*a_chunk, ...) of a_total
   size_t fwd_elems = 0;      // forward-exchange region of the operators
+  // streaming multi-GPU route (pf_stream.cuh): this rank computes the planes
+  // [plane0, plane0 + planes) of k0 through BOTH first axes and stores pass
+  // B's lines into the owners' Zt buffers; two buffers (parity of the epoch)
+  // of m0 * cl * c1 complex numbers behind the forward region of the block
+  bool stream_slab = false;
+  int plane0 = 0, planes = 0;
+  size_t zt_elems = 0;
   unsigned long long red_seq = 0; // cross-rank reductions issued so far
   unsigned char* slab_block = nullptr; // [2 exchange buffers][flags]
   void* peer_block[8] = { nullptr };
@@ -1300,6 +1312,8 @@ plan_resize(pf_plan* pl)
   pl->Dl = pl->D;
   pl->a_begin = 0;
   pl->a_count = 0;
+  pl->stream_slab = false;
+  pl->zt_elems = 0;
   if (pl->nranks > 1) {
     const int P = pl->nranks;
     if (pl->dim < 2)
@@ -1326,6 +1340,22 @@ plan_resize(pf_plan* pl)
                     (pl->dim == 3 ? pl->m0 : 1) * pl->c[pl->dim - 1];
     pl->xbuf_elems = pl->dim == 3 ? (size_t)pl->m0 * pl->cl * pl->n[1]
                                   : (size_t)pl->cl * pl->m0p;
+    // streaming route: cubic tori of 512 / 1024, factor 2, whole B-items per
+    // owner (PF_STREAM=0: exchange route)
+    const long long N0 = pl->n[0];
+    const int lpg = N0 == 1024 ? 4 : 8;
+    bool want = pl->dim == 3 && pl->factor == 2 && (N0 == 512 || N0 == 1024) &&
+                pl->n[1] == N0 && pl->n[2] == N0 && pl->cl % lpg == 0 &&
+                pl->m0 >= P;
+    if (const char* env = getenv("PF_STREAM"))
+      want = want && atoi(env) != 0;
+    pl->stream_slab = want;
+    if (want) {
+      const long long base = pl->m0 / P, extra = pl->m0 % P;
+      pl->planes = (int)(base + (pl->rank < extra ? 1 : 0));
+      pl->plane0 = (int)(base * pl->rank + std::min<long long>(pl->rank, extra));
+      pl->zt_elems = (size_t)pl->m0 * pl->cl * pl->c[1];
+    }
   }
   return 0;
 }
@@ -2160,14 +2190,60 @@ encode_map3(void* base, cuuint64_t d0, cuuint64_t d1, cuuint64_t d2,
   return 0;
 }
 
-// `a`: pass A as prepared by generate_dev (table, noise, counters, Hermitian
-// rule; lines a = k1, b = k0, elements k2)
+// last axis of the streaming route: Zt[k0][x2 < layers][x1] -> field
 int
-generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
+stream_last_axis(pf_plan* pl, cplx* zt, long long layers, double* out_dev,
+                 int transform)
 {
   const long long N = pl->n[0];
   const long long* c = pl->c;
-  const long long m0 = pl->m0;
+  const cplx* tw = nullptr;
+  PF_TRY(twiddles(pl, N, &tw));
+  auto fn = N == 1024 ? pf_stream_launch_n1024 : pf_stream_launch_n512;
+  const int grid = pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count;
+  CUtensorMap maps[2];
+  PassArgs cc = blank_args();
+  cc.A = (int)c[1];
+  cc.B = (int)layers;
+  cc.out = out_dev;
+  cc.out_pitch = c[0];
+  cc.keep = (int)c[0];
+  cc.transform = transform;
+  cc.tparam = pl->d.boxcox_lambda;
+  PF_TRY(encode_map3(zt, 2 * (cuuint64_t)c[1], (cuuint64_t)layers, (cuuint64_t)pl->m0,
+                     (cuuint64_t)c[1] * 16, (cuuint64_t)layers * c[1] * 16, 16, 1, 256,
+                     CU_TENSOR_MAP_SWIZZLE_128B, &maps[0]));
+  PF_TRY(encode_map3(zt, 2 * (cuuint64_t)c[1], (cuuint64_t)layers, (cuuint64_t)pl->m0,
+                     (cuuint64_t)c[1] * 16, (cuuint64_t)layers * c[1] * 16, 16, 1, 8,
+                     CU_TENSOR_MAP_SWIZZLE_128B, &maps[1]));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (pl->profiling) {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, pl->stream);
+  }
+  const int e = fn(1, &cc, tw, maps, grid, pl->stream);
+  if (e != 0)
+    return fail(PF_ERR_CUDA, std::string("kernel launch failed (kp_c2rt): ") +
+                               cudaGetErrorString((cudaError_t)e));
+  pl->launches++;
+  if (pl->profiling) {
+    cudaEventRecord(e1, pl->stream);
+    pl->prof_events.push_back({ pf::K_C2R, { e0, e1 } });
+  }
+  return 0;
+}
+
+// first two axes of the streaming route for the planes [plane0, plane0 +
+// planes) of k0.  `a`: pass A as prepared by generate_dev / slab_issue_a
+// (table, noise, counters, Hermitian rule; lines a = k1, b = k0, elements k2).
+// peer_zt != nullptr: pass B's lines go to the owners' buffers (multi-GPU).
+int
+stream_first_axes(pf_plan* pl, const PassArgs& a, int plane0, int planes,
+                  cplx* zt, cplx* const* peer_zt, long long layers_per_peer)
+{
+  const long long N = pl->n[0];
+  const long long* c = pl->c;
   const int lpg = N == 1024 ? 4 : 8;
   const int grid = pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count;
   // B-items run `lag` planes behind the A-lines: the groups in flight hold
@@ -2176,7 +2252,7 @@ generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
   // the ring holds the planes in between plus slack
   if (pl->stream_lag <= 0) {
     const long long per_plane = N / lpg + c[2] / lpg;
-    pl->stream_lag = (int)((3LL * grid + per_plane - 1) / per_plane) + 2;
+    pl->stream_lag = (int)((3LL * pl->sm_count + per_plane - 1) / per_plane) + 2;
   }
   if (pl->stream_slots < pl->stream_lag + 3) {
     dev_free(&pl->ring);
@@ -2184,9 +2260,8 @@ generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
   }
   const int slots = pl->stream_slots;
   PF_TRY(dev_alloc(&pl->ring, (size_t)slots * N * c[2]));
-  const size_t nsync = 16 + 2 * (size_t)m0;
+  const size_t nsync = 16 + 2 * (size_t)pl->m0;
   PF_TRY(dev_alloc(&pl->stream_sync, nsync));
-  cplx* zt = pl->Z; // [m0][c2][c1] fits the Z buffer (c2 * c1 * m0p)
   const cplx* tw = nullptr;
   PF_TRY(twiddles(pl, N, &tw));
   auto fn = N == 1024 ? pf_stream_launch_n1024 : pf_stream_launch_n512;
@@ -2194,15 +2269,25 @@ generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
   pf::StreamArgs sa;
   memset(&sa, 0, sizeof(sa));
   sa.a = a;
+  sa.a.B = planes;
   sa.a.keep = (int)c[2];
   sa.ring = pl->ring;
   sa.slots = slots;
   sa.zt = zt;
-  if (pl->stream_zt == 1) { // Z[x2][x1][k0], row pitch m0p
+  sa.plane0 = plane0;
+  if (peer_zt) {
+    sa.n_peers = pl->nranks;
+    sa.rows_per_peer = (int)layers_per_peer;
+    for (int q = 0; q < pl->nranks; q++)
+      sa.peer_zt[q] = peer_zt[q];
+    sa.zs_k0 = layers_per_peer * c[1];
+    sa.zs_x2 = c[1];
+    sa.zs_x1 = 1;
+  } else if (pl->stream_zt == 1) { // Z[x2][x1][k0], row pitch m0p
     sa.zs_k0 = 1;
     sa.zs_x1 = pl->m0p;
     sa.zs_x2 = c[1] * pl->m0p;
-  } else {                  // Zt[k0][x2][x1]
+  } else {                         // Zt[k0][x2][x1]
     sa.zs_k0 = c[2] * c[1];
     sa.zs_x2 = c[1];
     sa.zs_x1 = 1;
@@ -2211,37 +2296,44 @@ generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
   sa.c2 = (int)c[2];
   sa.lag = pl->stream_lag;
   sa.sync = pl->stream_sync;
-  CUtensorMap maps[2];
+  CUtensorMap map;
   // ring[slot][k1][x2]: box = lpg x2 (64 / 128 bytes) x 256 k1
   PF_TRY(encode_map3(pl->ring, 2 * (cuuint64_t)c[2], (cuuint64_t)N, (cuuint64_t)slots,
                      (cuuint64_t)c[2] * 16, (cuuint64_t)N * c[2] * 16,
                      (cuuint32_t)(2 * lpg), 256, 1,
                      lpg == 4 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
-                     &maps[0]));
-  cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+                     &map));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (pl->profiling) {
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
-    cudaEventCreate(&e2);
     cudaEventRecord(e0, pl->stream);
   }
-  int e = fn(0, &sa, tw, maps, grid, pl->stream);
+  const int e = fn(0, &sa, tw, &map, grid, pl->stream);
   if (e != 0)
     return fail(PF_ERR_CUDA, std::string("kernel launch failed (kp_ab): ") +
                                cudaGetErrorString((cudaError_t)e));
   pl->launches++;
-  if (pl->profiling)
+  if (pl->profiling) {
     cudaEventRecord(e1, pl->stream);
+    pl->prof_events.push_back({ 12, { e0, e1 } }); // fused first two axes
+  }
+  return 0;
+}
+
+// one GPU: both kernels back to back
+int
+generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
+{
+  const long long N = pl->n[0];
+  const long long* c = pl->c;
+  PF_TRY(stream_first_axes(pl, a, 0, (int)pl->m0, pl->Z, nullptr, 0));
   if (pl->stream_zt == 1) {
-    if (pl->profiling) {
-      pl->prof_events.push_back({ 12, { e0, e1 } });
-      cudaEventDestroy(e2);
-    }
     // contiguous-line pass C of the three-pass route on Z[x2][x1][k0]
     PassArgs c3 = blank_args();
     c3.A = (int)(c[1] * c[2]);
     c3.B = 1;
-    c3.in = zt;
+    c3.in = pl->Z;
     c3.isa = pl->m0p;
     c3.out = out_dev;
     c3.out_pitch = c[0];
@@ -2250,37 +2342,7 @@ generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
     c3.tparam = pl->d.boxcox_lambda;
     return run_pass(pl, N, pf::K_C2R, c3);
   }
-  cudaEvent_t e1b = nullptr;
-  if (pl->profiling) {
-    cudaEventCreate(&e1b); // prof_collect destroys both events of a pair
-    cudaEventRecord(e1b, pl->stream);
-  }
-  // last axis: Zt[k0][x2][x1] -> field
-  PassArgs cc = blank_args();
-  cc.A = (int)c[1];
-  cc.B = (int)c[2];
-  cc.out = out_dev;
-  cc.out_pitch = c[0];
-  cc.keep = (int)c[0];
-  cc.transform = transform;
-  cc.tparam = pl->d.boxcox_lambda;
-  PF_TRY(encode_map3(zt, 2 * (cuuint64_t)c[1], (cuuint64_t)c[2], (cuuint64_t)m0,
-                     (cuuint64_t)c[1] * 16, (cuuint64_t)c[2] * c[1] * 16, 16, 1, 256,
-                     CU_TENSOR_MAP_SWIZZLE_128B, &maps[0]));
-  PF_TRY(encode_map3(zt, 2 * (cuuint64_t)c[1], (cuuint64_t)c[2], (cuuint64_t)m0,
-                     (cuuint64_t)c[1] * 16, (cuuint64_t)c[2] * c[1] * 16, 16, 1, 8,
-                     CU_TENSOR_MAP_SWIZZLE_128B, &maps[1]));
-  e = fn(1, &cc, tw, maps, grid, pl->stream);
-  if (e != 0)
-    return fail(PF_ERR_CUDA, std::string("kernel launch failed (kp_c2rt): ") +
-                               cudaGetErrorString((cudaError_t)e));
-  pl->launches++;
-  if (pl->profiling) {
-    cudaEventRecord(e2, pl->stream);
-    pl->prof_events.push_back({ 12, { e0, e1 } });  // fused first two axes
-    pl->prof_events.push_back({ pf::K_C2R, { e1b, e2 } });
-  }
-  return 0;
+  return stream_last_axis(pl, pl->Z, c[2], out_dev, transform);
 }
 
 // Matrix::generateField (matrix.hh:343-438) into device memory
@@ -2396,6 +2458,12 @@ slab_fwd(const pf_plan* pl, void* block)
   return reinterpret_cast<cplx*>(static_cast<unsigned char*>(block) +
                                  2 * pl->xbuf_elems * sizeof(cplx) + 512);
 }
+// streaming route: buffer `which` of pass B's output Zt[k0][x2 local][x1]
+cplx*
+slab_zt(const pf_plan* pl, void* block, int which)
+{
+  return slab_fwd(pl, block) + pl->fwd_elems + (size_t)which * pl->zt_elems;
+}
 
 // first half of a slab-mode realization: pass A + start of the exchange.
 // Returns the epoch of this realization in *epoch_out.
@@ -2417,6 +2485,45 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
   const unsigned long long e = ++pl->epoch;
   const int s = (int)(e & 1);
   *epoch_out = e;
+  if (pl->stream_slab) {
+    // streaming route: this rank takes its planes of k0 through BOTH first
+    // axes (kp_ab) and stores pass B's lines straight into the owners' Zt
+    // buffers -- no exchange pass, half the NVLink volume of the transposed
+    // transform (the lines are pruned twice before they travel)
+    if (e > 2) { // the owners have finished reading buffer s (epoch e - 2)
+      k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P,
+                                            e - 2, pl->d_timeout, pl->slab_limit_ns);
+      pl->launches++;
+    }
+    PassArgs a = blank_args();
+    set_table(pl, a, pl->sig_gen);
+    a.tab_pitch = pl->Pg;
+    a.noise_kind = noise_kind;
+    a.keys = pf::philox_keys(seed);
+    a.realization = realization;
+    a.noise = noise_dev;
+    a.hermitian = 1;
+    a.corrected = pl->d.parity_mode == 1;
+    a.A = (int)n[1]; // a = k1, b = k0 (this rank's planes), e = k2
+    a.cma = m0 * (n[2] / 2);
+    a.cmb = 1;
+    a.cme = m0;
+    a.ima = m0 * n[2];
+    a.imb = 1;
+    a.ime = m0;
+    a.na_self = (int)n[1];
+    a.nb_self = (int)n[0];
+    a.plane_axis = 1;
+    cplx* peers[8] = { nullptr };
+    for (int q = 0; q < P; q++)
+      peers[q] = slab_zt(pl, pl->peer_block[q], s);
+    PF_TRY(stream_first_axes(pl, a, pl->plane0, pl->planes, peers[pl->rank], peers,
+                             pl->cl));
+    k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e);
+    pl->launches++;
+    PF_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (pl->slab_dma) {
     for (int i = 0; i < 2; i++)
       PF_TRY(dev_alloc(&pl->send_stage[i], (size_t)(P - 1) * pl->xbuf_elems));
@@ -2548,15 +2655,19 @@ slab_issue_a(pf_plan* pl, int noise_kind, unsigned long long seed,
 // second half: wait for every rank's rows, passes B and C on the local slab
 int
 slab_issue_tail(pf_plan* pl, unsigned long long e, double* out_dev,
-                int transform)
+                int transform, bool from_zt = false)
 {
   const int P = pl->nranks;
   const int s = (int)(e & 1);
   k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e,
                                         pl->d_timeout, pl->slab_limit_ns);
   pl->launches++;
-  PF_TRY(inverse_tail(pl, slab_buffer(pl, pl->slab_block, s), pl->cl, out_dev,
-                      transform, pl->dim == 3 && pl->n[1] % 8 == 0));
+  if (from_zt)
+    PF_TRY(stream_last_axis(pl, slab_zt(pl, pl->slab_block, s), pl->cl, out_dev,
+                            transform));
+  else
+    PF_TRY(inverse_tail(pl, slab_buffer(pl, pl->slab_block, s), pl->cl, out_dev,
+                        transform, pl->dim == 3 && pl->n[1] % 8 == 0));
   // publish "buffer s consumed"
   k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsB, P, pl->rank, e);
   pl->launches++;
@@ -2571,7 +2682,7 @@ generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
 {
   unsigned long long e = 0;
   PF_TRY(slab_issue_a(pl, noise_kind, seed, realization, noise_dev, &e));
-  return slab_issue_tail(pl, e, out_dev, transform);
+  return slab_issue_tail(pl, e, out_dev, transform, pl->stream_slab);
 }
 
 // The same operators in slab mode (P ranks, fields distributed over the last
@@ -3107,8 +3218,9 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     // IPC handle describes it
     // [buffer 0][buffer 1][flags A, B, reduction slots: 512 bytes][forward
     // exchange region of the covariance operators]
-    const size_t bytes =
-      2 * pl->xbuf_elems * sizeof(cplx) + 512 + pl->fwd_elems * sizeof(cplx);
+    const size_t bytes = 2 * pl->xbuf_elems * sizeof(cplx) + 512 +
+                         pl->fwd_elems * sizeof(cplx) +
+                         2 * pl->zt_elems * sizeof(cplx);
     void* blk = nullptr;
     if (cudaMalloc(&blk, bytes) != cudaSuccess ||
         cudaMemset(blk, 0, bytes) != cudaSuccess ||
@@ -3155,6 +3267,11 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
     if (!pl->slab_dma)
       pl->split_a = (pl->nranks >= 8 ? pl->sm_count * 4 / 7
                                      : pl->sm_count * 2 / 3) & ~1;
+    // streaming route: the fused kernel is long, the last axis short; they
+    // simply alternate on one stream (kp_ab of realization r+1, then kp_c2rt of
+    // realization r, whose inputs have long arrived)
+    if (pl->stream_slab)
+      pl->split_a = 0;
     if (const char* env = getenv("PF_SLAB_SPLIT"))
       pl->split_a = std::max(0, std::min(pl->sm_count - 8, atoi(env)));
     pl->peer_streams = pl->nranks - 1;
@@ -3539,7 +3656,7 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
         pl->stream = pl->tail_stream;
         pl->sm_cap = pl->sm_count - pl->split_a;
       }
-      const int rc = slab_issue_tail(pl, ep, o, tr);
+      const int rc = slab_issue_tail(pl, ep, o, tr, pl->stream_slab);
       pl->stream = main_stream;
       pl->sm_cap = 0;
       PF_TRY(rc);

@@ -398,6 +398,7 @@ template <int N>
 struct G3Cfg
 {
   using K = KCfg<N>;
+  using C = LineCfg<N>;
   static constexpr int GROUPS = 3;
   static constexpr int THREADS = GROUPS * PF_THREADS;
   static constexpr int ROWB = K::LPC * 16;          // bytes per stage row
@@ -407,7 +408,11 @@ struct G3Cfg
   static constexpr int SIG_OFF = STAGE_BYTES;
   static constexpr int SIG_LINE = N * 8;
   static constexpr int BOXR = MAXKEEP < 256 ? MAXKEEP : 256;
-  static constexpr int SMEM = GROUPS * REGION + 64 + 1024;
+  // the table of inter-pass twiddles is copied to shared memory: with ~200 KB
+  // of shared memory in use the remaining L1 (~20 KB) misses on 10 % of the
+  // table loads (ncu, profiles/r2a), each a trip to L2
+  static constexpr int TWB = C::TW2 * 16;
+  static constexpr int SMEM = GROUPS * REGION + 64 + TWB + 1024;
   static_assert(K::LPC == 4 || K::LPC == 8, "64- or 128-byte stage rows");
   static_assert(REGION % 1024 == 0, "swizzle atoms need aligned regions");
   static_assert(SIG_OFF + K::LPC * SIG_LINE <= REGION, "landing zone");
@@ -438,6 +443,9 @@ kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
   const double* srow =
     reinterpret_cast<const double*>(region + G::SIG_OFF + lic * G::SIG_LINE);
   const uint32_t bar = smem_u32(base + G::GROUPS * G::REGION) + 8u * g;
+  cplx* tws = reinterpret_cast<cplx*>(base + G::GROUPS * G::REGION + 64);
+  for (int i = threadIdx.x; i < C::TW2; i += G::THREADS)
+    tws[i] = __ldg(tw2 + i);
   if (tg == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -474,7 +482,7 @@ kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
     if (tg == 0 && pending)
       bulk_wait_read0();
     group_sync(g);
-    line_fft<N, +1>(v, xbuf, t, tw2);
+    line_fft<N, +1, true>(v, xbuf, t, tws);
     group_sync(g);
 #pragma unroll
     for (int q = 0; q < C::E; q++) {

@@ -73,6 +73,15 @@ struct StreamArgs
   cplx* zt;            // pass B output, element (k0, x2, x1) at
   long long zs_k0, zs_x2, zs_x1; //   k0 * zs_k0 + x2 * zs_x2 + x1 * zs_x1
   int c1, c2;
+  // multi-GPU (one process per GPU): this rank computes the planes
+  // plane0 .. plane0 + planes - 1 of k0 (a.B = planes); the lines x2 of pass
+  // B's output belong to rank x2 / rows_per_peer and are stored into that
+  // rank's buffer peer_zt[] (peer memory over NVLink, x2 taken modulo
+  // rows_per_peer) -- the exchange of FFTW-MPI's transposed transform fused
+  // into the producing pass, after BOTH prunings.  n_peers <= 1: zt alone.
+  int plane0;
+  int n_peers, rows_per_peer;
+  cplx* peer_zt[8];
   int lag;             // B-items run `lag` planes behind the A-lines
   unsigned* sync;      // [0] ticket, [16 + p] A-lines done, [16 + m0 + p] B-items done
 };
@@ -291,7 +300,7 @@ kp_ab(const __grid_constant__ StreamArgs s, const cplx* __restrict__ tw2,
     uint64_t pol;
     if (!w.is_b) {
       // ================= A: noise * sigma (k0 = plane, k1 = a) ==============
-      const int b = w.plane;
+      const int b = s.plane0 + w.plane;        // global k0
       const int a = w.index * S::LPG + lic;
       if (lane == 0) {
         mbar_expect_tx(wbar, S::LPW * sig_bytes);
@@ -305,12 +314,13 @@ kp_ab(const __grid_constant__ StreamArgs s, const cplx* __restrict__ tw2,
       mbar_wait(wbar, wph);
       wph ^= 1;
       scale_noise<N>(v, p, reinterpret_cast<const double*>(xbuf), a, b, t);
-      out = s.ring + (long long)(b % s.slots) * plane_elems + (long long)a * c2 + t;
+      out = s.ring + (long long)(w.plane % s.slots) * plane_elems +
+            (long long)a * c2 + t;
       ostep = S::TPL;
       keep = c2;
       pol = keep_pol;
       if (tg == 0)
-        pendA = b;
+        pendA = w.plane;
     } else {
       // ================= B: transposed tile of the ring (k0 = plane, x2) ====
       const int pb = w.plane;
@@ -334,8 +344,14 @@ kp_ab(const __grid_constant__ StreamArgs s, const cplx* __restrict__ tw2,
       group_sync(g); // every warp holds its lines: the region becomes exchange space
       if (tg == 0)
         atomicAdd(doneB + pb, 1u);
-      out = s.zt + (long long)pb * s.zs_k0 + (long long)x2 * s.zs_x2 +
-            (long long)t * s.zs_x1;
+      if (s.n_peers > 1) {
+        const int owner = x2 / s.rows_per_peer;
+        out = s.peer_zt[owner] + (long long)(s.plane0 + pb) * s.zs_k0 +
+              (long long)(x2 - owner * s.rows_per_peer) * s.zs_x2 +
+              (long long)t * s.zs_x1;
+      } else
+        out = s.zt + (long long)pb * s.zs_k0 + (long long)x2 * s.zs_x2 +
+              (long long)t * s.zs_x1;
       ostep = (long long)S::TPL * s.zs_x1;
       keep = c1;
       pol = stream_pol;

@@ -21,6 +21,11 @@ CASES = [
     dict(cells=[32, 16, 8], covariance="gaussian", corr_length=[0.05, 0.03, 0.02], anisotropy="axiparallel", approximate=True),
     dict(cells=[256, 256], covariance="exponential", corr_length=0.05),
     dict(cells=[64, 32], covariance="cubic", corr_length=[0.08, 0.03, 0.03, 0.05], anisotropy="geometric", approximate=True),
+    # 512^3 torus: the streaming multi-GPU route (every rank takes its planes of
+    # k0 through both first axes, lines stored to the layer owners); the
+    # operators keep the exchange route
+    dict(cells=[256, 256, 256], covariance="exponential", corr_length=0.05),
+    dict(cells=[256, 256, 256], covariance="exponential", corr_length=[0.1, 0.02, 0.0, 0.02, 0.2, 0.01, 0.0, 0.01, 0.15], anisotropy="geometric", approximate=True, transform="logNormal"),
 ]
 
 

@@ -1,6 +1,6 @@
 """Streaming route (csrc/pf_stream.cuh: first two axes fused in one persistent
 kernel over an L2-resident ring of planes, transposing TMA loads, no staging
-tiles) against the three-pass route (PF_STREAM=0): same arithmetic per line,
+tiles) (PF_STREAM=1 on one GPU) against the three-pass route (PF_STREAM=0): same arithmetic per line,
 so the fields must be IDENTICAL bit for bit -- device noise in both modes,
 injected noise, fused value transform, repeated calls (ring / counter reuse),
 several ring depths."""
@@ -57,14 +57,14 @@ def test_stream_route_equals_three_pass_route(case, rng, monkeypatch):
         n = 2 * 257 * 512 * 512
         injected = torch.randn(n, dtype=torch.float64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
     ref, l_ref = run(m, case, rng, {"PF_STREAM": "0"}, monkeypatch, injected)
-    new, l_new = run(m, case, rng, {}, monkeypatch, injected)
+    new, l_new = run(m, case, rng, {"PF_STREAM": "1"}, monkeypatch, injected)
     assert l_new < l_ref  # two kernels per realization instead of three
     for a, b in zip(ref, new):
         assert torch.isfinite(a).all()
         assert torch.equal(a, b)
     if case["cells"][0] == 256 and rng == "fast":
         # ring depth / lag only change the schedule, never the values
-        for env in ({"PF_RING": "3", "PF_LAG": "1"}, {"PF_RING": "12", "PF_LAG": "5"}):
+        for env in ({"PF_STREAM": "1", "PF_RING": "3", "PF_LAG": "1"}, {"PF_STREAM": "1", "PF_RING": "12", "PF_LAG": "5"}):
             alt, _ = run(m, case, rng, env, monkeypatch, None)
             for a, b in zip(ref, alt):
                 assert torch.equal(a, b)
