@@ -75,6 +75,7 @@ struct RefBase
   virtual void refine() = 0;
   virtual void coarsen() = 0;
   virtual void evaluate(size_t n, const double* loc, double* out) = 0;
+  virtual void write(const std::string& base) = 0;
 };
 
 template<unsigned int dim>
@@ -88,6 +89,13 @@ struct Ref : RefBase
   explicit Ref(const Dune::ParameterTree& config)
     : field(new Field(config))
   {}
+  // RandomField(fileName): config from <base>.field, values from
+  // <base>.stoch.h5 / <base>.trend (randomfield.hh:190-225)
+  explicit Ref(const std::string& base)
+    : field(new Field(base))
+  {}
+  // RandomField::writeToFile (randomfield.hh:656-663)
+  void write(const std::string& base) override { field->writeToFile(base); }
 
   void generate(unsigned seed) override { field->generate(seed); }
   void generate_uncorrelated(unsigned seed) override
@@ -286,6 +294,35 @@ ref_create(const char* ini_text)
     }
   });
   return rc == 0 ? r : nullptr;
+}
+
+// file-reading constructor of RandomField; dim = dimension of the stored field
+void*
+ref_read(const char* base, int dim)
+{
+  RefBase* r = nullptr;
+  const int rc = guarded([&] {
+    switch (dim) {
+      case 1:
+        r = new Ref<1>(std::string(base));
+        break;
+      case 2:
+        r = new Ref<2>(std::string(base));
+        break;
+      case 3:
+        r = new Ref<3>(std::string(base));
+        break;
+      default:
+        throw std::runtime_error("dimension must be 1, 2 or 3");
+    }
+  });
+  return rc == 0 ? r : nullptr;
+}
+
+int
+ref_write(void* h, const char* base)
+{
+  return guarded([&] { static_cast<RefBase*>(h)->write(base); });
 }
 
 void

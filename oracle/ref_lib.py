@@ -42,6 +42,9 @@ def lib():
         L.ref_refine.argtypes = [C.c_void_p]
         L.ref_coarsen.argtypes = [C.c_void_p]
         L.ref_evaluate.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        L.ref_write.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_read.restype = C.c_void_p
+        L.ref_read.argtypes = [C.c_char_p, C.c_int]
         _lib = L
     return _lib
 
@@ -175,6 +178,22 @@ class Reference:
         self._ck(lib().ref_coarsen(self.h))
         self.cells = [c // 2 for c in self.cells]
         return self.get()
+
+    def write(self, base):
+        """RandomField::writeToFile (randomfield.hh:656-663): <base>.stoch.h5
+        (+ .xdmf), <base>.trend, <base>.field"""
+        self._ck(lib().ref_write(self.h, str(base).encode()))
+
+    @classmethod
+    def read(cls, base, cells):
+        """the file-reading constructor RandomField(fileName) (randomfield.hh:190-225)"""
+        self = cls.__new__(cls)
+        self.cells = list(cells)
+        self.text = None
+        self.h = lib().ref_read(str(base).encode(), len(cells))
+        if not self.h:
+            raise RefError(lib().ref_last_error().decode())
+        return self
 
     def evaluate(self, locations):
         """RandomField::evaluate (randomfield.hh:585-595) at n x dim locations."""
