@@ -51,7 +51,8 @@ def test_reference_files_round_trip_on_the_npy_container(tmp_path, cells, kw):
     assert np.array_equal(back.get(), f)
     # RandomField::operator* adds the trend part's product: the .trend file
     # round-trips too
-    assert back.dot_self() == r.dot_self()
+    # (the reference prints trend coefficients with 6 significant digits)
+    assert abs(back.dot_self() - r.dot_self()) <= 1e-5 * r.dot_self()
 
 
 def test_npy_header_is_plain_numpy(tmp_path):
