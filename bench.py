@@ -406,7 +406,7 @@ def other_workloads(torch, pfb, stream, peak):
                 ms = timed_generate(torch, p, stream, 20 if name != "K4" else 10, 3, tr)
                 entry(name, "generate, one call per realization", ms, algorithmic_bytes(wl["cells"], compact=compact)["total"], label=WORKLOADS[name]["label"], note="K1 is L2-resident (12.6 MB): informational" if name == "K1" else None)
                 nb = 64 if name != "K2" else 16
-                msb = timed_generate(torch, p, stream, 2, 1, tr, first=1000, batch=nb if name != "K4" else 16)
+                msb = timed_generate(torch, p, stream, 3, 1, tr, first=1000, batch=nb if name != "K4" else 16)
                 entry(name, "generate_batch (%d realizations per call; bytes of a batch of 64: sigma read once per batch)" % (nb if name != "K4" else 16), msb, algorithmic_bytes(wl["cells"], compact=compact, batch=64)["total"])
         except Exception as e:
             out.append(dict(workload=name, error="%s: %s" % (type(e).__name__, e)))

@@ -978,6 +978,8 @@ struct pf_plan
   cplx *LY = nullptr, *LU = nullptr; // step buffers of the long passes
   cplx* Y = nullptr;
   cplx* Z = nullptr;
+  cplx* Zb = nullptr;      // batched 2D generate: Z of a whole batch
+  size_t zb_elems = 0;
   cplx* V = nullptr;
   // streaming route (pf_stream.cuh): ring of pass-A planes (L2-resident),
   // ticket + per-plane completion counters
@@ -1146,6 +1148,8 @@ free_sized(pf_plan* pl)
   dev_free(&pl->stream_sync);
   dev_free(&pl->Y2);
   dev_free(&pl->Z);
+  dev_free(&pl->Zb);
+  pl->zb_elems = 0;
   dev_free(&pl->V);
   dev_free(&pl->LY);
   dev_free(&pl->LU);
@@ -2151,6 +2155,67 @@ int
 generate_slab_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
                   unsigned long long realization, const double2* noise_dev,
                   double* out_dev, int transform);
+
+// `count` realizations of a 2D field in TWO launches: pass A takes the
+// realization as its second line index (b), pass C sees count * c1 lines.
+// The sigma table is read once per batch (L2-resident for the small grids
+// where this matters: BASELINE config K1 is launch-bound one by one).
+int
+generate2d_batch(pf_plan* pl, int noise_kind, unsigned long long seed,
+                 unsigned long long first, size_t count, double* out_dev,
+                 int transform)
+{
+  PF_TRY(ensure_sig_gen(pl, 0));
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  const size_t zper = (size_t)c[1] * pl->m0p;
+  // batch buffer: at most 1 GiB of Z
+  const size_t chunk = std::max<size_t>(1, std::min<size_t>(count, ((size_t)1 << 26) / zper));
+  if (pl->zb_elems < chunk * zper) {
+    PF_CUDA(cudaStreamSynchronize(pl->stream));
+    dev_free(&pl->Zb);
+    PF_TRY(dev_alloc(&pl->Zb, chunk * zper));
+    pl->zb_elems = chunk * zper;
+  }
+  for (size_t r0 = 0; r0 < count; r0 += chunk) {
+    const size_t nb = std::min(chunk, count - r0);
+    PassArgs a = blank_args();
+    set_table(pl, a, pl->sig_gen);
+    a.tab_pitch = pl->Pg;
+    a.noise_kind = noise_kind;
+    a.keys = pf::philox_keys(seed);
+    a.realization = first + r0;
+    a.real_b = 1;
+    a.hermitian = 1;
+    a.corrected = pl->d.parity_mode == 1;
+    a.A = (int)m0; // a = k0, b = realization, e = k1
+    a.B = (int)nb;
+    a.cma = 1;
+    a.cmb = 0;
+    a.cme = m0;
+    a.na_self = (int)n[0];
+    a.nb_self = 1;
+    a.plane_axis = 0;
+    a.out = pl->Zb; // Zb[realization][x1][k0]
+    a.osb = (long long)zper;
+    a.ose = pl->m0p;
+    a.keep = (int)c[1];
+    PF_TRY(run_pass(pl, n[1], pf::K_GEN_TILE, a));
+    PassArgs cc = blank_args(); // pass C over all lines of the batch
+    cc.A = (int)(c[1] * (long long)nb);
+    cc.B = 1;
+    cc.in = pl->Zb;
+    cc.isa = pl->m0p;
+    cc.out = out_dev + r0 * pl->D;
+    cc.out_pitch = c[0];
+    cc.keep = (int)c[0];
+    cc.transform = transform;
+    cc.tparam = pl->d.boxcox_lambda;
+    PF_TRY(run_pass(pl, n[0], pf::K_C2R, cc));
+  }
+  return 0;
+}
 
 // ---------------------------------------------------------------------------
 // streaming route (pf_stream.cuh): large cubic 3D tori on one GPU
@@ -3741,6 +3806,8 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
     PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_join, 0));
     return rc;
   }
+  if (dev && pl->dim == 2 && !pl->long2d && count > 1 && pl->c[1] * (long long)count < 0x7fffffffLL)
+    return generate2d_batch(pl, nk, seed, first, count, out, tr);
   if (dev) {
     for (size_t r = 0; r < count; r++)
       PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->Dl,

@@ -127,6 +127,9 @@ struct PassArgs
   int noise_kind;
   PhiloxKeys keys;         // round keys of the user seed
   unsigned long long realization;
+  // batched 2D launches: line index b is the realization within the batch,
+  // realization word of the counter = realization + b * real_b (0 otherwise)
+  unsigned long long real_b;
   long long cma, cmb, cme; // philox counter = a*cma + b*cmb + (e mod N/2)*cme
   const double2* noise;    // injected
   long long ima, imb, ime; // injected index = a*ima + b*imb + e*ime

@@ -424,6 +424,7 @@ load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
   const int dir2 = p.tab_mirror_e ? -1 : 1;
   const unsigned long long cbase =
     (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
+  const unsigned long long rea = p.realization + (unsigned long long)b * p.real_b;
   const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
   double s1[H], s2[H];
 #pragma unroll
@@ -442,11 +443,11 @@ load_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t,
     } else {
       const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
       if constexpr (NOISE == NOISE_PHILOX_FAST) {
-        const uint4 w = philox4x32_r<7>(ctr, p.realization, p.keys);
+        const uint4 w = philox4x32_r<7>(ctr, rea, p.keys);
         n1 = box_muller_fast(w.x, w.y);
         n2 = box_muller_fast(w.z, w.w);
       } else {
-        const uint4 w = philox4x32_r<10>(ctr, p.realization, p.keys);
+        const uint4 w = philox4x32_r<10>(ctr, rea, p.keys);
         n1 = box_muller_f64(w.x, w.y);
         n2 = box_muller_f64(w.z, w.w);
       }
@@ -483,6 +484,7 @@ gen_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t)
   constexpr int H = C::E / 2;
   const unsigned long long cbase =
     (unsigned long long)a * p.cma + (unsigned long long)b * p.cmb;
+  const unsigned long long rea = p.realization + (unsigned long long)b * p.real_b;
   const long long ibase = (long long)a * p.ima + (long long)b * p.imb;
 #pragma unroll
   for (int q = 0; q < H; q++) {
@@ -494,11 +496,11 @@ gen_noise(cplx (&v)[LineCfg<N>::E], const PassArgs& p, int a, int b, int t)
     } else {
       const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
       if constexpr (NOISE == NOISE_PHILOX_FAST) {
-        const uint4 w = philox4x32_r<7>(ctr, p.realization, p.keys);
+        const uint4 w = philox4x32_r<7>(ctr, rea, p.keys);
         n1 = box_muller_fast(w.x, w.y);
         n2 = box_muller_fast(w.z, w.w);
       } else {
-        const uint4 w = philox4x32_r<10>(ctr, p.realization, p.keys);
+        const uint4 w = philox4x32_r<10>(ctr, rea, p.keys);
         n1 = box_muller_f64(w.x, w.y);
         n2 = box_muller_f64(w.z, w.w);
       }

@@ -89,6 +89,27 @@ def test_batch_equals_single_calls(m):
             assert np.array_equal(batch[i], p.generate(5, 2 + i))
 
 
+@pytest.mark.parametrize("cells", [[64, 64], [512, 512], [48 * 0 + 32, 256]], ids=["64x64", "K1", "32x256"])
+@pytest.mark.parametrize("rng", ["fast", "fp64"])
+def test_2d_batch_in_two_launches_equals_single_calls(m, cells, rng):
+    """pf_generate_batch on a device buffer, 2D: pass A takes the realization
+    as its second line index, pass C sees the lines of the whole batch"""
+    import torch
+
+    case = dict(cells=cells, covariance="exponential", corr_length=0.05, transform="logNormal", rng_mode=rng)
+    with m.Plan(**case) as p:
+        dev = torch.empty((7, p.domain_size), dtype=torch.float64, device="cuda")
+        l0 = p.launch_count
+        p.generate_batch(3, (1 << 33) + 5, 7, out=dev, apply_transform=True)
+        p.synchronize()
+        assert p.launch_count - l0 == 2
+        one = torch.empty(p.domain_size, dtype=torch.float64, device="cuda")
+        for i in range(7):
+            p.generate(3, (1 << 33) + 5 + i, out=one, apply_transform=True)
+            p.synchronize()
+            assert torch.equal(one, dev[i])
+
+
 def test_1d_is_a_pure_function_of_seed_and_realization(m):
     """pf_generate(seed, r) must not depend on the call history"""
     case = dict(cells=[64], covariance="exponential", corr_length=0.05)
