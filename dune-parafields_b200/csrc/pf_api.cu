@@ -694,15 +694,59 @@ k_residual(size_t n, const double* __restrict__ b, const double* __restrict__ Mx
        i += (size_t)gridDim.x * blockDim.x)
     r[i] = b[i] - Mx[i];
 }
-// d = z + beta d
+// ---- innerCG with device-resident scalars (matrix.hh:1385-1444) ------------
+// S[0] z.r   S[1] r.r   S[2] first energy   S[3] d.Md   S[4] old energy
+// S[5] energy   S[6] new z.r   S[7] converged (0 / 1)   S[8] iterations done
+// Every update is guarded by S[7], so an iteration enqueued after convergence
+// (the host learns about it one iteration late) changes nothing.
 __global__ void
-k_direction(size_t n, double beta, const double* __restrict__ z,
-            double* __restrict__ d)
+k_cg_init(double* S)
 {
+  S[7] = sqrt(fabs(S[1])) < 1e-6 ? 1. : 0.;
+  S[8] = 0.;
+}
+// x += alpha d, Mx += alpha Md with alpha = (z.r) / (d.Md)
+__global__ void
+k_cg_update(size_t n, const double* __restrict__ S, const double* __restrict__ d,
+            const double* __restrict__ Md, double* __restrict__ x,
+            double* __restrict__ Mx)
+{
+  if (S[7] != 0.)
+    return;
+  const double alpha = S[0] / S[3];
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    x[i] += alpha * d[i];
+    Mx[i] += alpha * Md[i];
+  }
+}
+// d = z + beta d with beta = (1 / old z.r) * new z.r  (the reference's order)
+__global__ void
+k_cg_direction(size_t n, const double* __restrict__ S,
+               const double* __restrict__ z, double* __restrict__ d)
+{
+  if (S[7] != 0.)
+    return;
+  double beta = 1. / S[0];
+  beta *= S[6];
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x)
     d[i] = z[i] + beta * d[i];
 }
+// end of an iteration: shift z.r, energy stagnation test, count
+__global__ void
+k_cg_scalars(double* S)
+{
+  if (S[7] != 0.)
+    return;
+  S[0] = S[6];
+  const double value = S[5], oldValue = S[4], firstValue = S[2];
+  if (value != firstValue)
+    if (fabs(value - oldValue) / fabs(value - firstValue) < 1e-16)
+      S[7] = 1.;
+  S[8] += 1.;
+}
+
 __global__ void
 k_transform(size_t n, const double* __restrict__ in, double* __restrict__ out,
             int kind, double lambda)
@@ -1008,6 +1052,9 @@ struct pf_plan
   double* dev_in = nullptr;
   double* cg[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
   double* red_partial = nullptr; // RED_BLOCKS + 8 doubles
+  double* cg_scalars = nullptr;  // device scalars of innerCG (k_cg_*)
+  double* cg_host = nullptr;     // pinned copies of (converged, count), 4 slots
+  cudaEvent_t cg_ev[4] = {};
   unsigned long long* census = nullptr; // 4 x u64
   pf_eig_stats stats{};
   bool eig_valid = false;
@@ -3029,6 +3076,29 @@ reduce_dev(pf_plan* pl, size_t nn, const double* x, const double* y,
   return slab_check(pl);
 }
 
+// the same reduction with the result left in device memory (`dst`): no host
+// round trip, no synchronisation
+int
+reduce_to(pf_plan* pl, size_t nn, const double* x, const double* y,
+          const double* z, int mode, double* dst)
+{
+  PF_TRY(dev_alloc(&pl->red_partial, RED_BLOCKS + 8));
+  const int nb = (int)std::min<size_t>(RED_BLOCKS, (nn + RED_THREADS - 1) / RED_THREADS);
+  k_reduce1<<<std::max(nb, 1), RED_THREADS, 0, pl->stream>>>(nn, x, y, z, mode,
+                                                           pl->red_partial);
+  k_reduce2<<<1, RED_THREADS, 0, pl->stream>>>(std::max(nb, 1), pl->red_partial,
+                                               mode, dst);
+  pl->launches += 2;
+  if (pl->nranks > 1) {
+    k_slab_reduce<<<1, 32, 0, pl->stream>>>(
+      pl->d_flagsA, slab_flags(pl, pl->slab_block, 0), pl->nranks, pl->rank,
+      ++pl->red_seq, mode, dst, pl->d_timeout, pl->slab_limit_ns);
+    pl->launches++;
+  }
+  PF_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // staging of host arrays
 struct Staged
 {
@@ -3379,6 +3449,12 @@ pf_plan_destroy(pf_plan* pl)
   for (int i = 0; i < 6; i++)
     dev_free(&pl->cg[i]);
   dev_free(&pl->red_partial);
+  dev_free(&pl->cg_scalars);
+  if (pl->cg_host)
+    cudaFreeHost(pl->cg_host);
+  for (int i = 0; i < 4; i++)
+    if (pl->cg_ev[i])
+      cudaEventDestroy(pl->cg_ev[i]);
   dev_free(&pl->census);
   for (int q = 0; q < pl->nranks; q++)
     if (q != pl->rank && pl->peer_block[q])
@@ -3932,8 +4008,8 @@ pf_apply(pf_plan* pl, int op, const double* in, double* out)
   return slab_check(pl);
 }
 
-// Matrix::multiplyInverse + innerCG (matrix.hh:198-215,1331-1448).  All
-// vectors stay in HBM; only the scalars of the recurrence visit the host.
+// Matrix::multiplyInverse + innerCG (matrix.hh:198-215,1331-1448).  Vectors AND
+// the scalars of the recurrence stay in HBM.
 int
 pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
 {
@@ -3970,35 +4046,62 @@ pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
     PF_TRY(apply_dev(pl, PF_OP_INVERSE_EXT, r, z));
     PF_CUDA(cudaMemcpyAsync(dir, z, D * sizeof(double), cudaMemcpyDeviceToDevice,
                             pl->stream));
-    double scalarProd, scalarProd2, firstValue;
-    PF_TRY(reduce_dev(pl, D, z, r, nullptr, 0, &scalarProd));
-    PF_TRY(reduce_dev(pl, D, r, r, nullptr, 0, &scalarProd2));
-    bool converged = std::sqrt(std::fabs(scalarProd2)) < 1e-6;
-    PF_TRY(reduce_dev(pl, D, x, Mx, b, 3, &firstValue));
-    while (!converged && count < pl->d.cg_iterations) {
+    // scalars of the recurrence stay on the device (k_cg_*); the host only
+    // learns "converged?" -- one iteration late, through a pinned copy -- to
+    // decide whether to enqueue another iteration.  The decision for iteration
+    // i + 1 uses the flag after iteration i - 1 (a blocking wait on that copy),
+    // so it is deterministic and identical on all ranks of a slab plan; the
+    // one iteration that may be enqueued after convergence is a no-op.
+    PF_TRY(dev_alloc(&pl->cg_scalars, 16));
+    if (!pl->cg_host) {
+      PF_CUDA(cudaHostAlloc((void**)&pl->cg_host, 4 * 2 * sizeof(double),
+                            cudaHostAllocDefault));
+      for (int i = 0; i < 4; i++)
+        PF_CUDA(cudaEventCreateWithFlags(&pl->cg_ev[i], cudaEventDisableTiming));
+    }
+    double* S = pl->cg_scalars;
+    PF_TRY(reduce_to(pl, D, z, r, nullptr, 0, S + 0));
+    PF_TRY(reduce_to(pl, D, r, r, nullptr, 0, S + 1));
+    PF_TRY(reduce_to(pl, D, x, Mx, b, 3, S + 2));
+    k_cg_init<<<1, 1, 0, pl->stream>>>(S);
+    pl->launches++;
+    auto publish = [&](int slot) -> int {
+      PF_CUDA(cudaMemcpyAsync(pl->cg_host + 2 * slot, S + 7, 2 * sizeof(double),
+                              cudaMemcpyDeviceToHost, pl->stream));
+      PF_CUDA(cudaEventRecord(pl->cg_ev[slot], pl->stream));
+      return 0;
+    };
+    PF_TRY(publish(3)); // state before the first iteration
+    PF_CUDA(cudaEventSynchronize(pl->cg_ev[3]));
+    bool converged = pl->cg_host[2 * 3] != 0.;
+    const unsigned maxit = pl->d.cg_iterations;
+    unsigned enq = 0; // iterations enqueued
+    while (!converged && enq < maxit) {
       PF_TRY(apply_dev(pl, PF_OP_MATRIX, dir, Md));
-      double alphaDenominator, oldValue, value;
-      PF_TRY(reduce_dev(pl, D, dir, Md, nullptr, 0, &alphaDenominator));
-      const double alpha = scalarProd / alphaDenominator;
-      PF_TRY(reduce_dev(pl, D, x, Mx, b, 3, &oldValue));
-      k_axpy<<<g, 256, 0, pl->stream>>>(D, alpha, dir, x);
-      k_axpy<<<g, 256, 0, pl->stream>>>(D, alpha, Md, Mx);
-      pl->launches += 2;
-      PF_TRY(reduce_dev(pl, D, x, Mx, b, 3, &value));
+      PF_TRY(reduce_to(pl, D, dir, Md, nullptr, 0, S + 3));
+      PF_TRY(reduce_to(pl, D, x, Mx, b, 3, S + 4));
+      k_cg_update<<<g, 256, 0, pl->stream>>>(D, S, dir, Md, x, Mx);
+      pl->launches++;
+      PF_TRY(reduce_to(pl, D, x, Mx, b, 3, S + 5));
       k_residual<<<g, 256, 0, pl->stream>>>(D, b, Mx, r);
       pl->launches++;
       PF_TRY(apply_dev(pl, PF_OP_INVERSE_EXT, r, z));
-      double beta = 1. / scalarProd;
-      PF_TRY(reduce_dev(pl, D, z, r, nullptr, 0, &scalarProd));
-      beta *= scalarProd;
-      k_direction<<<g, 256, 0, pl->stream>>>(D, beta, z, dir);
-      pl->launches++;
-      if (value != firstValue) {
-        if (std::fabs(value - oldValue) / std::fabs(value - firstValue) < 1e-16)
-          converged = true;
+      PF_TRY(reduce_to(pl, D, z, r, nullptr, 0, S + 6));
+      k_cg_direction<<<g, 256, 0, pl->stream>>>(D, S, z, dir);
+      k_cg_scalars<<<1, 1, 0, pl->stream>>>(S);
+      pl->launches += 2;
+      PF_TRY(publish((int)(enq % 3)));
+      enq++;
+      if (enq >= 2) { // flag after iteration enq - 2
+        const int slot = (int)((enq - 2) % 3);
+        PF_CUDA(cudaEventSynchronize(pl->cg_ev[slot]));
+        converged = pl->cg_host[2 * slot] != 0.;
       }
-      count++;
     }
+    // final state: the number of iterations that really ran
+    PF_TRY(publish(3));
+    PF_CUDA(cudaEventSynchronize(pl->cg_ev[3]));
+    count = (unsigned)pl->cg_host[2 * 3 + 1];
   }
   if (iterations)
     *iterations = count;

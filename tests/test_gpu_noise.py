@@ -99,6 +99,7 @@ def test_2d_batch_in_two_launches_equals_single_calls(m, cells, rng):
     case = dict(cells=cells, covariance="exponential", corr_length=0.05, transform="logNormal", rng_mode=rng)
     with m.Plan(**case) as p:
         dev = torch.empty((7, p.domain_size), dtype=torch.float64, device="cuda")
+        p.generate(3, 0, out=dev[0])  # eigenvalues, tables
         l0 = p.launch_count
         p.generate_batch(3, (1 << 33) + 5, 7, out=dev, apply_transform=True)
         p.synchronize()
