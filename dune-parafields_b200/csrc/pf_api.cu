@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <complex>
 #include <cstdlib>
 #include <cmath>
 #include <cstdio>
@@ -844,6 +845,7 @@ k_uncorrelated(size_t n, unsigned long long seed, unsigned long long q0,
 #include "pf_rng.cuh"
 #include "pf_long.cuh"
 #include "pf_stream.cuh"
+#include "pf_generic.cuh"
 
 namespace {
 
@@ -1014,6 +1016,17 @@ struct pf_plan
   double* sig = nullptr;
   double* inv = nullptr;
   std::map<long long, cplx*> tw; // twiddle tables per line length
+  // arbitrary extended sizes (pf_generic.cuh): natural-order arrays, one
+  // shared-memory transform per line (Bluestein for non powers of two)
+  bool generic = false;
+  struct GenTab
+  {
+    int M = 0;
+    cplx *chirp = nullptr, *bhat = nullptr;
+  };
+  std::map<std::pair<long long, int>, GenTab> gen_tabs; // (n, dir)
+  std::map<long long, cplx*> gen_tw;                    // per M
+  cplx* GW = nullptr; // stored spectrum m0 * n1 * n2
   // 2D plans with an axis longer than 1024 (pf_long.cuh): n[i] = LN1[i] * LN2[i]
   bool long2d = false;
   long long LN1[2] = { 1, 1 }, LN2[2] = { 1, 1 };
@@ -1200,6 +1213,7 @@ free_sized(pf_plan* pl)
   dev_free(&pl->V);
   dev_free(&pl->LY);
   dev_free(&pl->LU);
+  dev_free(&pl->GW);
   dev_free(&pl->spare);
   pl->spare_valid = false;
   pl->eig_valid = false;
@@ -1212,12 +1226,24 @@ supported_n(long long n)
 }
 
 // extended sizes this build has kernels for
+// generic route: any even length (any length in 1D) whose shared-memory
+// transform fits: powers of two up to 4096, otherwise 2 n - 1 <= 4096
+bool
+generic_n(const pf_plan* pl, long long n)
+{
+  if (pl->nranks > 1 || n < 2 || (pl->dim > 1 && n % 2 != 0))
+    return false;
+  if ((n & (n - 1)) == 0)
+    return n <= 4096;
+  return 2 * n - 1 <= 4096;
+}
+
 bool
 size_supported(const pf_plan* pl, long long n)
 {
   const bool long_ok = pl->dim == 2 && pl->nranks <= 1 && n > 1024 &&
                        n <= 16384 && (n & (n - 1)) == 0;
-  return supported_n(n) || long_ok;
+  return supported_n(n) || long_ok || generic_n(pl, n);
 }
 
 // sizes, fieldtraits.hh:214-311 (single device = single rank)
@@ -1238,8 +1264,10 @@ plan_resize(pf_plan* pl)
       return fail(PF_ERR_INVALID,
                   "unsupported extended size " + std::to_string(pl->n[i]) +
                     " in dimension " + std::to_string(i) +
-                    " (this build supports powers of two, 2..1024, and up to "
-                    "16384 for single-GPU 2D fields)");
+                    " (this build supports powers of two up to 1024 per axis "
+                    "[16384 in 2D] on the specialised kernels, and on one GPU any "
+                    "even size up to 2048 [any size in 1D, powers of two up to "
+                    "4096] on the generic route)");
     pl->D *= pl->c[i];
     pl->Next *= pl->n[i];
   }
@@ -1248,7 +1276,23 @@ plan_resize(pf_plan* pl)
   pl->m0 = pl->hermitian ? pl->n[0] / 2 + 1 : pl->n[0];
   pl->m0p = (pl->m0 + 7) / 8 * 8;
   pl->long2d = false;
-  if (pl->dim == 2 && (pl->n[0] > 1024 || pl->n[1] > 1024)) {
+  // generic route: some axis has no specialised kernel (not a power of two, or
+  // longer than the line kernels in 3D / mixed with one in 2D)
+  pl->generic = false;
+  for (int i = 0; i < pl->dim; i++) {
+    const long long ni = pl->n[i];
+    const bool long_ok = pl->dim == 2 && pl->nranks <= 1 && ni > 1024 &&
+                         ni <= 16384 && (ni & (ni - 1)) == 0;
+    if (!supported_n(ni) && !long_ok)
+      pl->generic = true;
+  }
+  if (pl->generic)
+    for (int i = 0; i < pl->dim; i++)
+      if (!generic_n(pl, pl->n[i]))
+        return fail(PF_ERR_INVALID,
+                    "unsupported combination of extended sizes (generic route: "
+                    "every axis even and <= 2048, or a power of two <= 4096)");
+  if (!pl->generic && pl->dim == 2 && (pl->n[0] > 1024 || pl->n[1] > 1024)) {
     pl->long2d = true;
     for (int i = 0; i < 2; i++) {
       pl->LN2[i] = std::min<long long>(pl->n[i], 1024);
@@ -1269,6 +1313,8 @@ plan_resize(pf_plan* pl)
     pl->P = pl->n[0];
   }
   pl->tab_elems = (size_t)pl->rows * pl->P;
+  if (pl->generic) // natural order [k2][k1][k0 < m0]
+    pl->tab_elems = (size_t)pl->m0 * pl->n[1] * pl->n[2];
   pl->Pg = (pl->P + 1) & ~1LL;
 
   // covariance parameters (matrix.hh:624-648, covariance.hh:17-136)
@@ -1821,6 +1867,243 @@ eigen_long2d(pf_plan* pl)
 }
 
 // ---------------------------------------------------------------------------
+// generic route (pf_generic.cuh): host side
+// ---------------------------------------------------------------------------
+// tables of one (length, direction): the shared-memory transform length M, the
+// twiddles of M, and for Bluestein the chirp and the spectrum of its conjugate
+int
+gen_tables(pf_plan* pl, long long n, int dir, pf::GenLineArgs& g)
+{
+  const bool pow2 = (n & (n - 1)) == 0;
+  int M = (int)n;
+  if (!pow2) {
+    M = 1;
+    while (M < 2 * n - 1)
+      M <<= 1;
+  }
+  g.n = (int)n;
+  g.M = M;
+  g.dir = dir;
+  auto tw = pl->gen_tw.find(M);
+  if (tw == pl->gen_tw.end()) {
+    std::vector<cplx> h((size_t)std::max(M / 2, 1));
+    for (int m = 0; m < M / 2; m++) {
+      const long double a = -2.0L * 3.14159265358979323846264338327950288L * m / M;
+      h[m] = make_double2((double)cosl(a), (double)sinl(a));
+    }
+    cplx* d = nullptr;
+    PF_TRY(dev_alloc(&d, h.size()));
+    PF_CUDA(cudaMemcpy(d, h.data(), h.size() * sizeof(cplx), cudaMemcpyHostToDevice));
+    tw = pl->gen_tw.emplace((long long)M, d).first;
+  }
+  g.twM = tw->second;
+  g.chirp = nullptr;
+  g.bhat = nullptr;
+  if (pow2)
+    return 0;
+  auto key = std::make_pair(n, dir);
+  auto it = pl->gen_tabs.find(key);
+  if (it == pl->gen_tabs.end()) {
+    // w_j = exp(dir pi i j^2 / n), j^2 reduced modulo 2n for accuracy
+    std::vector<cplx> w((size_t)n);
+    std::vector<std::complex<long double>> b((size_t)M, { 0, 0 });
+    for (long long j = 0; j < n; j++) {
+      const long long q = (j * j) % (2 * n);
+      const long double a = dir * 3.14159265358979323846264338327950288L * q / n;
+      w[j] = make_double2((double)cosl(a), (double)sinl(a));
+      const std::complex<long double> c(cosl(a), -sinl(a)); // conj(w_j)
+      b[j] = c;
+      if (j > 0)
+        b[M - j] = c;
+    }
+    // forward FFT of b on the host (long double, recursive radix 2)
+    std::vector<std::complex<long double>> tmp(b.size());
+    for (int len = 1; len < M; len <<= 1) {
+      const int T = M / 2, tstep = T / len;
+      for (int j = 0; j < T; j++) {
+        const int k = j & (len - 1);
+        const long double a = -2.0L * 3.14159265358979323846264338327950288L * (k * tstep) / M;
+        const std::complex<long double> tww(cosl(a), sinl(a));
+        const auto u0 = b[j], u1 = b[j + T] * tww;
+        const int j0 = ((j - k) << 1) + k;
+        tmp[j0] = u0 + u1;
+        tmp[j0 + len] = u0 - u1;
+      }
+      b.swap(tmp);
+    }
+    std::vector<cplx> bh((size_t)M);
+    for (int j = 0; j < M; j++)
+      bh[j] = make_double2((double)b[j].real(), (double)b[j].imag());
+    pf_plan::GenTab t;
+    t.M = M;
+    PF_TRY(dev_alloc(&t.chirp, w.size()));
+    PF_TRY(dev_alloc(&t.bhat, bh.size()));
+    PF_CUDA(cudaMemcpy(t.chirp, w.data(), w.size() * sizeof(cplx), cudaMemcpyHostToDevice));
+    PF_CUDA(cudaMemcpy(t.bhat, bh.data(), bh.size() * sizeof(cplx), cudaMemcpyHostToDevice));
+    it = pl->gen_tabs.emplace(key, t).first;
+  }
+  g.chirp = it->second.chirp;
+  g.bhat = it->second.bhat;
+  return 0;
+}
+
+// one batch of lines through k_generic_lines; `g` carries addressing and modes
+int
+gen_lines(pf_plan* pl, long long n, int dir, pf::GenLineArgs g)
+{
+  PF_TRY(gen_tables(pl, n, dir, g));
+  const long long lines = g.L0 * g.L1;
+  if (lines <= 0)
+    return 0;
+  if (lines > 0x7fffffffLL)
+    return fail(PF_ERR_INVALID, "generic route: too many lines");
+  const size_t smem = 2 * (size_t)g.M * sizeof(cplx);
+  static bool attr_set = false;
+  if (!attr_set) {
+    PF_CUDA(cudaFuncSetAttribute(pf::k_generic_lines,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 2 * 4096 * (int)sizeof(cplx)));
+    attr_set = true;
+  }
+  pf::k_generic_lines<<<(unsigned)lines, 256, smem, pl->stream>>>(g);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return 0;
+}
+
+pf::GenGeom
+gen_geom(const pf_plan* pl)
+{
+  pf::GenGeom g;
+  g.dim = pl->dim;
+  for (int i = 0; i < 3; i++)
+    g.n[i] = pl->n[i];
+  g.m0 = pl->m0;
+  g.half = (pl->n[pl->dim - 1] + 1) / 2;
+  return g;
+}
+
+pf::GenLineArgs
+gen_blank()
+{
+  pf::GenLineArgs g;
+  memset(&g, 0, sizeof(g));
+  g.L0 = g.L1 = 1;
+  g.scale = 1.0;
+  return g;
+}
+
+// inverse transform of the stored spectrum W[k2][k1][k0 < m0] into a field
+// (backwardTransform + extendedFieldToField, r2cfieldbackend.hh:250-274,423-441;
+// 1D: dftfieldbackend.hh:223-247,380-393), pruned axis by axis
+int
+generic_inverse(pf_plan* pl, cplx* W, double* out_dev, double* spare_dev,
+                int transform)
+{
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  if (pl->dim == 1) {
+    pf::GenLineArgs g = gen_blank();
+    g.in_mode = 0;
+    g.in = W;
+    g.in_se = 1;
+    g.n_valid = (int)n[0];
+    g.out_mode = 2;
+    g.out = out_dev;
+    g.out2 = spare_dev;
+    g.out_se = 1;
+    g.keep = (int)c[0];
+    g.transform = transform;
+    g.tparam = pl->d.boxcox_lambda;
+    return gen_lines(pl, n[0], +1, g);
+  }
+  if (pl->dim == 3) { // axis 2: lines (k0, k1), keep x2 < c2
+    pf::GenLineArgs g = gen_blank();
+    g.L0 = m0;
+    g.L1 = n[1];
+    g.in = g.out = W;
+    g.in_s0 = g.out_s0 = 1;
+    g.in_s1 = g.out_s1 = m0;
+    g.in_se = g.out_se = m0 * n[1];
+    g.n_valid = (int)n[2];
+    g.keep = (int)c[2];
+    PF_TRY(gen_lines(pl, n[2], +1, g));
+  }
+  { // axis 1: lines (k0, x2 < c2), keep x1 < c1
+    pf::GenLineArgs g = gen_blank();
+    g.L0 = m0;
+    g.L1 = pl->dim == 3 ? c[2] : 1;
+    g.in = g.out = W;
+    g.in_s0 = g.out_s0 = 1;
+    g.in_s1 = g.out_s1 = m0 * n[1];
+    g.in_se = g.out_se = m0;
+    g.n_valid = (int)n[1];
+    g.keep = (int)c[1];
+    PF_TRY(gen_lines(pl, n[1], +1, g));
+  }
+  { // axis 0, c2r: lines (x1 < c1, x2 < c2) -> real field, keep x0 < c0
+    pf::GenLineArgs g = gen_blank();
+    g.L0 = c[1];
+    g.L1 = pl->dim == 3 ? c[2] : 1;
+    g.in_mode = 2;
+    g.in = W;
+    g.in_s0 = m0;
+    g.in_s1 = m0 * n[1];
+    g.in_se = 1;
+    g.out_mode = 1;
+    g.out = out_dev;
+    g.out_s0 = c[0];
+    g.out_s1 = c[0] * c[1];
+    g.out_se = 1;
+    g.keep = (int)c[0];
+    g.transform = transform;
+    g.tparam = pl->d.boxcox_lambda;
+    PF_TRY(gen_lines(pl, n[0], +1, g));
+  }
+  return 0;
+}
+
+// Matrix::fillTransformedMatrix on the generic route: full complex transforms
+// of the torus covariance (one-time cost), table in natural order
+int
+eigen_generic(pf_plan* pl)
+{
+  const long long* n = pl->n;
+  const long long N = (long long)pl->Next;
+  cplx* C = nullptr;
+  PF_TRY(dev_alloc(&C, (size_t)N));
+  const pf::GenGeom gg = gen_geom(pl);
+  pf::k_generic_cov<<<grid_for((size_t)N), 256, 0, pl->stream>>>(gg, pl->cov, C, N);
+  pl->launches++;
+  int rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "k_generic_cov");
+  const long long str[3] = { 1, n[0], n[0] * n[1] };
+  for (int ax = 0; ax < pl->dim && rc == 0; ax++) {
+    pf::GenLineArgs g = gen_blank();
+    const int o0 = ax == 0 ? 1 : 0, o1 = ax == 2 ? 1 : 2;
+    g.L0 = n[o0];
+    g.L1 = n[o1];
+    g.in = g.out = C;
+    g.in_s0 = g.out_s0 = str[o0];
+    g.in_s1 = g.out_s1 = str[o1];
+    g.in_se = g.out_se = str[ax];
+    g.n_valid = g.keep = (int)n[ax];
+    rc = gen_lines(pl, n[ax], -1, g);
+  }
+  if (rc == 0) {
+    const long long total = (long long)pl->tab_elems;
+    pf::k_generic_lambda<<<grid_for((size_t)total), 256, 0, pl->stream>>>(
+      gg, C, pl->lam, 1.0 / (double)pl->Next, pl->d.threshold, pl->compact ? 1 : 0,
+      pl->census, pl->census + 3, total);
+    pl->launches++;
+    rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "k_generic_lambda");
+  }
+  cudaStreamSynchronize(pl->stream);
+  cudaFree(C);
+  return rc;
+}
+
+// ---------------------------------------------------------------------------
 // eigenvalues: Matrix::fillTransformedMatrix, matrix.hh:232-331
 // ---------------------------------------------------------------------------
 int
@@ -1836,7 +2119,9 @@ eigen_once(pf_plan* pl)
                             cudaMemcpyHostToDevice, pl->stream));
   }
   const double invN = 1.0 / (double)pl->Next;
-  if (pl->dim == 1) {
+  if (pl->generic) {
+    PF_TRY(eigen_generic(pl));
+  } else if (pl->dim == 1) {
     PassArgs a = blank_args();
     a.A = 1;
     a.B = 1;
@@ -2457,6 +2742,90 @@ generate_stream(pf_plan* pl, const PassArgs& a, double* out_dev, int transform)
   return stream_last_axis(pl, pl->Z, c[2], out_dev, transform);
 }
 
+// generateField and the covariance operators on the generic route
+int
+generate_generic(pf_plan* pl, int noise_kind, unsigned long long seed,
+                 unsigned long long realization, const double2* noise_dev,
+                 double* out_dev, double* spare_dev, int transform)
+{
+  PF_TRY(ensure_table(pl, &pl->sig_gen, pl->hermitian ? 0 : 1));
+  PF_TRY(dev_alloc(&pl->GW, pl->tab_elems));
+  const pf::GenGeom gg = gen_geom(pl);
+  const long long total = (long long)pl->tab_elems;
+  const pf::PhiloxKeys keys = pf::philox_keys(seed);
+  const unsigned grid = grid_for((size_t)total);
+  const int herm = pl->hermitian ? 1 : 0, corr = pl->d.parity_mode == 1;
+  if (noise_kind == pf::NOISE_PHILOX_FAST)
+    pf::k_generic_noise<pf::NOISE_PHILOX_FAST><<<grid, 256, 0, pl->stream>>>(
+      gg, pl->sig_gen, keys, realization, noise_dev, herm, corr, pl->GW, total);
+  else if (noise_kind == pf::NOISE_PHILOX_F64)
+    pf::k_generic_noise<pf::NOISE_PHILOX_F64><<<grid, 256, 0, pl->stream>>>(
+      gg, pl->sig_gen, keys, realization, noise_dev, herm, corr, pl->GW, total);
+  else
+    pf::k_generic_noise<pf::NOISE_INJECTED><<<grid, 256, 0, pl->stream>>>(
+      gg, pl->sig_gen, keys, realization, noise_dev, herm, corr, pl->GW, total);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return generic_inverse(pl, pl->GW, out_dev, spare_dev, transform);
+}
+
+int
+apply_generic(pf_plan* pl, const double* tab, const double* in_dev, double* out_dev)
+{
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  PF_TRY(dev_alloc(&pl->GW, pl->tab_elems));
+  cplx* W = pl->GW;
+  { // axis 0 (r2c; 1D: complex transform of the real line), zero padding implicit
+    pf::GenLineArgs g = gen_blank();
+    g.L0 = pl->dim > 1 ? c[1] : 1;
+    g.L1 = pl->dim == 3 ? c[2] : 1;
+    g.in_mode = 1;
+    g.in = in_dev;
+    g.in_s0 = c[0];
+    g.in_s1 = c[0] * c[1];
+    g.in_se = 1;
+    g.n_valid = (int)c[0];
+    g.out = W;
+    g.out_s0 = m0;
+    g.out_s1 = m0 * n[1];
+    g.out_se = 1;
+    g.keep = (int)m0;
+    PF_TRY(gen_lines(pl, n[0], -1, g));
+  }
+  if (pl->dim >= 2) { // axis 1: lines (k0, x2 < c2), input x1 < c1
+    pf::GenLineArgs g = gen_blank();
+    g.L0 = m0;
+    g.L1 = pl->dim == 3 ? c[2] : 1;
+    g.in = g.out = W;
+    g.in_s0 = g.out_s0 = 1;
+    g.in_s1 = g.out_s1 = m0 * n[1];
+    g.in_se = g.out_se = m0;
+    g.n_valid = (int)c[1];
+    g.keep = (int)n[1];
+    PF_TRY(gen_lines(pl, n[1], -1, g));
+  }
+  if (pl->dim == 3) { // axis 2: lines (k0, k1), input x2 < c2
+    pf::GenLineArgs g = gen_blank();
+    g.L0 = m0;
+    g.L1 = n[1];
+    g.in = g.out = W;
+    g.in_s0 = g.out_s0 = 1;
+    g.in_s1 = g.out_s1 = m0;
+    g.in_se = g.out_se = m0 * n[1];
+    g.n_valid = (int)c[2];
+    g.keep = (int)n[2];
+    PF_TRY(gen_lines(pl, n[2], -1, g));
+  }
+  const long long total = (long long)pl->tab_elems;
+  pf::k_generic_mult<<<grid_for((size_t)total), 256, 0, pl->stream>>>(
+    W, tab, 1.0 / (double)pl->Next, total);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  return generic_inverse(pl, W, out_dev, nullptr, 0);
+}
+
 // Matrix::generateField (matrix.hh:343-438) into device memory
 int
 generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
@@ -2466,6 +2835,9 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
   if (pl->nranks > 1)
     return generate_slab_dev(pl, noise_kind, seed, realization, noise_dev,
                              out_dev, transform);
+  if (pl->generic)
+    return generate_generic(pl, noise_kind, seed, realization, noise_dev, out_dev,
+                            spare_dev, transform);
   PF_TRY(ensure_sig_gen(pl, pl->hermitian ? 0 : 1));
   const bool stream = stream_route(pl) && pl->gen_phase == 0 && !pl->y_override &&
                       (pl->Pg % 2 == 0);
@@ -2949,7 +3321,7 @@ apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
 {
   if (pl->nranks > 1)
     return apply_slab_dev(pl, op, in_dev, out_dev);
-  if (pl->long2d)
+  if (pl->long2d && !pl->generic)
     return fail(PF_ERR_INVALID,
                 "covariance operators need extended sizes <= 1024 in this "
                 "build (sampling supports up to 16384 in 2D)");
@@ -2960,6 +3332,8 @@ apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
     PF_TRY(ensure_eigen(pl));
   else
     PF_TRY(ensure_table(pl, tabp, op == PF_OP_ROOT ? 1 : 2));
+  if (pl->generic)
+    return apply_generic(pl, *tabp, in_dev, out_dev);
   PF_TRY(ensure_work(pl));
   const double* tab = *tabp;
   const long long* n = pl->n;
@@ -3441,6 +3815,12 @@ pf_plan_destroy(pf_plan* pl)
     cudaFree(kv.second);
   for (auto& kv : pl->twl)
     cudaFree(kv.second);
+  for (auto& kv : pl->gen_tw)
+    cudaFree(kv.second);
+  for (auto& kv : pl->gen_tabs) {
+    cudaFree(kv.second.chirp);
+    cudaFree(kv.second.bhat);
+  }
   dev_free(&pl->dev_io[0]);
   dev_free(&pl->dev_io[1]);
   dev_free(&pl->axis_tab);
@@ -3676,8 +4056,13 @@ pf_get_eigenvalues(pf_plan* pl, double* out, size_t count, int layout)
     PF_TRY(dev_alloc(&tmp, total));
     dst = tmp;
   }
-  k_gather_lambda<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
-    pl->lam, dst, g, total);
+  if (pl->generic)
+    pf::k_generic_gather<<<grid_for(total), 256, 0, pl->stream>>>(
+      gen_geom(pl), pl->lam, dst, g.ob[0], g.ob[1], g.ob[2], g.transposed,
+      (long long)total);
+  else
+    k_gather_lambda<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
+      pl->lam, dst, g, total);
   cudaError_t e = cudaGetLastError();
   pl->launches++;
   if (e == cudaSuccess && !dev)
@@ -3882,7 +4267,7 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
     PF_CUDA(cudaStreamWaitEvent(main_stream, pl->ev_join, 0));
     return rc;
   }
-  if (dev && pl->dim == 2 && !pl->long2d && count > 1 && pl->c[1] * (long long)count < 0x7fffffffLL)
+  if (dev && pl->dim == 2 && !pl->long2d && !pl->generic && count > 1 && pl->c[1] * (long long)count < 0x7fffffffLL)
     return generate2d_batch(pl, nk, seed, first, count, out, tr);
   if (dev) {
     for (size_t r = 0; r < count; r++)

@@ -1486,7 +1486,7 @@ orc_field_bulk_evaluate(int dim, const unsigned* cells,
 // as 1, 2, 3", SC'11, Philox4x32-R with the Random123 multipliers and Weyl
 // key increments -- and not from the CUDA source:
 //   counter = (c lo, c hi, realization lo, realization hi), key = (seed lo,
-//   seed hi); c = k0 + m0 * (e mod L/2) [+ m0 * (L/2) * k1 in 3D], where e is
+//   seed hi); c = k0 + m0 * (e mod H) [+ m0 * H * k1 in 3D], H = ceil(L/2), where e is
 //   the index along the LAST frequency axis (length L) and one Philox block of
 //   four words serves the two entries e and e + L/2: words (0,1) -> entry
 //   e < L/2, words (2,3) -> entry e + L/2.  Box-Muller on a word pair (w0,w1):
@@ -1551,7 +1551,7 @@ philox_noise(const OrcCfg& cfg, uint64_t seed, uint64_t realization, int mode,
   const uint32_t key[2] = { (uint32_t)seed, (uint32_t)(seed >> 32) };
   const bool dft = cfg.field_backend == 1;
   const size_t b0 = dft ? s.n[0] : s.m0;
-  const size_t L = s.n[d - 1], half = L / 2;
+  const size_t L = s.n[d - 1], half = (L + 1) / 2; // odd L (1D only): ceil
   const bool tr = cfg.transposed && d == 3;
   const size_t S = b0 * (d > 1 ? s.n[1] : 1) * (d > 2 ? s.n[2] : 1);
   for (size_t idx = 0; idx < S; idx++) {

@@ -60,6 +60,13 @@ CASES = {
     "cov_whiteNoise_1d": dict(cells=[64], covariance="whiteNoise", corr_length=0.07),
     "cov_cauchy_2d": dict(cells=[32, 32], covariance="cauchy", corr_length=0.05, approximate=True),
     "cov_matern52_3d": dict(cells=[8, 8, 8], covariance="matern52", corr_length=0.1, approximate=True),
+    # extended sizes that are not powers of two (FFTW takes any n, fieldtraits.hh:268)
+    "anysize_1d": dict(cells=[25], covariance="exponential", corr_length=0.05),
+    "anysize_1d_odd": dict(cells=[37], covariance="exponential", corr_length=0.05, factor=3, cg_iterations=2),
+    "anysize_2d": dict(cells=[50, 30], covariance="exponential", corr_length=0.1),
+    "anysize_2d_geometric": dict(cells=[18, 26], covariance="cubic", corr_length=[0.08, 0.03, 0.03, 0.05], anisotropy="geometric", approximate=True),
+    "anysize_3d": dict(cells=[12, 10, 14], covariance="spherical", corr_length=0.3, extensions=[1.0, 0.8, 1.2]),
+    "anysize_3d_gaussian": dict(cells=[6, 20, 9], covariance="gaussian", corr_length=[0.05, 0.03, 0.02], anisotropy="axiparallel", transform="logNormal", approximate=True, factor=4),
 }
 SEED = 20240611
 
