@@ -76,6 +76,10 @@ def test_long_operators_fail_loudly(m):
             p.apply("matrix", np.zeros((8, 1024)))
 
 
-def test_long_3d_unsupported(m):
-    with pytest.raises(m.PfError, match="unsupported extended size"):
-        m.Plan([1024, 4, 4], covariance="exponential", corr_length=0.05)
+def test_long_3d_limits(m):
+    # 3D axes of 2048 / 4096 take the generic route (tests/test_gpu_anysize.py);
+    # beyond the shared-memory transform length they are refused
+    with m.Plan([1024, 4, 4], covariance="exponential", corr_length=0.05) as p:
+        assert p.extended_size == 2048 * 8 * 8
+    with pytest.raises(m.PfError, match="unsupported"):
+        m.Plan([4096, 4, 4], covariance="exponential", corr_length=0.05)
