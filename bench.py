@@ -461,7 +461,7 @@ def slab_parity(torch, dist, pfb, local_rank, rank, world):
     max over ranks of max|diff| / max|field|"""
     worst = 0.0
     for n in (64, 256):
-        case = dict(cells=[n, n, n], covariance="exponential", corr_length=0.1)
+        case = dict(cells=[n, n, n], covariance="exponential", corr_length=0.05)
         with pfb.Plan(device=local_rank, **case) as single, pfb.Plan(device=local_rank, n_ranks=world, rank=rank, **case) as slab:
             slab.connect()
             layers = n // world

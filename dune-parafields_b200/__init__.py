@@ -38,6 +38,7 @@ COVARIANCE = {
     "cubic": 10,
     "whiteNoise": 11,
     "matern": 12,  # general nu = cov_param[0] (stochastic.maternNu)
+    "custom": 13,  # custom-iso / custom-aniso: values through set_covariance_table
 }
 ANISOTROPY = {"none": 0, "axiparallel": 1, "geometric": 2}
 TRANSFORM = {"none": 0, "logNormal": 1, "foldedNormal": 2, "sign": 3, "boxCox": 4}
@@ -66,6 +67,7 @@ ABI_SYMBOLS = [
     "pf_local_domain_size",
     "pf_slab_handle",
     "pf_slab_connect",
+    "pf_set_covariance_table",
     "pf_compute_eigenvalues",
     "pf_eigenvalue_count",
     "pf_get_eigenvalues",
@@ -210,6 +212,7 @@ def lib():
     for f in (L.pf_domain_size, L.pf_extended_size, L.pf_noise_entries, L.pf_local_domain_size):
         f.argtypes = [vp]
         f.restype = sz
+    L.pf_set_covariance_table.argtypes = [vp, dp, sz]
     L.pf_compute_eigenvalues.argtypes = [vp, C.POINTER(PfEigStats)]
     L.pf_eigenvalue_count.argtypes = [vp, C.c_int]
     L.pf_eigenvalue_count.restype = sz
@@ -480,6 +483,15 @@ class Plan:
         dist.barrier(group)
 
     # -- eigenvalues ---------------------------------------------------------
+    def set_covariance_table(self, values):
+        """custom covariance: its values on the extended domain, natural order"""
+        if isinstance(values, np.ndarray):
+            values = np.ascontiguousarray(values, dtype=np.float64)
+            n = values.size
+        else:
+            n = values.numel()
+        _check(lib().pf_set_covariance_table(self._h, _ptr(values), n))
+
     def compute_eigenvalues(self):
         st = PfEigStats()
         rc = lib().pf_compute_eigenvalues(self._h, C.byref(st))

@@ -1027,6 +1027,9 @@ struct pf_plan
   std::map<std::pair<long long, int>, GenTab> gen_tabs; // (n, dir)
   std::map<long long, cplx*> gen_tw;                    // per M
   cplx* GW = nullptr; // stored spectrum m0 * n1 * n2
+  // custom covariance (custom-iso / custom-aniso, matrix.hh:270-279): the torus
+  // covariance evaluated by the caller, natural order [x2][x1][x0]
+  double* cov_table = nullptr;
   // 2D plans with an axis longer than 1024 (pf_long.cuh): n[i] = LN1[i] * LN2[i]
   bool long2d = false;
   long long LN1[2] = { 1, 1 }, LN2[2] = { 1, 1 };
@@ -1286,6 +1289,8 @@ plan_resize(pf_plan* pl)
     if (!supported_n(ni) && !long_ok)
       pl->generic = true;
   }
+  if (d.covariance == PF_COV_CUSTOM && (pl->dim == 1 || pl->n[0] > 1024 || pl->n[1] > 1024))
+    pl->generic = true; // the table-reading eigenvalue passes exist for short 2D / 3D lines
   if (pl->generic)
     for (int i = 0; i < pl->dim; i++)
       if (!generic_n(pl, pl->n[i]))
@@ -2074,7 +2079,10 @@ eigen_generic(pf_plan* pl)
   cplx* C = nullptr;
   PF_TRY(dev_alloc(&C, (size_t)N));
   const pf::GenGeom gg = gen_geom(pl);
-  pf::k_generic_cov<<<grid_for((size_t)N), 256, 0, pl->stream>>>(gg, pl->cov, C, N);
+  if (pl->cov_table)
+    pf::k_generic_cov_table<<<grid_for((size_t)N), 256, 0, pl->stream>>>(pl->cov_table, C, N);
+  else
+    pf::k_generic_cov<<<grid_for((size_t)N), 256, 0, pl->stream>>>(gg, pl->cov, C, N);
   pl->launches++;
   int rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "k_generic_cov");
   const long long str[3] = { 1, n[0], n[0] * n[1] };
@@ -2119,6 +2127,9 @@ eigen_once(pf_plan* pl)
                             cudaMemcpyHostToDevice, pl->stream));
   }
   const double invN = 1.0 / (double)pl->Next;
+  if (pl->d.covariance == PF_COV_CUSTOM && !pl->cov_table)
+    return fail(PF_ERR_INVALID, // matrix.hh:236-239
+                "you need to call fillMatrix with your covariance class as parameter");
   if (pl->generic) {
     PF_TRY(eigen_generic(pl));
   } else if (pl->dim == 1) {
@@ -2148,7 +2159,12 @@ eigen_once(pf_plan* pl)
     a.osb = 0;
     a.ose = n[1];
     a.keep = (int)m0;
-    int rc = run_pass(pl, n[0], pf::K_R2C_COV, a);
+    if (pl->cov_table) { // custom covariance: rows of the uploaded torus table
+      a.in = pl->cov_table;
+      a.isa = n[0];
+      a.n_valid = (int)n[0];
+    }
+    int rc = run_pass(pl, n[0], pl->cov_table ? pf::K_R2C_LOAD : pf::K_R2C_COV, a);
     if (rc == 0) {
       PassArgs e = blank_args();
       e.A = (int)m0;
@@ -2184,7 +2200,13 @@ eigen_once(pf_plan* pl)
       a.osb = m0 * n[1];
       a.ose = n[1];
       a.keep = (int)m0;
-      rc = run_pass(pl, n[0], pf::K_R2C_COV, a);
+      if (pl->cov_table) { // custom covariance: rows of the uploaded torus table
+        a.in = pl->cov_table;
+        a.isa = n[0];
+        a.isb = n[0] * n[1];
+        a.n_valid = (int)n[0];
+      }
+      rc = run_pass(pl, n[0], pl->cov_table ? pf::K_R2C_LOAD : pf::K_R2C_COV, a);
     }
     if (rc == 0) {
       PassArgs a = blank_args(); // E1: x1 lines, (a,b) = (x2,k0)
@@ -3631,8 +3653,12 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
   *out = nullptr;
   if (desc->dim < 1 || desc->dim > 3)
     return fail(PF_ERR_INVALID, "dimension must be 1, 2 or 3");
-  if (desc->covariance < 0 || desc->covariance > PF_COV_MATERN)
+  if (desc->covariance < 0 || desc->covariance > PF_COV_CUSTOM)
     return fail(PF_ERR_INVALID, "covariance structure not known");
+  if (desc->covariance == PF_COV_CUSTOM &&
+      (desc->periodization != 0 || desc->max_factor != 0 || desc->n_ranks > 1))
+    return fail(PF_ERR_INVALID, "custom covariance tables: classical periodisation, "
+                                "no embedding-factor retry, one GPU");
   // covariance.hh:547-548 (nu = 0 divides by Gamma(0) there; rejected too)
   if (desc->covariance == PF_COV_MATERN && !(desc->cov_param[0] > 0.))
     return fail(PF_ERR_INVALID, "matern nu has to be positive");
@@ -3829,6 +3855,7 @@ pf_plan_destroy(pf_plan* pl)
   for (int i = 0; i < 6; i++)
     dev_free(&pl->cg[i]);
   dev_free(&pl->red_partial);
+  dev_free(&pl->cov_table);
   dev_free(&pl->cg_scalars);
   if (pl->cg_host)
     cudaFreeHost(pl->cg_host);
@@ -3995,6 +4022,28 @@ pf_noise_entries(const pf_plan* pl)
   if (!pl)
     return 0;
   return (size_t)pl->m0 * pl->n[1] * pl->n[2];
+}
+
+int
+pf_set_covariance_table(pf_plan* pl, const double* values, size_t count)
+{
+  PF_TRY(check_plan(pl));
+  if (pl->d.covariance != PF_COV_CUSTOM)
+    return fail(PF_ERR_INVALID, // matrix.hh:272-276
+                "you can't fill the matrix explicitly if a default covariance was chosen");
+  if (!values || count != pl->Next)
+    return fail(PF_ERR_INVALID, "pf_set_covariance_table: need one value per cell of the extended domain");
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  PF_TRY(dev_alloc(&pl->cov_table, pl->Next));
+  PF_CUDA(cudaMemcpyAsync(pl->cov_table, values, pl->Next * sizeof(double),
+                          cudaMemcpyDefault, pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  // eigenvalues and everything derived from them are stale
+  pl->eig_valid = false;
+  dev_free(&pl->sig_gen);
+  dev_free(&pl->sig);
+  dev_free(&pl->inv);
+  return 0;
 }
 
 int

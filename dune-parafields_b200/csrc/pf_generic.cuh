@@ -159,6 +159,16 @@ k_generic_cov(GenGeom g, CovParams cov, cplx* __restrict__ C, long long total)
   }
 }
 
+// the same from a caller-supplied table (custom covariance)
+__global__ void
+k_generic_cov_table(const double* __restrict__ table, cplx* __restrict__ C,
+                    long long total)
+{
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x)
+    C[i] = make_double2(table[i], 0.);
+}
+
 // eigenvalues: Re / N of the transformed covariance on the stored index set
 // (k0 < m0), census over the entries the reference's matrix backend stores
 // (compact: k_i <= n_i / 2 for i >= 1; matrix.hh:283-306), clamp

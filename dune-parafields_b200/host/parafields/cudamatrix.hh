@@ -94,11 +94,10 @@ private:
     for (const auto& e : table)
       if (name == e.first)
         return e.second;
+    // host functors of the caller: evaluated once on the host into a table
+    // (fillTransformedMatrix<Covariance>, pf_set_covariance_table)
     if (name == "custom-iso" || name == "custom-aniso")
-      throw std::runtime_error{
-        "custom covariance classes are host functors and cannot be evaluated "
-        "by the CUDA path"
-      };
+      return PF_COV_CUSTOM;
     // same text as matrix.hh:267-268
     throw std::runtime_error{ "covariance structure " + name + " not known" };
   }
@@ -152,7 +151,17 @@ public:
     // covariance.hh:32,61,94 (arity follows the anisotropy)
     const std::string anisotropy =
       config.template get<std::string>("stochastic.anisotropy", "none");
-    if (anisotropy == "none") {
+    if (d.covariance == PF_COV_CUSTOM) {
+      // always evaluated with ScaledIdentityMatrix (matrix.hh:277-278);
+      // custom-iso keeps the symmetric storage, custom-aniso the half spectrum
+      d.anisotropy = (*traits).covariance == "custom-aniso" ? PF_ANISO_GEOMETRIC
+                                                            : PF_ANISO_NONE;
+      d.corr_length[0] = config.template get<RF>("stochastic.corrLength");
+      if (d.anisotropy == PF_ANISO_GEOMETRIC)
+        for (unsigned int i = 0; i < dim; i++)
+          for (unsigned int j = 0; j < dim; j++)
+            d.corr_length[i * dim + j] = i == j ? d.corr_length[0] : 0.;
+    } else if (anisotropy == "none") {
       d.anisotropy = PF_ANISO_NONE;
       d.corr_length[0] = config.template get<RF>("stochastic.corrLength");
     } else if (anisotropy == "axiparallel") {
@@ -304,11 +313,16 @@ public:
   template<typename Covariance = void>
   void fillTransformedMatrix() const
   {
-    if constexpr (!std::is_same<Covariance, void>::value)
-      throw std::runtime_error{
-        "custom covariance classes are host functors and cannot be evaluated "
-        "by the CUDA path"
-      };
+    if constexpr (!std::is_same<Covariance, void>::value) {
+      // matrix.hh:270-279: only with custom-iso / custom-aniso
+      if ((*traits).covariance != "custom-iso" &&
+          (*traits).covariance != "custom-aniso")
+        throw std::runtime_error{
+          "you can't fill the matrix explicitly if a default "
+          "covariance was chosen"
+        };
+      uploadCustomCovariance<Covariance>();
+    }
     pf_eig_stats stats{};
     const int rc = pf_compute_eigenvalues(plan, &stats);
     if ((*traits).verbose && (*traits).rank == 0)
@@ -406,6 +420,43 @@ private:
   {
     if (!filled)
       fillTransformedMatrix();
+  }
+
+  // Matrix::computeMatrixEntriesWithMirroring<Covariance, ScaledIdentityMatrix>
+  // (matrix.hh:624-648) on the host over the WHOLE extended domain: the
+  // caller's functor cannot run on the device, its values can
+  template<typename Covariance>
+  void uploadCustomCovariance() const
+  {
+    const auto& config = (*traits).config;
+    const Covariance covariance(config);
+    // ScaledIdentityMatrix (covariance.hh:31-41): value = 1 / corrLength
+    const RF scale = 1. / config.template get<RF>("stochastic.corrLength");
+    const RF variance = (*traits).variance;
+    const unsigned int factor = (*traits).embeddingFactor;
+    std::array<unsigned int, dim> n;
+    size_t total = 1;
+    for (unsigned int i = 0; i < dim; i++) {
+      n[i] = factor * (*traits).cells[i];
+      total *= n[i];
+    }
+    std::vector<double> table(total);
+    std::array<RF, dim> coord, transCoord;
+    std::array<unsigned int, dim> idx{};
+    for (size_t index = 0; index < total; index++) {
+      size_t r = index;
+      for (unsigned int i = 0; i < dim; i++) {
+        idx[i] = r % n[i];
+        r /= n[i];
+        const RF ext = (*traits).extensions[i];
+        coord[i] = idx[i] * (ext / (*traits).cells[i]);
+        if (coord[i] > 0.5 * ext * factor)
+          coord[i] -= ext * factor;
+        transCoord[i] = scale * coord[i];
+      }
+      table[index] = covariance(variance, transCoord);
+    }
+    check(pf_set_covariance_table(plan, table.data(), table.size()));
   }
 
   StochasticPartType apply(int op, const StochasticPartType& input) const

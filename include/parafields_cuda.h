@@ -58,8 +58,14 @@ typedef enum pf_covariance
   PF_COV_GENERALIZED_CAUCHY = 9,
   PF_COV_CUBIC = 10,
   PF_COV_WHITE_NOISE = 11,
-  PF_COV_MATERN = 12 /* general nu (covariance.hh:527-581; the reference needs
-                        GSL's K_nu for it, here a device function)       */
+  PF_COV_MATERN = 12, /* general nu (covariance.hh:527-581; the reference needs
+                         GSL's K_nu for it, here a device function)       */
+  PF_COV_CUSTOM = 13  /* custom-iso / custom-aniso (matrix.hh:236,270-279): the
+                         covariance is a host functor of the caller; its values
+                         on the extended domain arrive through
+                         pf_set_covariance_table.  anisotropy NONE = the
+                         symmetric (DCT matrix backend) storage of custom-iso,
+                         GEOMETRIC = the half-spectrum storage of custom-aniso */
 } pf_covariance;
 
 /* stochastic.anisotropy, matrix.hh:496-508 */
@@ -214,6 +220,13 @@ size_t pf_local_domain_size(const pf_plan* plan);
 #define PF_SLAB_HANDLE_BYTES 64
 int pf_slab_handle(pf_plan* plan, void* handle_out);
 int pf_slab_connect(pf_plan* plan, const void* handles, int count);
+
+/* Matrix::fillTransformedMatrix<Covariance>, matrix.hh:270-279 (custom-iso /
+ * custom-aniso): the torus covariance evaluated by the caller, one value per
+ * cell of the EXTENDED domain in natural order (index 0 fastest), cell j at
+ * coordinate j_i * meshsize_i folded to (-L_i, L_i] as in matrix.hh:637-642;
+ * host or device memory, copied.  The eigenvalues are recomputed from it. */
+int pf_set_covariance_table(pf_plan* plan, const double* values, size_t count);
 
 /* Matrix::fillTransformedMatrix, matrix.hh:232-331 (lazy in every other
  * entry point, like matrixBackend.valid()).  Returns

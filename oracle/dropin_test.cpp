@@ -151,6 +151,80 @@ run(const std::string& name, const std::string& ini)
   }
 }
 
+// custom-iso / custom-aniso (randomfield.hh:445-452, matrix.hh:270-279): a
+// covariance class of the CALLER, installed with fillMatrix<Cov>() on both sides
+struct UserCovariance
+{
+  explicit UserCovariance(const Dune::ParameterTree&) {}
+  template<typename RF, long unsigned int dim>
+  RF operator()(const RF variance, const std::array<RF, dim>& x) const
+  {
+    RF sum = 0.;
+    for (unsigned int i = 0; i < dim; i++)
+      sum += x[i] * x[i];
+    const RF h = std::sqrt(sum);
+    return variance * (1. + 0.5 * h) * std::exp(-1.5 * h);
+  }
+};
+struct SkewCovariance // not symmetric per dimension: needs custom-aniso
+{
+  explicit SkewCovariance(const Dune::ParameterTree&) {}
+  template<typename RF, long unsigned int dim>
+  RF operator()(const RF variance, const std::array<RF, dim>& x) const
+  {
+    RF sum = 0.;
+    for (unsigned int i = 0; i < dim; i++)
+      sum += x[i] * x[i];
+    if (dim > 1)
+      sum += 0.8 * x[0] * x[1];
+    return variance * std::exp(-std::sqrt(sum));
+  }
+};
+
+template<unsigned int dim, typename Cov>
+void
+runCustom(const std::string& name, const std::string& ini)
+{
+  using GT = GridTraits<double, double, dim>;
+  using RefField = parafields::RandomField<GT>;
+  using CudaField =
+    parafields::RandomField<GT, parafields::CudaMatrix, parafields::CudaMatrix>;
+  std::printf("%s\n", name.c_str());
+  Dune::ParameterTree config;
+  std::istringstream in(ini);
+  Dune::ParameterTreeParser::readINITree(in, config);
+  Dune::ParameterTree cconfig = config;
+  cconfig["cuda.noise"] = "reference";
+  RefField ref(config);
+  CudaField gpu(cconfig);
+  bool threw = false;
+  try {
+    gpu.generate(1u); // matrix.hh:236-239: the class has to be supplied first
+  } catch (const std::runtime_error&) {
+    threw = true;
+  }
+  report("generate before fillMatrix<Cov> throws", threw ? 0. : 1., 0.5);
+  ref.template fillMatrix<Cov>();
+  gpu.template fillMatrix<Cov>();
+  ref.generate(20240611u);
+  gpu.generate(20240611u);
+  report("generate(seed), custom covariance", relDiff(ref, gpu), 1e-10);
+  {
+    RefField a(ref);
+    CudaField b(gpu);
+    a.timesMatrix();
+    b.timesMatrix();
+    report("timesMatrix, custom covariance", relDiff(a, b), 1e-10);
+  }
+  {
+    RefField a(ref);
+    CudaField b(gpu);
+    a.timesMatrixRoot();
+    b.timesMatrixRoot();
+    report("timesMatrixRoot, custom covariance", relDiff(a, b), 1e-10);
+  }
+}
+
 int
 main()
 {
@@ -176,6 +250,22 @@ main()
          "[grid]\nextensions = 1 1\ncells = 128 128\n" + tail +
            "covariance = matern32\ncorrLength = 0.05\n"
            "[randomField]\ncgIterations = 4\ncacheInvMatvec = 1\ncacheInvRootMatvec = 1\n");
+  const std::string capp = "[embedding]\napproximate = 1\n";
+  runCustom<1, UserCovariance>("1D 64, custom-iso (user functor; generic route)",
+                               "[grid]\nextensions = 1\ncells = 64\n" + tail +
+                                 "covariance = custom-iso\ncorrLength = 0.05\n" + capp);
+  runCustom<2, UserCovariance>("2D 32x16, custom-iso (user functor)",
+                               "[grid]\nextensions = 1 1\ncells = 32 16\n" + tail +
+                                 "covariance = custom-iso\ncorrLength = 0.05\n" + capp);
+  runCustom<3, UserCovariance>("3D 8x16x8, custom-iso (user functor)",
+                               "[grid]\nextensions = 1 1 1\ncells = 8 16 8\n" + tail +
+                                 "covariance = custom-iso\ncorrLength = 0.1\n" + capp);
+  runCustom<2, SkewCovariance>("2D 16x32, custom-aniso (asymmetric user functor)",
+                               "[grid]\nextensions = 1 1\ncells = 16 32\n" + tail +
+                                 "covariance = custom-aniso\ncorrLength = 0.05\n" + capp);
+  runCustom<2, UserCovariance>("2D 50x30, custom-iso on a non power-of-two grid",
+                               "[grid]\nextensions = 1 1\ncells = 50 30\n" + tail +
+                                 "covariance = custom-iso\ncorrLength = 0.05\n" + capp);
   std::printf("%s (%d failure%s)\n", failures ? "DROP-IN FAILED" : "DROP-IN OK",
               failures, failures == 1 ? "" : "s");
   return failures ? 1 : 0;
