@@ -90,6 +90,9 @@ ABI_SYMBOLS = [
     "pf_field_evaluate",
     "pf_field_evaluate_trend",
     "pf_field_bulk_evaluate",
+    "pf_field_overlap_size",
+    "pf_field_slab_to_blocks",
+    "pf_field_blocks_to_slab",
     "pf_device_alloc",
     "pf_device_free",
     "pf_memcpy",
@@ -238,6 +241,11 @@ def lib():
     tp = C.POINTER(PfTrendComponent)
     L.pf_field_evaluate_trend.argtypes = [vp, C.c_int, up, dp, dp, sz, dp, C.c_int, tp, C.c_int, dp]
     L.pf_field_bulk_evaluate.argtypes = [vp, C.c_int, up, dp, dp, C.c_int, tp, C.c_int, dp]
+    ip = C.POINTER(C.c_int)
+    L.pf_field_overlap_size.argtypes = [vp, ip]
+    L.pf_field_overlap_size.restype = sz
+    L.pf_field_slab_to_blocks.argtypes = [vp, ip, dp, dp, dp]
+    L.pf_field_blocks_to_slab.argtypes = [vp, ip, dp, dp]
     L.pf_device_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.pf_device_free.argtypes = [vp, vp]
     L.pf_memcpy.argtypes = [vp, vp, vp, sz]
@@ -358,6 +366,45 @@ def slab_layout(cells, factor, n_ranks, rank):
     b0, b1 = min(A, chunk * rank), min(A, chunk * (rank + 1))
     layers = cells[-1] // n_ranks
     return dict(a_begin=b0, a_count=b1 - b0, layers=layers, layer_begin=rank * layers, lines=A, line_length=N)
+
+
+def default_load_balance(cells, n_ranks):
+    """DefaultLoadBalance::loadbalance (fieldtraits.hh:497-561): processors per
+    dimension minimising the largest local extent, exact divisibility only;
+    the recursion tries the last dimension first and keeps the FIRST optimum."""
+    dim = len(cells)
+    best = [None, 1e100]
+    trial = [0] * dim
+
+    def rec(i, P):
+        if i > 0:
+            for k in range(1, P + 1):
+                if P % k == 0 and cells[i] % k == 0:
+                    trial[i] = k
+                    rec(i - 1, P // k)
+        elif cells[0] % P == 0:
+            trial[0] = P
+            m = max(cells[k] / trial[k] for k in range(dim))
+            if m < best[1]:
+                best[1] = m
+                best[0] = list(trial)
+
+    rec(dim - 1, n_ranks)
+    return best[0]
+
+
+def eval_block(cells, proc_per_dim, rank):
+    """localEvalCells / localEvalOffset of StochasticPart::update (stochastic.hh:237-257)"""
+    dim = len(cells)
+    le = [c // p for c, p in zip(cells, proc_per_dim)]
+    p = list(proc_per_dim) + [1] * (3 - dim)
+    if dim == 3:
+        lo = [(rank % (p[0] * p[1])) % p[0] * le[0], (rank % (p[0] * p[1])) // p[0] * le[1], rank // (p[0] * p[1]) * le[2]]
+    elif dim == 2:
+        lo = [rank % p[0] * le[0], rank // p[0] * le[1]]
+    else:
+        lo = [rank * le[0]]
+    return le, lo
 
 
 def stream_slab_layout(cells, factor, n_ranks, rank):
@@ -481,6 +528,34 @@ class Plan:
         dist.all_gather_object(handles, self.slab_handle(), group=group)
         self.slab_connect(handles)
         dist.barrier(group)
+
+    # -- slab <-> block redistribution with overlap (multi-GPU plans) -----------
+    def _ppd(self, proc_per_dim):
+        return (C.c_int * 3)(*(list(proc_per_dim) + [1] * (3 - self.dim)))
+
+    def overlap_size(self, proc_per_dim):
+        return int(lib().pf_field_overlap_size(self._h, self._ppd(proc_per_dim)))
+
+    def slab_to_blocks(self, proc_per_dim, slab, eval_out=None, overlap_out=None):
+        """StochasticPart::dataToEval + exchangeOverlap (stochastic.hh:830-925,
+        1016-1127): returns (evalVector, overlap) of this rank"""
+        if isinstance(slab, np.ndarray):
+            slab = np.ascontiguousarray(slab, dtype=np.float64)
+            if eval_out is None:
+                eval_out = np.empty(self.local_domain_size)
+            if overlap_out is None:
+                overlap_out = np.empty(self.overlap_size(proc_per_dim))
+        _check(lib().pf_field_slab_to_blocks(self._h, self._ppd(proc_per_dim), _ptr(slab), _ptr(eval_out), _ptr(overlap_out)))
+        return eval_out, overlap_out
+
+    def blocks_to_slab(self, proc_per_dim, eval_in, slab_out=None):
+        """StochasticPart::evalToData (stochastic.hh:935-1005)"""
+        if isinstance(eval_in, np.ndarray):
+            eval_in = np.ascontiguousarray(eval_in, dtype=np.float64)
+            if slab_out is None:
+                slab_out = np.empty(self.shape)
+        _check(lib().pf_field_blocks_to_slab(self._h, self._ppd(proc_per_dim), _ptr(eval_in), _ptr(slab_out)))
+        return slab_out
 
     # -- eigenvalues ---------------------------------------------------------
     def set_covariance_table(self, values):

@@ -3336,6 +3336,167 @@ apply_slab_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
   return slab_issue_tail(pl, e2, out_dev, 0);
 }
 
+// ---------------------------------------------------------------------------
+// slab <-> block redistribution with overlap (StochasticPart::dataToEval /
+// evalToData / exchangeOverlap, stochastic.hh:830-1127; block layout of
+// DefaultLoadBalance, fieldtraits.hh:483-562, offsets stochastic.hh:237-257)
+// ---------------------------------------------------------------------------
+struct BlockGeom
+{
+  int dim, P, rank;
+  unsigned cl;     // layers of the last dimension per slab
+  unsigned c[3];   // global cells
+  unsigned ppd[3]; // processors per dimension
+  unsigned le[3];  // localEvalCells
+  unsigned lo[3];  // localEvalOffset of this rank
+  const double* peer[8]; // staged arrays of all ranks (peer memory)
+};
+
+__device__ __forceinline__ double
+slab_value(const BlockGeom& g, unsigned x, unsigned y, unsigned z)
+{
+  // the slab decomposition splits the LAST dimension
+  const unsigned last = g.dim == 3 ? z : (g.dim == 2 ? y : x);
+  const unsigned owner = last / g.cl, ll = last - owner * g.cl;
+  size_t idx;
+  if (g.dim == 3)
+    idx = x + (size_t)g.c[0] * (y + (size_t)g.c[1] * ll);
+  else if (g.dim == 2)
+    idx = x + (size_t)g.c[0] * ll;
+  else
+    idx = ll;
+  return g.peer[owner][idx];
+}
+
+// evalVector (block of this rank, natural order) followed by the 2 * dim
+// overlap faces: [lower halo of dim 0][upper halo of dim 0][lower of dim 1] ...
+__global__ void
+k_slab_to_blocks(BlockGeom g, double* __restrict__ eval, double* __restrict__ overlap,
+                 size_t Dl, size_t total)
+{
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    if (t < Dl) {
+      const unsigned e0 = (unsigned)(t % g.le[0]);
+      const unsigned e1 = (unsigned)((t / g.le[0]) % g.le[1]);
+      const unsigned e2 = (unsigned)(t / ((size_t)g.le[0] * g.le[1]));
+      eval[t] = slab_value(g, g.lo[0] + e0, g.lo[1] + e1, g.lo[2] + e2);
+      continue;
+    }
+    size_t r = t - Dl;
+    for (int i = 0; i < g.dim; i++) {
+      const size_t F = Dl / g.le[i];
+      if (r >= 2 * F) {
+        r -= 2 * F;
+        continue;
+      }
+      const bool upper = r >= F;
+      const size_t f = upper ? r - F : r;
+      unsigned e[3] = { 0, 0, 0 };
+      if (g.dim == 3) {
+        const int in = (i + 1) % 3, inn = (i + 2) % 3;
+        e[in] = (unsigned)(f % g.le[in]);
+        e[inn] = (unsigned)(f / g.le[in]);
+      } else if (g.dim == 2)
+        e[(i + 1) % 2] = (unsigned)f;
+      unsigned x[3] = { g.lo[0] + e[0], g.lo[1] + e[1], g.lo[2] + e[2] };
+      // periodic neighbours (exchangeOverlap wraps the processor grid)
+      x[i] = upper ? (g.lo[i] + g.le[i]) % g.c[i] : (g.lo[i] + g.c[i] - 1) % g.c[i];
+      overlap[t - Dl] = slab_value(g, x[0], x[1], x[2]);
+      break;
+    }
+  }
+}
+
+// evalToData: the slab of this rank gathered from the blocks of all ranks
+__global__ void
+k_blocks_to_slab(BlockGeom g, double* __restrict__ slab, size_t Dl)
+{
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < Dl;
+       t += (size_t)gridDim.x * blockDim.x) {
+    unsigned x[3] = { 0, 0, 0 };
+    if (g.dim == 3) {
+      x[0] = (unsigned)(t % g.c[0]);
+      x[1] = (unsigned)((t / g.c[0]) % g.c[1]);
+      x[2] = (unsigned)(t / ((size_t)g.c[0] * g.c[1])) + g.rank * g.cl;
+    } else if (g.dim == 2) {
+      x[0] = (unsigned)(t % g.c[0]);
+      x[1] = (unsigned)(t / g.c[0]) + g.rank * g.cl;
+    } else
+      x[0] = (unsigned)t + g.rank * g.cl;
+    unsigned b[3], e[3];
+    for (int i = 0; i < 3; i++) {
+      b[i] = x[i] / g.le[i];
+      e[i] = x[i] - b[i] * g.le[i];
+    }
+    const unsigned owner = b[0] + g.ppd[0] * (b[1] + g.ppd[1] * b[2]);
+    slab[t] = g.peer[owner][e[0] + (size_t)g.le[0] * (e[1] + (size_t)g.le[1] * e[2])];
+  }
+}
+
+int
+block_geom(pf_plan* pl, const int* ppd, BlockGeom& g)
+{
+  if (pl->nranks <= 1 || !pl->connected)
+    return fail(PF_ERR_INVALID, "slab <-> block redistribution needs a connected "
+                                "multi-GPU plan (pf_slab_connect)");
+  memset(&g, 0, sizeof(g));
+  g.dim = pl->dim;
+  g.P = pl->nranks;
+  g.rank = pl->rank;
+  g.cl = (unsigned)pl->cl;
+  long long prod = 1;
+  for (int i = 0; i < 3; i++) {
+    g.c[i] = (unsigned)pl->c[i];
+    g.ppd[i] = i < pl->dim ? (unsigned)ppd[i] : 1u;
+    if (g.ppd[i] < 1 || g.c[i] % g.ppd[i] != 0) // stochastic.hh:239-243
+      return fail(PF_ERR_INVALID, "cells in dimension not divisable by numProcs");
+    g.le[i] = g.c[i] / g.ppd[i];
+    prod *= g.ppd[i];
+  }
+  if (prod != pl->nranks)
+    return fail(PF_ERR_INVALID, "procPerDim does not multiply to the number of ranks");
+  // stochastic.hh:244-257
+  const unsigned r = (unsigned)pl->rank;
+  if (pl->dim == 3) {
+    g.lo[0] = (r % (g.ppd[0] * g.ppd[1])) % g.ppd[0] * g.le[0];
+    g.lo[1] = (r % (g.ppd[0] * g.ppd[1])) / g.ppd[0] * g.le[1];
+    g.lo[2] = r / (g.ppd[0] * g.ppd[1]) * g.le[2];
+  } else if (pl->dim == 2) {
+    g.lo[0] = r % g.ppd[0] * g.le[0];
+    g.lo[1] = r / g.ppd[0] * g.le[1];
+  } else
+    g.lo[0] = r * g.le[0];
+  return 0;
+}
+
+// stage `src` (Dl doubles) in this rank's exchange buffer, tell the peers, wait
+// for all of them; returns the epoch and fills g.peer[]
+int
+block_stage(pf_plan* pl, const double* src_dev, BlockGeom& g, unsigned long long* e_out)
+{
+  const int P = pl->nranks;
+  const unsigned long long e = ++pl->epoch;
+  const int s = (int)(e & 1);
+  if (e > 2) {
+    k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 1), P, e - 2,
+                                          pl->d_timeout, pl->slab_limit_ns);
+    pl->launches++;
+  }
+  if (pl->Dl * sizeof(double) > pl->xbuf_elems * sizeof(cplx))
+    return fail(PF_ERR_INVALID, "redistribution: exchange buffer too small");
+  PF_CUDA(cudaMemcpyAsync(slab_buffer(pl, pl->slab_block, s), src_dev,
+                          pl->Dl * sizeof(double), cudaMemcpyDeviceToDevice, pl->stream));
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsA, P, pl->rank, e);
+  k_slab_wait<<<1, 32, 0, pl->stream>>>(slab_flags(pl, pl->slab_block, 0), P, e,
+                                        pl->d_timeout, pl->slab_limit_ns);
+  pl->launches += 2;
+  for (int q = 0; q < P; q++)
+    g.peer[q] = reinterpret_cast<const double*>(slab_buffer(pl, pl->peer_block[q], s));
+  *e_out = e;
+  return 0;
+}
+
 // multiplyExtended / multiplyRootExtended / multiplyInverseExtended
 // (matrix.hh:1459-1662) on device fields; in_dev may equal out_dev
 int
@@ -4916,6 +5077,69 @@ pf_field_bulk_evaluate(pf_plan* pl, int dim, const unsigned* cells,
 #undef PF_BULK
   PF_CUDA(cudaGetLastError());
   pl->launches++;
+  return so.finish();
+}
+
+size_t
+pf_field_overlap_size(const pf_plan* pl, const int* ppd)
+{
+  if (!pl || !ppd)
+    return 0;
+  size_t total = 0;
+  for (int i = 0; i < pl->dim; i++) {
+    if (ppd[i] < 1 || pl->c[i] % ppd[i] != 0)
+      return 0;
+    total += 2 * (pl->Dl / (size_t)(pl->c[i] / ppd[i]));
+  }
+  return total;
+}
+
+int
+pf_field_slab_to_blocks(pf_plan* pl, const int* ppd, const double* slab,
+                        double* eval, double* overlap)
+{
+  PF_TRY(check_plan(pl));
+  if (!ppd || !slab || !eval)
+    return fail(PF_ERR_INVALID, "null argument");
+  BlockGeom g;
+  PF_TRY(block_geom(pl, ppd, g));
+  const size_t nov = pf_field_overlap_size(pl, ppd);
+  Staged si;
+  StagedOut se, so;
+  PF_TRY(stage_in(pl, slab, pl->Dl, si));
+  PF_TRY(stage_out(pl, eval, pl->Dl, false, se));
+  if (overlap)
+    PF_TRY(stage_out(pl, overlap, nov, false, so));
+  unsigned long long e = 0;
+  PF_TRY(block_stage(pl, si.dev, g, &e));
+  const size_t total = pl->Dl + (overlap ? nov : 0);
+  k_slab_to_blocks<<<grid_for(total), 256, 0, pl->stream>>>(g, se.dev, so.dev, pl->Dl, total);
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsB, pl->nranks, pl->rank, e);
+  PF_CUDA(cudaGetLastError());
+  pl->launches += 2;
+  if (overlap)
+    PF_TRY(so.finish());
+  return se.finish();
+}
+
+int
+pf_field_blocks_to_slab(pf_plan* pl, const int* ppd, const double* eval, double* slab)
+{
+  PF_TRY(check_plan(pl));
+  if (!ppd || !slab || !eval)
+    return fail(PF_ERR_INVALID, "null argument");
+  BlockGeom g;
+  PF_TRY(block_geom(pl, ppd, g));
+  Staged si;
+  StagedOut so;
+  PF_TRY(stage_in(pl, eval, pl->Dl, si));
+  PF_TRY(stage_out(pl, slab, pl->Dl, false, so));
+  unsigned long long e = 0;
+  PF_TRY(block_stage(pl, si.dev, g, &e));
+  k_blocks_to_slab<<<grid_for(pl->Dl), 256, 0, pl->stream>>>(g, so.dev, pl->Dl);
+  k_slab_signal<<<1, 32, 0, pl->stream>>>(pl->d_flagsB, pl->nranks, pl->rank, e);
+  PF_CUDA(cudaGetLastError());
+  pl->launches += 2;
   return so.finish();
 }
 

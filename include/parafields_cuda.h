@@ -361,6 +361,25 @@ int pf_field_bulk_evaluate(pf_plan* plan, int dim, const unsigned* cells,
                            int ntrend, const pf_trend_component* trend,
                            int apply_transform, double* out);
 
+/* Slab <-> block redistribution with overlap on a connected multi-GPU plan
+ * (StochasticPart::dataToEval / evalToData / exchangeOverlap,
+ * stochastic.hh:830-1127).  proc_per_dim[dim] = the processor grid of the
+ * reference's load balancer (DefaultLoadBalance, fieldtraits.hh:483-562;
+ * product = n_ranks, cells divisible); rank r owns the block at
+ * localEvalOffset of stochastic.hh:244-257.  slab = this rank's layers of the
+ * last dimension (pf_local_domain_size doubles, what pf_generate returns);
+ * eval = its block in natural order (same count); overlap (may be NULL) =
+ * pf_field_overlap_size doubles: for every dimension i the lower halo (the
+ * lower neighbour's last layer) followed by the upper halo, neighbours
+ * periodic, face index as in stochastic.hh:1025-1040.  Collective: all ranks
+ * call it in the same order; the data moves as loads from the peers' exchange
+ * buffers over NVLink (no host round trip).  Arrays may be host or device. */
+size_t pf_field_overlap_size(const pf_plan* plan, const int* proc_per_dim);
+int pf_field_slab_to_blocks(pf_plan* plan, const int* proc_per_dim,
+                            const double* slab, double* eval, double* overlap);
+int pf_field_blocks_to_slab(pf_plan* plan, const int* proc_per_dim,
+                            const double* eval, double* slab);
+
 /* device memory helpers so that a host-only caller (C++, cgo, ctypes) can
  * keep fields resident in HBM */
 int pf_device_alloc(pf_plan* plan, size_t bytes, void** ptr);

@@ -72,6 +72,46 @@ def main():
             mine = slab.generate_from_noise(noise)
             err = float(np.max(np.abs(mine - full[rank * layers : (rank + 1) * layers])) / np.max(np.abs(full)))
             worst = max(worst, err)
+            # slab -> block redistribution with overlap (dataToEval +
+            # exchangeOverlap, stochastic.hh:830-925,1016-1127) and back
+            cells = case["cells"]
+            dim = len(cells)
+            full = single.generate(seed=11, realization=3)
+            mine = slab.generate(seed=11, realization=3)
+            tried = []
+            for ppd in (pfb.default_load_balance(cells, world), [1] * (dim - 1) + [world], ([world] + [1] * (dim - 1)) if cells[0] % world == 0 else None):
+                if ppd is None or ppd in tried:
+                    continue
+                tried.append(ppd)
+                le, lo = pfb.eval_block(cells, ppd, rank)
+                ev, ov = slab.slab_to_blocks(ppd, mine)
+                sl = tuple(slice(o, o + e) for o, e in zip(reversed(lo), reversed(le)))
+                if not np.array_equal(ev, full[sl].ravel()):
+                    worst = max(worst, 1.0)
+                # faces: lower / upper periodic neighbour layer of every dimension
+                pos = 0
+                for i in range(dim):
+                    ax = dim - 1 - i  # numpy axis of dimension i
+                    for coord in ((lo[i] - 1) % cells[i], (lo[i] + le[i]) % cells[i]):
+                        idx = list(sl)
+                        idx[ax] = slice(coord, coord + 1)
+                        face = np.squeeze(full[tuple(idx)], axis=ax)
+                        # face index: e_next + e_nextnext * le[next] (3D), e_next (2D)
+                        if dim == 3:
+                            nx, nn = (i + 1) % 3, (i + 2) % 3
+                            # `face` axes are the remaining dims in descending order
+                            rem = [d for d in (2, 1, 0) if d != i]
+                            want = np.transpose(face, (rem.index(nn), rem.index(nx))).ravel()
+                        else:
+                            want = face.ravel()
+                        got = ov[pos : pos + want.size]
+                        pos += want.size
+                        if not np.array_equal(got, want):
+                            worst = max(worst, 2.0)
+                assert pos == ov.size
+                back = slab.blocks_to_slab(ppd, ev)
+                if not np.array_equal(back, mine):
+                    worst = max(worst, 3.0)
             # covariance operators on the distributed field (two exchanges per
             # matvec) and the PCG inverse with cross-rank scalar products
             x_full = np.random.default_rng(9).standard_normal(single.shape)
