@@ -43,9 +43,18 @@ struct PCfg
   static constexpr int BOXR = SR < 256 ? SR : 256;   // TMA box rows
   static constexpr int SUB_BYTES = SR * 128;
   static constexpr int BAR_BYTES = 128;
+  // inter-pass twiddles copied to shared memory behind the barriers (with
+  // ~200 KB of shared memory in use the remaining L1 keeps missing on the
+  // table).  Measured on B200 (profiles/r2h): kp_c2t N = 512 0.194 -> 0.159 ms,
+  // N = 1024 1.073 -> 1.088 ms (kept on the global table); kp_c2r N = 1024
+  // 0.532 -> 0.499 ms, N = 512 unchanged
+  static constexpr bool TWS_C2T = N <= 512;
+  static constexpr bool TWS_C2R = true;
+  static constexpr int TWB = C::TW2 * 16;
   static constexpr int SMEM_TILE =
-    SLOTS_BYTES + NSTAGE * STAGE_BYTES + BAR_BYTES + 1024;
-  static constexpr int SMEM_LINES = SLOTS_BYTES + BAR_BYTES + 1024;
+    SLOTS_BYTES + NSTAGE * STAGE_BYTES + BAR_BYTES + (TWS_C2T ? TWB : 0) + 1024;
+  static constexpr int SMEM_LINES =
+    SLOTS_BYTES + BAR_BYTES + (TWS_C2R ? TWB : 0) + 1024;
   static_assert(SLOTS_BYTES % 1024 == 0, "stage must stay 1024-byte aligned");
   static_assert(N + 2 <= C::PITCH, "c2r landing zone needs 2*(N/2+1) entries");
 };
@@ -522,6 +531,13 @@ kp_c2t(const PassArgs p, const cplx* __restrict__ tw2,
   using P = PCfg<N>;
   extern __shared__ unsigned char smem_raw[];
   PSmem<N> sm(smem_raw);
+  if constexpr (P::TWS_C2T) {
+    cplx* tws = reinterpret_cast<cplx*>(sm.base + P::SLOTS_BYTES +
+                                        P::NSTAGE * P::STAGE_BYTES + P::BAR_BYTES);
+    for (int i = threadIdx.x; i < P::C::TW2; i += P::THREADS)
+      tws[i] = __ldg(tw2 + i);
+    tw2 = tws;
+  }
   pipe_init<N>(sm, true);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntA = (p.A + P::LT - 1) / P::LT;
@@ -582,7 +598,7 @@ kp_c2t(const PassArgs p, const cplx* __restrict__ tw2,
     const long long Tn = T + gridDim.x;
     if (Tn < ntiles)
       issue(Tn);
-    line_fft_phase2_compute<N, DIR>(v, t, tw2);
+    line_fft_phase2_compute<N, DIR, P::TWS_C2T>(v, t, tw2);
     stage_out<N>(v, sm, slot, t, p.keep, it);
   }
 }
@@ -599,6 +615,12 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
   constexpr int M0 = N / 2 + 1;
   extern __shared__ unsigned char smem_raw[];
   PSmem<N> sm(smem_raw);
+  if constexpr (P::TWS_C2R) {
+    cplx* tws = reinterpret_cast<cplx*>(sm.base + P::SLOTS_BYTES + P::BAR_BYTES);
+    for (int i = threadIdx.x; i < P::C::TW2; i += P::THREADS - 32)
+      tws[i] = __ldg(tw2 + i);
+    tw2 = tws;
+  }
   pipe_init<N>(sm, false);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long nl = (long long)p.A * p.B;
@@ -653,7 +675,7 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
     const long long Tn = T + gridDim.x;
     if (Tn < ntiles)
       issue(Tn);
-    line_fft_phase2_compute<N, +1>(v, t, tw2);
+    line_fft_phase2_compute<N, +1, P::TWS_C2R>(v, t, tw2);
     store_real_pair<N>(v, p, L0, v0, v1, t);
   }
 }
