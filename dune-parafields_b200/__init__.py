@@ -84,6 +84,8 @@ ABI_SYMBOLS = [
     "pf_vec_dot",
     "pf_vec_norm1",
     "pf_vec_norminf",
+    "pf_vec_equal",
+    "pf_vec_fill",
     "pf_field_refine",
     "pf_field_coarsen",
     "pf_field_localize",
@@ -233,6 +235,8 @@ def lib():
     L.pf_vec_dot.argtypes = [vp, sz, dp, dp, C.POINTER(C.c_double)]
     L.pf_vec_norm1.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
     L.pf_vec_norminf.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
+    L.pf_vec_equal.argtypes = [vp, sz, dp, dp, C.POINTER(C.c_int)]
+    L.pf_vec_fill.argtypes = [vp, sz, C.c_double, dp]
     up = C.POINTER(C.c_uint)
     L.pf_field_refine.argtypes = [vp, C.c_int, up, dp, dp]
     L.pf_field_coarsen.argtypes = [vp, C.c_int, up, dp, dp]
@@ -743,6 +747,17 @@ class Plan:
 
     def norminf(self, x):
         return self._red(lib().pf_vec_norminf, x)
+
+    def equal(self, x, y):
+        n = x.size if isinstance(x, np.ndarray) else x.numel()
+        same = C.c_int()
+        _check(lib().pf_vec_equal(self._h, n, _ptr(x), _ptr(y), C.byref(same)))
+        return bool(same.value)
+
+    def fill(self, value, x):
+        n = x.size if isinstance(x, np.ndarray) else x.numel()
+        _check(lib().pf_vec_fill(self._h, n, value, _ptr(x)))
+        return x
 
 
 def device_count():

@@ -798,6 +798,8 @@ k_reduce1(size_t n, const double* __restrict__ x, const double* __restrict__ y,
       t = fabs(x[i]);
     else if (mode == 2)
       t = fabs(x[i]);
+    else if (mode == 4)
+      t = (x[i] != y[i]) ? 1. : 0.; // number of differing entries
     else
       t = x[i] * (0.5 * y[i] - z[i]);
     acc = red_combine(acc, t, mode);
@@ -4795,6 +4797,30 @@ pf_vec_norminf(pf_plan* pl, size_t nn, const double* x, double* result)
 {
   return vec_reduce(pl, nn, x, nullptr, 2, result);
 }
+int
+pf_vec_equal(pf_plan* pl, size_t nn, const double* x, const double* y,
+             int* same)
+{
+  if (!same)
+    return fail(PF_ERR_INVALID, "pf_vec_equal: null result");
+  double differing = 0.;
+  PF_TRY(vec_reduce(pl, nn, x, y, 4, &differing));
+  *same = differing == 0. ? 1 : 0;
+  return 0;
+}
+int
+pf_vec_fill(pf_plan* pl, size_t nn, double value, double* x)
+{
+  PF_TRY(check_plan(pl));
+  StagedOut sx;
+  PF_TRY(stage_out(pl, x, nn, false, sx));
+  k_fill<<<grid_for(nn), 256, 0, pl->stream>>>(nn, value, sx.dev);
+  PF_CUDA(cudaGetLastError());
+  pl->launches++;
+  if (!sx.owned)
+    return 0;
+  return sx.finish();
+}
 
 // ---------------------------------------------------------------------------
 // resolution transfer, localisation, point evaluation
@@ -5158,8 +5184,12 @@ pf_device_alloc(pf_plan* pl, size_t bytes, void** ptr)
 int
 pf_device_free(pf_plan* pl, void* ptr)
 {
-  PF_TRY(check_plan(pl));
-  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  // plan may be NULL (a buffer that outlives the plan it was made with):
+  // cudaFree waits for the work that uses the buffer by itself
+  if (pl) {
+    PF_TRY(check_plan(pl));
+    PF_CUDA(cudaStreamSynchronize(pl->stream));
+  }
   PF_CUDA(cudaFree(ptr));
   return 0;
 }

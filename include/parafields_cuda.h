@@ -288,6 +288,12 @@ int pf_vec_dot(pf_plan* plan, size_t n, const double* x, const double* y,
                double* result);
 int pf_vec_norm1(pf_plan* plan, size_t n, const double* x, double* result);
 int pf_vec_norminf(pf_plan* plan, size_t n, const double* x, double* result);
+/* StochasticPart::operator== (stochastic.hh:438-452): *same = 1 when every
+ * entry of x equals the entry of y (NaN differs from everything) */
+int pf_vec_equal(pf_plan* plan, size_t n, const double* x, const double* y,
+                 int* same);
+/* StochasticPart::zero (stochastic.hh:581-587) and constant fields */
+int pf_vec_fill(pf_plan* plan, size_t n, double value, double* x);
 
 /* Resolution transfer, localisation and point evaluation of a field
  * (SURVEY 8(f) rows 1 and 3).  Arrays may be device or host memory (host
@@ -383,6 +389,7 @@ int pf_field_blocks_to_slab(pf_plan* plan, const int* proc_per_dim,
 /* device memory helpers so that a host-only caller (C++, cgo, ctypes) can
  * keep fields resident in HBM */
 int pf_device_alloc(pf_plan* plan, size_t bytes, void** ptr);
+/* plan may be NULL here: a buffer may outlive the plan it was made with */
 int pf_device_free(pf_plan* plan, void* ptr);
 int pf_memcpy(pf_plan* plan, void* dst, const void* src, size_t bytes);
 
