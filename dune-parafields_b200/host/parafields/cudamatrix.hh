@@ -36,14 +36,29 @@
 #include <random>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include <parafields_cuda.h>
+
+// device-resident StochasticPart for RandomField<GridTraits, CudaMatrix,
+// CudaMatrix> (and the plan registry both sides use)
+#include <parafields/cudastochastic.hh>
 
 namespace parafields {
 
 template<typename Traits>
 class StochasticPart;
+
+namespace cuda_detail {
+template<typename Part, typename = void>
+struct IsDeviceResident : std::false_type
+{};
+template<typename Part>
+struct IsDeviceResident<Part, std::void_t<typename Part::DeviceResidentTag>>
+  : std::true_type
+{};
+} // namespace cuda_detail
 
 template<typename Traits>
 class CudaMatrix
@@ -114,8 +129,11 @@ public:
 
   ~CudaMatrix()
   {
-    if (plan)
+    if (plan) {
+      cuda_detail::PlanRegistry::withdraw(traits.get(), plan);
+      cuda_detail::BufferPool::drain(traits.get(), plan);
       pf_plan_destroy(plan);
+    }
   }
 
   // Matrix::update, matrix.hh:130-142: (re)read sizes after construction or
@@ -123,6 +141,8 @@ public:
   void update()
   {
     if (plan) {
+      cuda_detail::PlanRegistry::withdraw(traits.get(), plan);
+      cuda_detail::BufferPool::drain(traits.get(), plan);
       pf_plan_destroy(plan);
       plan = nullptr;
     }
@@ -281,6 +301,8 @@ public:
       };
 
     check(pf_plan_create(&d, &plan));
+    // the fields of these traits find their plan here (cudastochastic.hh)
+    cuda_detail::PlanRegistry::announce(traits.get(), plan);
   }
 
   // Matrix::operator*, matrix.hh:151-160
@@ -299,11 +321,12 @@ public:
   StochasticPartType multiplyInverse(const StochasticPartType& input) const
   {
     ensureFilled();
-    StochasticPartType output(input);
+    if (isEmpty(input))
+      return input;
+    StochasticPartType output = likeInput(input);
     unsigned int iterations = 0;
-    check(pf_solve(plan, input.dataVector.data(), output.dataVector.data(),
-                   &iterations));
-    output.evalValid = false;
+    check(pf_solve(plan, readPointer(input),
+                   writePointer(output, fieldSize(input)), &iterations));
     if ((*traits).verbose && (*traits).rank == 0)
       std::cout << iterations << " iterations" << std::endl;
     return output;
@@ -342,13 +365,13 @@ public:
   void generateField(unsigned int seed, StochasticPartType& stochasticPart) const
   {
     ensureFilled();
-    stochasticPart.dataVector.resize((*traits).localDomainSize);
+    const std::size_t count = (*traits).localDomainSize;
     seed += (*traits).rank; // different seed for each processor (:352)
     if (referenceNoise) {
-      if (dim == 1 && spare.size() == stochasticPart.dataVector.size()) {
+      if (dim == 1 && spare.size() == count) {
         // DFT field backend: every second call returns the imaginary part
         // and ignores its seed (matrix.hh:349,433-437)
-        stochasticPart.dataVector = spare;
+        assignHost(stochasticPart, spare);
         spare.clear();
       } else {
         const size_t entries = pf_noise_entries(plan);
@@ -358,9 +381,9 @@ public:
         for (auto& v : noise)
           v = normalDist(generator);
         if (dim == 1)
-          spare.resize(stochasticPart.dataVector.size());
+          spare.resize(count);
         check(pf_generate_from_noise(plan, noise.data(),
-                                     stochasticPart.dataVector.data(),
+                                     writePointer(stochasticPart, count),
                                      dim == 1 ? spare.data() : nullptr));
       }
     } else if (dim == 1) {
@@ -370,42 +393,41 @@ public:
       // 2t+1 = real / imaginary part of transform t), so the protocol is kept
       // here.
       if (spareSeedValid) {
-        check(pf_generate(plan, spareSeed, 1, stochasticPart.dataVector.data(), 0));
+        check(pf_generate(plan, spareSeed, 1,
+                          writePointer(stochasticPart, count), 0));
         spareSeedValid = false;
       } else {
-        check(pf_generate(plan, seed, 0, stochasticPart.dataVector.data(), 0));
+        check(pf_generate(plan, seed, 0, writePointer(stochasticPart, count), 0));
         spareSeed = seed;
         spareSeedValid = true;
       }
     } else
-      check(
-        pf_generate(plan, seed, 0, stochasticPart.dataVector.data(), 0));
-    stochasticPart.evalValid = false;
+      check(pf_generate(plan, seed, 0, writePointer(stochasticPart, count), 0));
   }
 
   // Matrix::generateUncorrelatedField, matrix.hh:450-462
   void generateUncorrelatedField(unsigned int seed,
                                  StochasticPartType& stochasticPart) const
   {
-    stochasticPart.dataVector.resize((*traits).localDomainSize);
+    const std::size_t count = (*traits).localDomainSize;
     seed += (*traits).rank;
     if (referenceNoise) {
+      std::vector<RF> drawn(count);
       std::default_random_engine generator(seed);
       std::normal_distribution<RF> normalDist(0., 1.);
-      for (auto& v : stochasticPart.dataVector)
+      for (auto& v : drawn)
         v = normalDist(generator);
+      assignHost(stochasticPart, drawn);
     } else
       check(pf_generate_uncorrelated(plan, seed,
-                                     stochasticPart.dataVector.data()));
-    stochasticPart.evalValid = false;
+                                     writePointer(stochasticPart, count)));
   }
 
   // Matrix::setVarianceAsField, matrix.hh:473-479
   void setVarianceAsField(StochasticPartType& stochasticPart) const
   {
-    stochasticPart.dataVector.resize((*traits).localDomainSize);
-    check(pf_set_variance_as_field(plan, stochasticPart.dataVector.data()));
-    stochasticPart.evalValid = false;
+    check(pf_set_variance_as_field(
+      plan, writePointer(stochasticPart, (*traits).localDomainSize)));
   }
 
   // access for callers that want to keep data on the device
@@ -462,10 +484,74 @@ private:
   StochasticPartType apply(int op, const StochasticPartType& input) const
   {
     ensureFilled();
-    StochasticPartType output(input);
-    check(pf_apply(plan, op, input.dataVector.data(), output.dataVector.data()));
-    output.evalValid = false;
+    if (isEmpty(input))
+      return input; // a field that was never filled is the zero field
+    StochasticPartType output = likeInput(input);
+    check(pf_apply(plan, op, readPointer(input),
+                   writePointer(output, fieldSize(input))));
     return output;
+  }
+
+  // Where the values of a StochasticPart are.  The reference's class
+  // (stochastic.hh:54, this class is its friend through the traits) keeps
+  // them in a host vector that pf_* stages through the device; the
+  // specialisation of cudastochastic.hh hands out device pointers, and
+  // nothing is copied.
+  static constexpr bool deviceResident()
+  {
+    return cuda_detail::IsDeviceResident<StochasticPartType>::value;
+  }
+  static bool isEmpty(const StochasticPartType& part)
+  {
+    if constexpr (deviceResident())
+      return part.values.empty();
+    else
+      return part.dataVector.empty();
+  }
+  static std::size_t fieldSize(const StochasticPartType& part)
+  {
+    if constexpr (deviceResident())
+      return part.values.size();
+    else
+      return part.dataVector.size();
+  }
+  static const double* readPointer(const StochasticPartType& part)
+  {
+    if constexpr (deviceResident())
+      return part.values.deviceRead();
+    else
+      return part.dataVector.data();
+  }
+  // the whole field is about to be overwritten
+  static double* writePointer(StochasticPartType& part, std::size_t count)
+  {
+    if constexpr (deviceResident()) {
+      part.values.resize(count);
+      return part.values.deviceOverwrite();
+    } else {
+      part.dataVector.resize(count);
+      part.evalValid = false;
+      return part.dataVector.data();
+    }
+  }
+  static void assignHost(StochasticPartType& part, const std::vector<RF>& from)
+  {
+    if constexpr (deviceResident()) {
+      part.values.resize(from.size());
+      part.values.hostOverwrite() = from;
+    } else {
+      part.dataVector = from;
+      part.evalValid = false;
+    }
+  }
+  // a field with the geometry of `input` whose values will be overwritten:
+  // the device-resident class skips the copy of the values
+  static StochasticPartType likeInput(const StochasticPartType& input)
+  {
+    if constexpr (deviceResident())
+      return StochasticPartType(input, typename StochasticPartType::GeometryOnly{});
+    else
+      return StochasticPartType(input);
   }
 };
 

@@ -12,6 +12,7 @@
 // checkout at build time, a B200 at run time; run by tests/test_dropin.py).
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <iostream>
 #include <sstream>
 #include <string>
@@ -44,12 +45,27 @@ static int failures = 0;
 // compiled with -fno-access-control).  bulkEvaluate is not used here because
 // the reference's spare-field branch (matrix.hh:433-437) leaves evalValid set,
 // so it would return the previous field.
+// the reference's host class exposes dataVector; the device-resident class
+// of cudastochastic.hh hands out its host mirror
+template<class Part>
+auto
+cellValues(const Part& part, int) -> decltype(part.hostData())
+{
+  return part.hostData();
+}
+template<class Part>
+const std::vector<double>&
+cellValues(const Part& part, long)
+{
+  return part.dataVector;
+}
+
 template<class A, class B>
 double
 relDiff(const A& a, const B& b)
 {
-  const auto& va = a.stochasticPart.dataVector;
-  const auto& vb = b.stochasticPart.dataVector;
+  const auto& va = cellValues(a.stochasticPart, 0);
+  const auto& vb = cellValues(b.stochasticPart, 0);
   double num = 0., den = 0.;
   for (size_t i = 0; i < va.size() && i < vb.size(); i++) {
     num = std::max(num, std::abs(va[i] - vb[i]));
@@ -128,6 +144,65 @@ run(const std::string& name, const std::string& ini)
     b -= gpu;
     report("(2x - x) - x == 0", std::sqrt(b * b), 1e-12);
   }
+  { // the same operations against the reference's host loops, value by value
+    RefField a(ref);
+    CudaField b(gpu);
+    a *= 0.75;
+    b *= 0.75;
+    a.axpy(ref, 0.3);
+    b.axpy(gpu, 0.3);
+    a += ref;
+    b += gpu;
+    report("*=, axpy, += (values)", relDiff(a, b), 1e-10);
+    report("scalar product", std::abs(a * ref - b * gpu) / std::abs(a * ref), 1e-12);
+    report("oneNorm", std::abs(a.oneNorm() - b.oneNorm()) / a.oneNorm(), 1e-12);
+    report("infNorm", std::abs(a.infNorm() - b.infNorm()) / a.infNorm(), 1e-14);
+    CudaField c(b);
+    report("operator== (copy)", c == b ? 0. : 1., 0.5);
+    c *= 1.0000001;
+    report("operator!= (scaled copy)", c != b ? 0. : 1., 0.5);
+#ifndef PARAFIELDS_CUDA_HOST_STOCHASTIC
+    typename RefField::Traits::DomainType center;
+    for (unsigned int i = 0; i < dim; i++)
+      center[i] = 0.4 + 0.1 * i;
+    // the reference's own localize does not compile (stochastic.hh:806 calls
+    // the non-static indicesToCoords without an object), so its loop
+    // (stochastic.hh:798-817, cell centres by fieldtraits.hh:461-469) is
+    // applied to the reference's values here
+    {
+      auto& va = a.stochasticPart.dataVector;
+      const auto& tr = *a.traits;
+      const double factor = std::pow(2. * 3.14159, -(dim / 2.));
+      for (size_t i = 0; i < va.size(); i++) {
+        size_t r = i;
+        double dist = 0.;
+        for (unsigned int j = 0; j < dim; j++) {
+          const double x = (r % tr.localCells[j] + 0.5) * tr.extensions[j] / tr.cells[j];
+          r /= tr.localCells[j];
+          dist += (x - center[j]) * (x - center[j]);
+        }
+        va[i] *= factor * std::exp(-0.5 * dist / (0.3 * 0.3));
+      }
+    }
+    b.localize(center, 0.3);
+    report("localize", relDiff(a, b), 1e-12);
+#endif
+    a.zero();
+    b.zero();
+    report("zero", a.oneNorm() + b.oneNorm(), 1e-300);
+  }
+#ifndef PARAFIELDS_CUDA_HOST_STOCHASTIC
+  { // the plugin's field stays in HBM through an operator chain: nothing is
+    // staged through the host until values are asked for
+    CudaField b(gpu);
+    b.timesMatrix();
+    b.timesInverseMatrix();
+    b *= 2.;
+    const bool resident = b.stochasticPart.residentOnDevice() &&
+                          !b.stochasticPart.values.onHost();
+    report("operator chain stays on the device", resident ? 0. : 1., 0.5);
+  }
+#endif
   { // evaluation-time value transform through the reference's bulkEvaluate
     std::vector<typename RefField::Traits::RangeType> va, vb;
     typename RefField::Traits::Indices sa, sb;
@@ -225,9 +300,93 @@ runCustom(const std::string& name, const std::string& ini)
   }
 }
 
-int
-main()
+// `dropin_test chain [cells] [repeats]`: K5's operator chain
+// timesMatrix -> timesInverseMatrix through the reference's RandomField on the
+// plugin alone (3D cells^3 exponential, caches off, CG count pinned), timed
+// with the host clock around synchronised calls.  Compiled a second time with
+// PARAFIELDS_CUDA_HOST_STOCHASTIC (the reference's host StochasticPart, every
+// operand staged through PCIe) for the figure beside it.
+#include <chrono>
+static int
+chain(unsigned int cells, int repeats)
 {
+  using GT = GridTraits<double, double, 3>;
+  using CudaField =
+    parafields::RandomField<GT, parafields::CudaMatrix, parafields::CudaMatrix>;
+  const std::string c = std::to_string(cells);
+  const std::string ini =
+    "[grid]\nextensions = 1 1 1\ncells = " + c + " " + c + " " + c +
+    "\n[stochastic]\nvariance = 1.\ncovariance = exponential\ncorrLength = 0.05\n"
+    "[randomField]\ncgIterations = 10\ncacheInvMatvec = 0\ncacheInvRootMatvec = 0\n"
+    "[cuda]\nrng = fast\n";
+  Dune::ParameterTree config;
+  std::istringstream in(ini);
+  Dune::ParameterTreeParser::readINITree(in, config);
+  CudaField field(config);
+  field.generate(42u);
+  pf_plan* plan = field.isoMatrix->cudaPlan();
+  auto now = [&] {
+    pf_plan_synchronize(plan);
+    return std::chrono::steady_clock::now();
+  };
+  auto ms = [](auto a, auto b) {
+    return std::chrono::duration<double, std::milli>(b - a).count();
+  };
+  double tMat = 0., tInv = 0., tVec = 0.;
+  CudaField other(field);
+  if (std::getenv("PF_CHAIN_DETAIL")) { // where the time of one call goes
+    for (int r = 0; r < 3; r++) {
+      const auto t0 = now();
+      auto product = field.isoMatrix->multiplyInverse(field.stochasticPart);
+      const auto t1 = now();
+      field.stochasticPart = product;
+      const auto t2 = now();
+      field.trendPart.timesInverseMatrix();
+      const auto t3 = now();
+      std::fprintf(stderr, "multiplyInverse %.3f ms, assignment %.3f ms, trend %.3f ms\n",
+                   ms(t0, t1), ms(t1, t2), ms(t2, t3));
+    }
+  }
+  for (int r = -1; r < repeats; r++) { // one untimed round first
+    const auto t0 = now();
+    field.timesMatrix();
+    const auto t1 = now();
+    field.timesInverseMatrix();
+    const auto t2 = now();
+    field.axpy(other, 0.5);
+    field *= 0.5;
+    const double dot = field * other;
+    const auto t3 = now();
+    if (!(dot == dot))
+      return 2;
+    if (r >= 0) {
+      tMat += ms(t0, t1);
+      tInv += ms(t1, t2);
+      tVec += ms(t2, t3);
+    }
+  }
+#ifdef PARAFIELDS_CUDA_HOST_STOCHASTIC
+  const char* where = "host StochasticPart of the reference (values staged per call)";
+#else
+  const char* where = field.stochasticPart.values.onHost()
+                        ? "device-resident StochasticPart, HOST MIRROR TOUCHED"
+                        : "device-resident StochasticPart, host mirror never filled";
+#endif
+  std::printf("{\"chain\": \"K5 timesMatrix -> timesInverseMatrix (10 CG iterations) -> axpy, *=, "
+              "scalar product through RandomField\", \"cells\": %u, \"repeats\": %d, "
+              "\"timesMatrix_ms\": %.4f, \"timesInverseMatrix_ms\": %.4f, \"vector_ops_ms\": %.4f, "
+              "\"chain_ms\": %.4f, \"fields\": \"%s\"}\n",
+              cells, repeats, tMat / repeats, tInv / repeats, tVec / repeats,
+              (tMat + tInv + tVec) / repeats, where);
+  return 0;
+}
+
+int
+main(int argc, char** argv)
+{
+  if (argc > 1 && std::string(argv[1]) == "chain")
+    return chain(argc > 2 ? std::stoul(argv[2]) : 256u,
+                 argc > 3 ? std::stoi(argv[3]) : 5);
   const std::string tail = "[stochastic]\nvariance = 1.\n";
   run<1>("1D 32, exponential (test/randomfield1d.ini)",
          "[grid]\nextensions = 1\ncells = 32\n" + tail +

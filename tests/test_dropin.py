@@ -21,6 +21,21 @@ def test_reference_randomfield_with_cuda_matrix():
     assert "FAIL" not in out.stdout
 
 
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(BIN), reason="oracle/_ref/dropin_test not built (no /root/reference)")
+def test_operator_chain_keeps_fields_on_the_device():
+    """timesMatrix -> timesInverseMatrix -> axpy, *=, scalar product through
+    the reference's RandomField: with the StochasticPart specialisation of
+    cudastochastic.hh the host mirror of the field is never filled"""
+    import json
+
+    out = subprocess.run([BIN, "chain", "64", "2"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["fields"] == "device-resident StochasticPart, host mirror never filled"
+    assert line["chain_ms"] > 0
+
+
 # product binary: the reference's src/fieldgenerator.cc linked against
 # libparafields_cuda.so and the SIZES-ONLY FFTW stand-in (every CPU transform
 # entry point aborts), dune-parafields_b200/cli/Makefile
