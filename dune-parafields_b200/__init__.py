@@ -86,6 +86,7 @@ ABI_SYMBOLS = [
     "pf_vec_norminf",
     "pf_vec_equal",
     "pf_vec_fill",
+    "pf_vec_dot_static",
     "pf_field_refine",
     "pf_field_coarsen",
     "pf_field_localize",
@@ -237,6 +238,7 @@ def lib():
     L.pf_vec_norminf.argtypes = [vp, sz, dp, C.POINTER(C.c_double)]
     L.pf_vec_equal.argtypes = [vp, sz, dp, dp, C.POINTER(C.c_int)]
     L.pf_vec_fill.argtypes = [vp, sz, C.c_double, dp]
+    L.pf_vec_dot_static.argtypes = [vp, sz, dp, dp, dp]
     up = C.POINTER(C.c_uint)
     L.pf_field_refine.argtypes = [vp, C.c_int, up, dp, dp]
     L.pf_field_coarsen.argtypes = [vp, C.c_int, up, dp, dp]
@@ -747,6 +749,17 @@ class Plan:
 
     def norminf(self, x):
         return self._red(lib().pf_vec_norminf, x)
+
+    def dot_static(self, x, y, result=None):
+        """pf_vec_dot_static: no allocation inside the library; x, y device
+        tensors, result an optional 1-element device tensor (asynchronous)."""
+        n = x.numel()
+        if result is not None:
+            _check(lib().pf_vec_dot_static(self._h, n, _ptr(x), _ptr(y), _ptr(result)))
+            return result
+        r = C.c_double()
+        _check(lib().pf_vec_dot_static(self._h, n, _ptr(x), _ptr(y), C.byref(r)))
+        return r.value
 
     def equal(self, x, y):
         n = x.size if isinstance(x, np.ndarray) else x.numel()

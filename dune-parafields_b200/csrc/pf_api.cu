@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -4820,6 +4821,84 @@ pf_vec_fill(pf_plan* pl, size_t nn, double value, double* x)
   if (!sx.owned)
     return 0;
   return sx.finish();
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------
+// pf_vec_dot_static: the scalar product of pf_vec_dot with its scratch (the
+// per-block partial sums of k_reduce1 / k_reduce2) in a file-scope device
+// array instead of plan memory from cudaMalloc.  No counterpart in the
+// reference; added for callers that
+// cannot allocate (CUDA graph capture, serving loops).  Every GPU that loads
+// the library holds the array (4800 bytes) until exit; every call shares it,
+// so calls that overlap on one GPU race.  Nothing in it has to start at zero:
+// each of the nb blocks overwrites its partial before k_reduce2 reads the
+// first nb entries.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr size_t STATIC_DOT_MAX = size_t(1) << 28; // elements per call
+static __device__ __align__(256) double g_static_red[RED_BLOCKS + 8];
+constexpr int STATIC_MAX_DEVICES = 64;
+double* g_static_red_ptr[STATIC_MAX_DEVICES] = {};
+std::mutex g_static_red_guard;
+
+// device address of g_static_red on `device` (which is current): the name
+// itself is a host-side stand-in in host code
+int
+static_red_address(int device, double** ptr)
+{
+  if (device < 0 || device >= STATIC_MAX_DEVICES)
+    return fail(PF_ERR_INVALID, "pf_vec_dot_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_static_red_guard);
+  if (!g_static_red_ptr[device]) {
+    double* p = nullptr;
+    PF_CUDA(cudaGetSymbolAddress((void**)&p, g_static_red));
+    g_static_red_ptr[device] = p;
+  }
+  *ptr = g_static_red_ptr[device];
+  return 0;
+}
+} // namespace
+
+extern "C" {
+
+int
+pf_vec_dot_static(pf_plan* pl, size_t nn, const double* x, const double* y,
+                  double* result)
+{
+  PF_TRY(check_plan(pl));
+  if (!x || !y || !result)
+    return fail(PF_ERR_INVALID, "pf_vec_dot_static: null argument");
+  if (nn > STATIC_DOT_MAX)
+    return fail(PF_ERR_INVALID,
+                "pf_vec_dot_static: n = " + std::to_string(nn) +
+                  " exceeds the maximum of " + std::to_string(STATIC_DOT_MAX) +
+                  " elements (use pf_vec_dot)");
+  if (pl->nranks > 1)
+    return fail(PF_ERR_INVALID,
+                "pf_vec_dot_static: not available on a connected multi-GPU plan");
+  // host arrays would need a staging allocation
+  if (!is_device_ptr(x) || !is_device_ptr(y))
+    return fail(PF_ERR_INVALID,
+                "pf_vec_dot_static: x and y must be device arrays");
+  double* scratch = nullptr;
+  PF_TRY(static_red_address(pl->device, &scratch));
+  // same grid and summation order as pf_vec_dot (reduce_dev): bit-identical
+  const int nb =
+    std::max(1, (int)std::min<size_t>(RED_BLOCKS, (nn + RED_THREADS - 1) / RED_THREADS));
+  const bool dev_result = is_device_ptr(result);
+  double* dst = dev_result ? result : scratch + RED_BLOCKS;
+  k_reduce1<<<nb, RED_THREADS, 0, pl->stream>>>(nn, x, y, nullptr, 0, scratch);
+  k_reduce2<<<1, RED_THREADS, 0, pl->stream>>>(nb, scratch, 0, dst);
+  PF_CUDA(cudaGetLastError());
+  pl->launches += 2;
+  if (dev_result)
+    return 0; // asynchronous on the plan's stream
+  PF_CUDA(cudaMemcpyAsync(result, dst, sizeof(double), cudaMemcpyDeviceToHost,
+                          pl->stream));
+  PF_CUDA(cudaStreamSynchronize(pl->stream));
+  return 0;
 }
 
 // ---------------------------------------------------------------------------

@@ -294,6 +294,24 @@ int pf_vec_equal(pf_plan* plan, size_t n, const double* x, const double* y,
                  int* same);
 /* StochasticPart::zero (stochastic.hh:581-587) and constant fields */
 int pf_vec_fill(pf_plan* plan, size_t n, double value, double* x);
+/* pf_vec_dot without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The per-block partial sums live in a file-scope
+ * `static __device__` array of 600 doubles (4800 bytes, held by every GPU that
+ * loads the library until exit) instead of plan memory; the call performs no
+ * cudaMalloc / cudaFree.  x and y must be DEVICE arrays of n doubles (host
+ * arrays would need a staging buffer: PF_ERR_INVALID), n <= PF_STATIC_DOT_MAX
+ * (larger n: PF_ERR_INVALID, use pf_vec_dot), single-GPU plans only.  result
+ * may be a device pointer (written asynchronously on the plan's stream) or a
+ * host pointer (the call synchronises).  Same grid and summation order as
+ * pf_vec_dot: the value is bit-identical.  All calls on one GPU share the
+ * array (it keeps the last call's partial sums; nothing has to start at zero
+ * because every block overwrites its entry before it is read): calls that
+ * overlap on the GPU -- different plans or streams -- race. */
+#define PF_STATIC_DOT_MAX ((size_t)1 << 28)
+int pf_vec_dot_static(pf_plan* plan, size_t n, const double* x,
+                      const double* y, double* result);
 
 /* Resolution transfer, localisation and point evaluation of a field
  * (SURVEY 8(f) rows 1 and 3).  Arrays may be device or host memory (host
