@@ -167,6 +167,16 @@ extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
       // output with LPC*16-byte boxes in the matching swizzle mode
       using G = G3Cfg<N>;
       const TileMaps tms = *reinterpret_cast<const TileMaps*>(tmap);
+#if PF_N == 1024
+      // embedding factor 2: half of the line is kept (compile-time pruning)
+      if (a.keep == N / 2 && a.noise_kind == NOISE_PHILOX_FAST)
+        e = launch_pipe(kp_gen3<N, NOISE_PHILOX_FAST, true>, G::THREADS, G::SMEM,
+                        grid, st, a, tw2, tms);
+      else if (a.keep == N / 2 && a.noise_kind == NOISE_PHILOX_F64)
+        e = launch_pipe(kp_gen3<N, NOISE_PHILOX_F64, true>, G::THREADS, G::SMEM,
+                        grid, st, a, tw2, tms);
+      else
+#endif
       if (a.noise_kind == NOISE_PHILOX_FAST)
         e = launch_pipe(kp_gen3<N, NOISE_PHILOX_FAST>, G::THREADS, G::SMEM, grid,
                         st, a, tw2, tms);

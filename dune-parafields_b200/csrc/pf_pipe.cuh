@@ -434,7 +434,12 @@ group_sync(int g)
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(PF_THREADS) : "memory");
 }
 
-template <int N, int NOISE>
+// HALF: keep == N / 2 (embedding factor 2, the usual case) is known at compile
+// time, so the upper half of the transform's outputs is dead code: the last
+// butterflies that would produce it and the per-element bound checks go
+// (ncu source view, profiles/r2k: 192 of the 263 instructions between the FFT
+// and the tensor store were swizzle addresses and bound checks)
+template <int N, int NOISE, bool HALF = false>
 __global__ void __launch_bounds__(G3Cfg<N>::THREADS, 1)
 kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
         const __grid_constant__ TileMaps tms)
@@ -493,11 +498,14 @@ kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
     group_sync(g);
     line_fft<N, +1, true>(v, xbuf, t, tws);
     group_sync(g);
+    {
+      // element e = t + TPL q of line lic: the swizzle term of stage_slot
+      // does not change with q, the slot advances by TPL * LPC per step
+      cplx* sp = stage + stage_slot<N>(t, lic);
 #pragma unroll
-    for (int q = 0; q < C::E; q++) {
-      const int e = t + C::TPL * q;
-      if (e < keep)
-        stage[stage_slot<N>(e, lic)] = v[q];
+      for (int q = 0; q < (HALF ? C::E / 2 : C::E); q++)
+        if (HALF || t + C::TPL * q < keep)
+          sp[q * (C::TPL * K::LPC)] = v[q];
     }
     fence_proxy_async();
     group_sync(g);
