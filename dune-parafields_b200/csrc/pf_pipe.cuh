@@ -479,7 +479,8 @@ kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
     const int a0 = p.a_begin + at * K::LPC;
     // lines beyond A recompute the last valid line; the tensor store clips
     const int a = min(a0 + lic, a_last);
-    if (tg == 0) {
+    // issued by the second warp: the first one issues the tensor stores
+    if (tg == 32) {
       mbar_expect_tx(bar, K::LPC * sig_bytes);
 #pragma unroll
       for (int l = 0; l < K::LPC; l++)
@@ -508,11 +509,22 @@ kp_gen3(const PassArgs p, const cplx* __restrict__ tw2,
           sp[q * (C::TPL * K::LPC)] = v[q];
     }
     fence_proxy_async();
-    group_sync(g);
+    // only the storing thread has to see the whole tile: the other warps
+    // announce their rows and go on to the next tile's noise (registers only).
+    // Own barrier id: a warp that runs ahead waits at the next group_sync,
+    // which must not be taken for the missing arrivals of this one.
+    if (tg < 32)
+      asm volatile("bar.sync %0, %1;" ::"r"(g + 1 + G::GROUPS), "r"(PF_THREADS)
+                   : "memory");
+    else
+      asm volatile("bar.arrive %0, %1;" ::"r"(g + 1 + G::GROUPS), "r"(PF_THREADS)
+                   : "memory");
     if (tg == 0) {
-      for (int r0 = 0; r0 < keep; r0 += G::BOXR)
-        tma_store_3d(&tms.m[0], smem_u32(region) + r0 * G::ROWB,
-                     2 * at * K::LPC, r0, b);
+#pragma unroll
+      for (int r0 = 0; r0 < G::MAXKEEP; r0 += G::BOXR)
+        if (HALF || r0 < keep)
+          tma_store_3d(&tms.m[0], smem_u32(region) + r0 * G::ROWB,
+                       2 * at * K::LPC, r0, b);
       bulk_commit();
       pending = true;
     }
