@@ -245,7 +245,10 @@ extern "C" int PF_CAT(pf_stream_launch_n, PF_N)(int which, const void* args,
     return (int)cudaSuccess;
   if (which == 0) {
     const StreamArgs& sa = *reinterpret_cast<const StreamArgs*>(args);
-    if (sa.a.noise_kind == NOISE_PHILOX_FAST)
+    if (sa.a.noise_kind == NOISE_PHILOX_FAST && sa.c1 == N / 2 && sa.c2 == N / 2)
+      e = launch_stream(kp_ab<N, NOISE_PHILOX_FAST, true>, S::THREADS, S::SMEM, grid,
+                        st, sa, tw2, tm[0]);
+    else if (sa.a.noise_kind == NOISE_PHILOX_FAST)
       e = launch_stream(kp_ab<N, NOISE_PHILOX_FAST>, S::THREADS, S::SMEM, grid, st,
                       sa, tw2, tm[0]);
     else if (sa.a.noise_kind == NOISE_PHILOX_F64)

@@ -199,7 +199,9 @@ stream_ready(const StreamItem& w, const unsigned* doneA, const unsigned* doneB,
   return true;
 }
 
-template <int N, int NOISE>
+// HALF: c1 == c2 == N / 2 (embedding factor 2) known at compile time -- the
+// upper half of the outputs and the bound checks are dead code (as kp_gen3)
+template <int N, int NOISE, bool HALF = false>
 __global__ void __launch_bounds__(SCfg<N>::THREADS, 1)
 kp_ab(const __grid_constant__ StreamArgs s, const cplx* __restrict__ tw2,
       const __grid_constant__ CUtensorMap ring_map)
@@ -336,10 +338,12 @@ kp_ab(const __grid_constant__ StreamArgs s, const cplx* __restrict__ tw2,
       }
       mbar_wait(gbar, gph);
       gph ^= 1;
+      {
+        // row e = t + TPL q: the swizzle term does not change with q
+        const unsigned char* src = region + swz_off<S::ROWB>(t, lic);
 #pragma unroll
-      for (int q = 0; q < C::E; q++) {
-        const int e = t + S::TPL * q;
-        v[q] = *reinterpret_cast<const cplx*>(region + swz_off<S::ROWB>(e, lic));
+        for (int q = 0; q < C::E; q++)
+          v[q] = *reinterpret_cast<const cplx*>(src + q * (S::TPL * S::ROWB));
       }
       group_sync(g); // every warp holds its lines: the region becomes exchange space
       if (tg == 0)
@@ -360,8 +364,8 @@ kp_ab(const __grid_constant__ StreamArgs s, const cplx* __restrict__ tw2,
     __syncwarp();
     line_fft<N, +1, true>(v, xbuf, t, tws);
 #pragma unroll
-    for (int q = 0; q < C::E; q++) {
-      if (t + S::TPL * q < keep)
+    for (int q = 0; q < (HALF ? C::E / 2 : C::E); q++) {
+      if (HALF || t + S::TPL * q < keep)
         st_hint(out, v[q], pol);
       out += ostep;
     }
