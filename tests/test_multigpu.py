@@ -43,6 +43,20 @@ def test_slab_mode_equals_single_gpu():
     assert "SLAB PARITY" in out.stdout and "OK" in out.stdout
 
 
+@pytest.mark.gpu
+def test_slab_peer_wait_is_bounded_and_fatal():
+    """one rank sleeps past PF_SLAB_TIMEOUT_S: the waiting rank's call fails
+    within the limit and its plan stays failed (no hang, no silent result)"""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    out = torchrun(os.path.join(ROOT, "tests", "mgpu_slab_timeout.py"), 2, extra_env={"PF_SLAB_TIMEOUT_S": "2"}, timeout=180)
+    print(out.stdout[-3000:])
+    assert out.returncode == 0, out.stdout[-3000:]
+    assert "SLAB TIMEOUT OK" in out.stdout
+
+
 def test_slab_decomposition_gloo_world2():
     out = torchrun(os.path.join(ROOT, "tests", "gloo_slab_emulation.py"), 2, timeout=300)
     print(out.stdout[-3000:])
