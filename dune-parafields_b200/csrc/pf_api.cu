@@ -1030,6 +1030,7 @@ struct pf_plan
   std::map<std::pair<long long, int>, GenTab> gen_tabs; // (n, dir)
   std::map<long long, cplx*> gen_tw;                    // per M
   cplx* GW = nullptr; // stored spectrum m0 * n1 * n2
+  cplx* LO[4] = { nullptr, nullptr, nullptr, nullptr }; // operators on long lines: scratch
   // custom covariance (custom-iso / custom-aniso, matrix.hh:270-279): the torus
   // covariance evaluated by the caller, natural order [x2][x1][x0]
   double* cov_table = nullptr;
@@ -1220,6 +1221,8 @@ free_sized(pf_plan* pl)
   dev_free(&pl->LY);
   dev_free(&pl->LU);
   dev_free(&pl->GW);
+  for (auto& q : pl->LO)
+    dev_free(&q);
   dev_free(&pl->spare);
   pl->spare_valid = false;
   pl->eig_valid = false;
@@ -1790,10 +1793,13 @@ launch_long1(pf_plan* pl, int N1, const pf::LongArgs& g, const PassArgs& p,
 // step 1 (covariance evaluation or complex input) into Y, step 2 = k_c2t with
 // (a = j1, b = line), whose tile store interleaves the sub-lines back into
 // natural order: out[line*out_pitch + j1 + N1*e], e < keep
+// dir = +1: the backward transform (conjugate twiddles, kp_c2t<+1>);
+// in_valid / in_real: zero padding and real input of step 1 (LongArgs)
 int
 long_fft_forward(pf_plan* pl, int axis, bool from_cov, const cplx* in,
                  long long in_pitch, long long lines, cplx* Y, cplx* out,
-                 long long out_pitch, long long keep)
+                 long long out_pitch, long long keep, int dir = -1,
+                 long long in_valid = 0, int in_real = 0)
 {
   const long long n = pl->n[axis];
   const int N1 = (int)pl->LN1[axis], N2 = (int)pl->LN2[axis];
@@ -1804,11 +1810,15 @@ long_fft_forward(pf_plan* pl, int axis, bool from_cov, const cplx* in,
   PF_TRY(long_twiddles(pl, n, &g.tw));
   g.in = in;
   g.in_pitch = in_pitch;
+  g.in_valid = in_valid;
+  g.in_real = in_real;
   g.out = Y;
   PassArgs p = blank_args();
   p.cov = pl->cov;
   if (from_cov)
     PF_TRY((launch_long1<pf::LSRC_COV, -1>(pl, N1, g, p, lines)));
+  else if (dir > 0)
+    PF_TRY((launch_long1<pf::LSRC_CPLX, +1>(pl, N1, g, p, lines)));
   else
     PF_TRY((launch_long1<pf::LSRC_CPLX, -1>(pl, N1, g, p, lines)));
   PassArgs a = blank_args();
@@ -1822,7 +1832,74 @@ long_fft_forward(pf_plan* pl, int axis, bool from_cov, const cplx* in,
   a.osb = out_pitch;
   a.ose = N1;
   a.keep = (int)keep;
-  return run_pass(pl, N2, pf::K_C2T_FWD, a);
+  return run_pass(pl, N2, dir > 0 ? pf::K_C2T_INV : pf::K_C2T_FWD, a);
+}
+
+// multiplyExtended / multiplyRootExtended / multiplyInverseExtended
+// (matrix.hh:1459-1662) for 2D plans with long lines: full complex transforms
+// of the zero-padded field with the two-step primitive, rows first, transposed,
+// rows again; g(lambda) / N in between; the same backwards, pruned to the
+// physical sub-box.
+int
+apply_long2d(pf_plan* pl, const double* tab, const double* in_dev, double* out_dev)
+{
+  const long long* n = pl->n;
+  const long long* c = pl->c;
+  const long long m0 = pl->m0;
+  const long long N1a = pl->LN1[0], N2a = pl->LN2[0]; // axis 0: n0 = N1a * N2a
+  const long long N1b = pl->LN1[1], N2b = pl->LN2[1];
+  const long long keep0 = (c[0] + N1a - 1) / N1a, p0 = N1a * keep0; // >= c0
+  const long long keep1 = (c[1] + N1b - 1) / N1b, p1 = N1b * keep1; // >= c1
+  // scratch kept with the plan (13 GB at K4's size: a PCG would otherwise pay
+  // the allocations on every product)
+  cplx *&Y = pl->LO[0], *&A = pl->LO[1], *&At = pl->LO[2], *&S = pl->LO[3];
+  auto transpose = [&](const cplx* in, long long ipitch, cplx* out, long long opitch,
+                       long long rows, long long cols) -> int {
+    const dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
+    pf::k_long_transpose<<<grid, dim3(32, 8), 0, pl->stream>>>(in, ipitch, out, opitch,
+                                                             rows, cols);
+    pl->launches++;
+    return cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "transpose");
+  };
+  int rc = dev_alloc(&Y, (size_t)n[0] * n[1]);
+  if (rc == 0)
+    rc = dev_alloc(&A, (size_t)c[1] * n[0]);
+  if (rc == 0)
+    rc = dev_alloc(&At, (size_t)n[0] * std::max(c[1], p1));
+  if (rc == 0)
+    rc = dev_alloc(&S, (size_t)n[0] * n[1]);
+  // forward: rows x1 < c1 along axis 0 (real input, zero padded beyond c0)
+  if (rc == 0)
+    rc = long_fft_forward(pl, 0, false, reinterpret_cast<const cplx*>(in_dev), c[0],
+                          c[1], Y, A, n[0], N2a, -1, c[0], 1);
+  if (rc == 0)
+    rc = transpose(A, n[0], At, c[1], c[1], n[0]); // At[k0][x1 < c1]
+  // rows k0 along axis 1 (zero padded beyond c1)
+  if (rc == 0)
+    rc = long_fft_forward(pl, 1, false, At, c[1], n[0], Y, S, n[1], N2b, -1, c[1], 0);
+  if (rc == 0) {
+    const long long total = n[0] * n[1];
+    pf::k_long_spec<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
+      S, n[0], n[1], tab, m0, pl->P, pl->compact ? 1 : 0, 1.0 / (double)pl->Next);
+    pl->launches++;
+    rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "spectral multiply");
+  }
+  // backward along axis 1, kept x1 < p1 (>= c1)
+  if (rc == 0)
+    rc = long_fft_forward(pl, 1, false, S, n[1], n[0], Y, At, p1, keep1, +1);
+  if (rc == 0)
+    rc = transpose(At, p1, A, n[0], n[0], c[1]); // A[x1 < c1][k0]
+  // backward along axis 0, kept x0 < p0; S is free again
+  if (rc == 0)
+    rc = long_fft_forward(pl, 0, false, A, n[0], c[1], Y, S, p0, keep0, +1);
+  if (rc == 0) {
+    const long long total = c[1] * c[0];
+    pf::k_long_real<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
+      S, p0, out_dev, c[1], c[0]);
+    pl->launches++;
+    rc = cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "real part");
+  }
+  return rc;
 }
 
 // eigenvalues of a 2D plan with long lines: full complex transforms (one-time
@@ -3507,10 +3584,6 @@ apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
 {
   if (pl->nranks > 1)
     return apply_slab_dev(pl, op, in_dev, out_dev);
-  if (pl->long2d && !pl->generic)
-    return fail(PF_ERR_INVALID,
-                "covariance operators need extended sizes <= 1024 in this "
-                "build (sampling supports up to 16384 in 2D)");
   double** tabp = op == PF_OP_MATRIX ? &pl->lam
                   : op == PF_OP_ROOT ? &pl->sig
                                      : &pl->inv;
@@ -3520,6 +3593,8 @@ apply_dev(pf_plan* pl, int op, const double* in_dev, double* out_dev)
     PF_TRY(ensure_table(pl, tabp, op == PF_OP_ROOT ? 1 : 2));
   if (pl->generic)
     return apply_generic(pl, *tabp, in_dev, out_dev);
+  if (pl->long2d)
+    return apply_long2d(pl, *tabp, in_dev, out_dev);
   PF_TRY(ensure_work(pl));
   const double* tab = *tabp;
   const long long* n = pl->n;

@@ -33,9 +33,12 @@ struct LongArgs
   int perm_n1, perm_m;
   long long k0_max;  // columns with k0 > k0_max are padding (zeros)
   long long n_half;  // n / 2
-  // complex source
+  // complex source (in_real: the array holds doubles, the imaginary part is
+  // zero); entries x >= in_valid are zero padding (0: the whole line is present)
   const cplx* in;
   long long in_pitch;
+  long long in_valid;
+  int in_real;
   cplx* out;         // Y[line][j1][k2]
 };
 
@@ -146,9 +149,15 @@ k_long1(const LongArgs g, const PassArgs p)
 #pragma unroll
     for (int k1 = 0; k1 < N1; k1++) {
       const long long x = (long long)k1 * N2 + k2;
-      if constexpr (SRC == LSRC_CPLX)
-        v[k1] = __ldg(g.in + line * g.in_pitch + x);
-      else
+      if constexpr (SRC == LSRC_CPLX) {
+        if (g.in_valid > 0 && x >= g.in_valid)
+          v[k1] = make_double2(0., 0.);
+        else if (g.in_real)
+          v[k1] = make_double2(
+            __ldg(reinterpret_cast<const double*>(g.in) + line * g.in_pitch + x), 0.);
+        else
+          v[k1] = __ldg(g.in + line * g.in_pitch + x);
+      } else
         v[k1] = make_double2(cov_torus(p.cov, (unsigned)x, (unsigned)line, 0), 0.);
     }
     Dft<N1, DIR, 1>::run(v);
@@ -259,6 +268,39 @@ k_long_lambda(const cplx* __restrict__ C, long long c_pitch, double* __restrict_
       atomicAdd(census + 2, (unsigned long long)nneg);
     atomicMin(smallest_bits, ordered_bits(smallest));
   }
+}
+
+// covariance operators on long lines: S[k0][k1] *= g(lambda(k0, k1)) * scale,
+// table[k0' * P + k1'] holds rows k0' <= n0/2 (lambda(k) = lambda(-k) gives the
+// others) and, when mirror is set, entries k1' <= n1/2
+__global__ void __launch_bounds__(256)
+k_long_spec(cplx* __restrict__ S, long long n0, long long n1,
+            const double* __restrict__ tab, long long m0, long long P, int mirror,
+            double scale)
+{
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n0 * n1)
+    return;
+  long long k0 = i / n1, k1 = i % n1;
+  if (k0 >= m0) {
+    k0 = n0 - k0;
+    k1 = k1 ? n1 - k1 : 0;
+  }
+  if (mirror && 2 * k1 > n1)
+    k1 = n1 - k1;
+  const double g = __ldg(tab + k0 * P + k1) * scale;
+  const cplx v = S[i];
+  S[i] = make_double2(v.x * g, v.y * g);
+}
+
+// real part of a complex matrix, restricted: out[r][c] = Re in[r][c]
+__global__ void __launch_bounds__(256)
+k_long_real(const cplx* __restrict__ in, long long in_pitch, double* __restrict__ out,
+            long long rows, long long cols)
+{
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < rows * cols)
+    out[i] = in[(i / cols) * in_pitch + i % cols].x;
 }
 
 // tw[a * N2 + b] = exp(-2 pi i a b / n), a < N1, b < N2: the inter-step

@@ -70,10 +70,40 @@ def test_long_device_noise_statistics(m):
     assert rel(t, np.exp(a)) < 1e-13
 
 
-def test_long_operators_fail_loudly(m):
-    with m.Plan([1024, 8], covariance="exponential", corr_length=0.05) as p:
-        with pytest.raises(m.PfError, match="covariance operators need extended sizes"):
-            p.apply("matrix", np.zeros((8, 1024)))
+OP_CASES = [
+    dict(cells=[1024, 8], covariance="exponential", corr_length=0.05),
+    dict(cells=[8, 2048], covariance="exponential", corr_length=0.05),
+    dict(cells=[2048, 1024], covariance="exponential", corr_length=0.05),
+    dict(cells=[1024, 1024], **GEO),  # half-spectrum table (geometric anisotropy)
+    dict(cells=[8192, 4], covariance="spherical", corr_length=0.1),
+]
+
+
+@pytest.mark.parametrize("case", OP_CASES, ids=ids)
+def test_long_operators(m, case):
+    """multiplyExtended / multiplyRootExtended / multiplyInverseExtended
+    (matrix.hh:1459-1662) on long lines: full complex two-step transforms"""
+    o = ol.Oracle(**case)
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal(tuple(reversed(case["cells"])))
+    with m.Plan(**case) as p:
+        for op in ("matrix", "root", "inverse_ext"):
+            y = p.apply(op, x)
+            y_o = o.multiply(x, op)
+            assert y.shape == y_o.shape
+            # 1 / lambda on clamped (approximate) spectra amplifies the rounding
+            # of lambda itself (values ~1e11): looser there
+            tol = 1e-7 if (op == "inverse_ext" and case.get("approximate")) else TOL
+            assert rel(y, y_o) < tol, op
+
+
+def test_long_pcg(m):
+    # Matrix::multiplyInverse (innerCG, matrix.hh:1331-1448), pinned iteration count
+    case = dict(cells=[1024, 16], covariance="exponential", corr_length=0.05, cg_iterations=4)
+    o = ol.Oracle(**case)
+    x = np.random.default_rng(6).standard_normal((16, 1024))
+    with m.Plan(**case) as p:
+        assert rel(p.solve(x), o.multiply_inverse(x)) < 1e-8
 
 
 def test_long_3d_limits(m):
