@@ -408,6 +408,25 @@ def other_workloads(torch, pfb, stream, peak):
                 nb = 64 if name != "K2" else 16
                 msb = timed_generate(torch, p, stream, 3, 1, tr, first=1000, batch=nb if name != "K4" else 16)
                 entry(name, "generate_batch (%d realizations per call; bytes of a batch of 64: sigma read once per batch)" % (nb if name != "K4" else 16), msb, algorithmic_bytes(wl["cells"], compact=compact, batch=64)["total"])
+                if name == "K4":
+                    # timesMatrix at K4's size (two-step complex transforms of the padded
+                    # field, apply_long2d).  Algorithmic bytes, 2D analogue of matvec_bytes:
+                    # field in + out, U[c1][m0] and V[n1][m0] written and read twice, lambda
+                    c0, c1 = wl["cells"]
+                    m0 = c0 + 1
+                    nb2 = 2 * 8 * c0 * c1 + 4 * 16 * m0 * c1 + 4 * 16 * m0 * 2 * c1 + 8 * m0 * 2 * c1
+                    x = torch.empty(p.domain_size, dtype=torch.float64, device="cuda")
+                    y = torch.empty_like(x)
+                    p.generate(1, out=x)
+                    p.apply("matrix", x, out=y)
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    stream.synchronize()
+                    e0.record(stream)
+                    for _ in range(3):
+                        p.apply("matrix", x, out=y)
+                    e1.record(stream)
+                    e1.synchronize()
+                    entry(name, "timesMatrix (one matvec, long lines)", e0.elapsed_time(e1) / 3, nb2)
         except Exception as e:
             out.append(dict(workload=name, error="%s: %s" % (type(e).__name__, e)))
     try:

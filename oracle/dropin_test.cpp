@@ -217,6 +217,40 @@ run(const std::string& name, const std::string& ini)
     }
     report("bulkEvaluate (transform)", num / den, 1e-10);
   }
+  if (dim > 1) { // RandomField::refineMatrix / refine / coarsenMatrix / coarsen
+    // (randomfield.hh:829-962) on fields of their own (the traits are shared
+    // by copies, and refineMatrix changes them)
+    RefField a(config);
+    CudaField b(cconfig);
+    a.generate(99u);
+    b.generate(99u);
+    CudaField before(b);
+    bool referenceRefines = true;
+    try {
+      a.refineMatrix();
+      a.refine();
+    } catch (const std::runtime_error& e) {
+      // the reference's DCT matrix backend refuses ("matrix is finalized")
+      referenceRefines = false;
+      std::printf("  (reference cannot refine this configuration: %s)\n", e.what());
+    }
+    b.refineMatrix();
+    b.refine();
+    if (referenceRefines)
+      report("refineMatrix + refine", relDiff(a, b), 1e-10);
+    if (referenceRefines) {
+      a.coarsenMatrix();
+      a.coarsen();
+    }
+    b.coarsenMatrix();
+    b.coarsen();
+    if (referenceRefines)
+      report("coarsenMatrix + coarsen", relDiff(a, b), 1e-10);
+    // coarsen(refine(x)) averages 2^dim equal values: up to the rounding of the
+    // sums (stochastic.hh:725,745)
+    b -= before;
+    report("coarsen(refine(x)) == x (plugin)", std::sqrt(b * b) / std::sqrt(before * before), 1e-14);
+  }
   { // device RNG: different from the reference stream but a valid field
     Dune::ParameterTree pconfig = config;
     CudaField p(pconfig);
