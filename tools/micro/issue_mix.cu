@@ -16,7 +16,7 @@ __global__ void k(double* out, unsigned* iout, int iters, long long* cyc)
   const long long t0 = clock64();
 #pragma unroll 1
   for (int it = 0; it < iters; it++) {
-    if (MODE != 3 && MODE != 5) {
+    if (MODE != 3 && MODE != 5 && MODE != 8 && MODE != 9 && MODE != 10) {
       a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
       a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
     }
@@ -33,6 +33,23 @@ __global__ void k(double* out, unsigned* iout, int iters, long long* cyc)
       unsigned long long p2 = (unsigned long long)i2 * 0xD2511F53u, p3 = (unsigned long long)i3 * 0xCD9E8D57u;
       i0 = (unsigned)(p0 >> 32) ^ (unsigned)p1; i1 = (unsigned)(p1 >> 32) ^ (unsigned)p2;
       i2 = (unsigned)(p2 >> 32) ^ (unsigned)p3; i3 = (unsigned)(p3 >> 32) ^ (unsigned)p0;
+    }
+    if (MODE == 7 || MODE == 8) { // the same products as IMAD (low half) + IMAD.HI
+      unsigned l0 = i0 * 0xD2511F53u, h0 = __umulhi(i0, 0xD2511F53u);
+      unsigned l1 = i1 * 0xCD9E8D57u, h1 = __umulhi(i1, 0xCD9E8D57u);
+      unsigned l2 = i2 * 0xD2511F53u, h2 = __umulhi(i2, 0xD2511F53u);
+      unsigned l3 = i3 * 0xCD9E8D57u, h3 = __umulhi(i3, 0xCD9E8D57u);
+      asm volatile("" : "+r"(l0), "+r"(h0), "+r"(l1), "+r"(h1));
+      asm volatile("" : "+r"(l2), "+r"(h2), "+r"(l3), "+r"(h3));
+      i0 = h0 ^ l1; i1 = h1 ^ l2; i2 = h2 ^ l3; i3 = h3 ^ l0;
+    }
+    if (MODE == 9) { // 8 IMAD (32-bit low product)
+      i0 = i0 * 0xD2511F53u + i1; i1 = i1 * 0xCD9E8D57u + i2; i2 = i2 * 0xD2511F53u + i3; i3 = i3 * 0xCD9E8D57u + i4;
+      i4 = i4 * 0xD2511F53u + i5; i5 = i5 * 0xCD9E8D57u + i6; i6 = i6 * 0xD2511F53u + i7; i7 = i7 * 0xCD9E8D57u + i0;
+    }
+    if (MODE == 10) { // 8 IMAD.HI
+      i0 = __umulhi(i0, 0xD2511F53u) ^ i1; i1 = __umulhi(i1, 0xCD9E8D57u) ^ i2; i2 = __umulhi(i2, 0xD2511F53u) ^ i3; i3 = __umulhi(i3, 0xCD9E8D57u) ^ i4;
+      i4 = __umulhi(i4, 0xD2511F53u) ^ i5; i5 = __umulhi(i5, 0xCD9E8D57u) ^ i6; i6 = __umulhi(i6, 0xD2511F53u) ^ i7; i7 = __umulhi(i7, 0xCD9E8D57u) ^ i0;
     }
     if (MODE == 6) { // MUFU
       f0 = __sinf(f0); f1 = __cosf(f1); f2 = __sinf(f2); f3 = __cosf(f3);
@@ -70,6 +87,10 @@ int main()
     run<4>("8 DFMA + 4 IMAD.WIDE + 4 LOP3", w);
     run<5>("4 IMAD.WIDE + 4 LOP3", w);
     run<6>("8 DFMA + 4 MUFU(+range red.)", w);
+    run<7>("8 DFMA + 4 (IMAD + IMAD.HI) + 4 LOP3", w);
+    run<8>("4 (IMAD + IMAD.HI) + 4 LOP3", w);
+    run<9>("8 IMAD (low product + add)", w);
+    run<10>("8 IMAD.HI + 8 LOP3", w);
   }
   return 0;
 }
