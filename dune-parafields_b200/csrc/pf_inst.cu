@@ -55,6 +55,13 @@ extern "C" int PF_CAT(pf_launch_n, PF_N)(int kind, const PassArgs* ap,
     case K_GEN_TILE: {
       const size_t sm = K::smem_tile(a.keep);
       const long long nb = ntA * a.B;
+#if PF_N >= 256
+      // embedding factor 2, one rank: half of the line kept, known at compile time
+      if (a.noise_kind == NOISE_PHILOX_FAST && a.keep == N / 2 && a.scale == 1.0 &&
+          a.n_peers <= 1)
+        e = launch(k_gen_tile<N, NOISE_PHILOX_FAST, true>, a, tw2, nb, sm, st);
+      else
+#endif
       if (a.noise_kind == NOISE_PHILOX_FAST)
         e = launch(k_gen_tile<N, NOISE_PHILOX_FAST>, a, tw2, nb, sm, st);
       else if (a.noise_kind == NOISE_PHILOX_F64)

@@ -591,7 +591,11 @@ stage_pitch()
   return (K::LPC == 4 || K::LPC == 8) ? K::LPC : K::SP;
 }
 
-template <int N>
+// HALF: keep == N / 2 and scale == 1 known at compile time -- the upper half of
+// the transform's outputs is dead code (its last butterflies go with it), no
+// bound checks, one stage address per thread (the swizzle term of stage_slot
+// does not change over a step of TPL rows)
+template <int N, bool HALF = false>
 __device__ __forceinline__ void
 tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
            cplx* __restrict__ obase, long long ose, int lines_valid,
@@ -599,7 +603,13 @@ tile_store(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t, int keep,
 {
   using K = KCfg<N>;
   __syncthreads(); // exchange area is about to be reused as the stage
-  if (scale == 1.0) {
+  if constexpr (HALF) {
+    keep = N / 2;
+    cplx* sp0 = stage + stage_slot<N>(t, lic);
+#pragma unroll
+    for (int q = 0; q < K::E / 2; q++)
+      sp0[q * (K::TPL * stage_pitch<N>())] = v[q];
+  } else if (scale == 1.0) {
 #pragma unroll
     for (int q = 0; q < K::E; q++) {
       const int e = t + K::TPL * q;
@@ -699,7 +709,7 @@ tile_store_peers(cplx (&v)[LineCfg<N>::E], cplx* stage, int lic, int t,
 #ifndef PF_GEN_MINB
 #define PF_GEN_MINB 3
 #endif
-template <int N, int NOISE>
+template <int N, int NOISE, bool HALF = false>
 __global__ void __launch_bounds__(PF_THREADS, PF_GEN_MINB)
 k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
 {
@@ -722,7 +732,7 @@ k_gen_tile(const PassArgs p, const cplx* __restrict__ tw2)
                         (long long)b * p.osb + p.a_begin + at * K::LPC, lv, b,
                         p.a_begin + at * K::LPC, p.scale);
   else
-    tile_store<N>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
+    tile_store<N, HALF>(v, sm, lic, t, p.keep, obase, ose, lv, p.scale);
 }
 
 // 1D: noise -> inverse FFT -> real part / imaginary part lines
