@@ -371,3 +371,21 @@ def test_fast_and_fp64_modes_agree_in_distribution(m):
     for v in vals.values():
         assert stats.kstest(v, "norm").pvalue > 1e-3
         assert abs(v.var() - 1.0) < 5.0 * np.sqrt(2.0 / v.size)
+
+
+def test_fp64_box_muller_routines_match_library_forms(tmp_path):
+    """neg2_log_uniform / sincos_turn_fraction / sqrt_positive (pf_rng.cuh) against
+    log / sincospi / sqrt on the device, 2^27 normals + edge words"""
+    import os
+    import shutil
+    import subprocess
+
+    if shutil.which("nvcc") is None:
+        pytest.skip("nvcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "box_muller_f64")
+    subprocess.check_call(["nvcc", "-std=c++17", "-O2", "-gencode", "arch=compute_100a,code=sm_100a", "-I", os.path.join(root, "dune-parafields_b200", "csrc"), "-o", exe, os.path.join(root, "tests", "host", "box_muller_f64.cu")])
+    out = subprocess.run([exe], stdout=subprocess.PIPE, text=True, check=True, timeout=300).stdout
+    worst = float(out.split()[-1])
+    # normals reach 6.8: a few ulp of that (the library forms carry 1-2 ulp themselves)
+    assert 0.0 <= worst < 1e-14, out
