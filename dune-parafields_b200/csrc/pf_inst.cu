@@ -106,6 +106,12 @@ extern "C" int PF_CAT(pf_launch_n, PF_N)(int kind, const PassArgs* ap,
                  K::exch_bytes, st);
       break;
     case K_SPEC_TILE:
+#if PF_N >= 256
+      if (a.n_valid == N / 2 && a.keep == N / 2 && a.n_peers <= 1)
+        e = launch(k_spec<N, false, true>, a, tw2, ntA * a.B,
+                   K::smem_tile(a.keep), st);
+      else
+#endif
       e = launch(k_spec<N, false>, a, tw2, ntA * a.B, K::smem_tile(a.keep),
                  st);
       break;

@@ -1110,7 +1110,11 @@ k_lambda(const PassArgs p, const cplx* __restrict__ tw2)
 // -> inverse FFT -> tile store (fieldBackend.mult between forwardTransform
 // and backwardTransform, matrix.hh:1495-1513).  REAL1D: 1D variant, real
 // input line, real output line (DFT field backend, component 0).
-template <int N, bool REAL1D>
+// HALF (tile variant, one rank): n_valid == keep == N / 2 known at compile
+// time -- the zero half of the input folds away in the first butterflies of
+// the forward transform, the dropped half of the output in the last ones of
+// the inverse
+template <int N, bool REAL1D, bool HALF = false>
 __global__ void __launch_bounds__(PF_THREADS, 3)
 k_spec(const PassArgs p, const cplx* __restrict__ tw2)
 {
@@ -1134,7 +1138,13 @@ k_spec(const PassArgs p, const cplx* __restrict__ tw2)
   } else {
     const cplx* line = reinterpret_cast<const cplx*>(p.in) +
                        (long long)a * p.isa + (long long)b * p.isb;
-    load_contig<N>(v, line, t, p.n_valid, valid);
+    if constexpr (HALF) {
+#pragma unroll
+      for (int q = 0; q < K::E; q++)
+        v[q] = (q < K::E / 2 && valid) ? __ldg(line + t + K::TPL * q)
+                                       : make_double2(0., 0.);
+    } else
+      load_contig<N>(v, line, t, p.n_valid, valid);
   }
   line_fft<N, -1>(v, sm + lic * K::C::PITCH, t, tw2);
   if (valid) {
@@ -1167,8 +1177,8 @@ k_spec(const PassArgs p, const cplx* __restrict__ tw2)
                           (long long)b * p.osb + p.a_begin + at * K::LPC, lv, b,
                           p.a_begin + at * K::LPC, 1.0);
     else
-      tile_store<N>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC), p.ose,
-                    lv, 1.0);
+      tile_store<N, HALF>(v, sm, lic, t, p.keep, tile_base(p, b, at * K::LPC),
+                          p.ose, lv, 1.0);
   }
 }
 
