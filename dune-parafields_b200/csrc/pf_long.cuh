@@ -60,7 +60,9 @@ long_sigma(const PassArgs& p, const double* row, long long e, long long n)
 
 // step 1 of decomposition (I); grid = (ceil(N2 / 256), lines)
 template <int N1, int SRC, int DIR>
-__global__ void __launch_bounds__(256)
+// three blocks per SM (85 registers; measured at K4: 2.10 -> 2.02 ms per
+// realization; four blocks spill and lose, 2.19 ms)
+__global__ void __launch_bounds__(256, 3)
 k_long1(const LongArgs g, const PassArgs p)
 {
   constexpr double SQRT2 = 1.41421356237309504880168872420969808;
