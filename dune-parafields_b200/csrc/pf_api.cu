@@ -1158,6 +1158,7 @@ struct pf_plan
   // pass A is dispatch-bound and needs 12 FFT warps per SM; kp_gen remains
   // the slab-mode pass A, where it stores to peer memory)
   bool gen3_force = false; // tests: take kp_gen3 whenever it is applicable
+  bool long_pipe = true;   // PF_LONG_PIPE=0: plain k_long_c2r1
   // bit K_GEN3: grouped persistent pass A (kp_gen3), 12 FFT warps per SM
   unsigned pipe_mask = (1u << pf::K_C2T_INV) | (1u << pf::K_C2T_FWD) |
                        (1u << pf::K_C2R) | (1u << pf::K_GEN3);
@@ -1689,6 +1690,14 @@ run_pass(pf_plan* pl, long long N, int kind, const PassArgs& a)
       tmptr = &c2t;
     }
     grid = (int)std::min<long long>(ntiles, pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count);
+  }
+  // long c2r axis, step 1: persistent pair kernel (pf_pipe.cuh)
+  if (kind == pf::K_LONG_C2R1 && N == 1024 && pl->long_pipe && pipe_launcher_for(N)) {
+    const long long items = (long long)(a.long_n1 / 2 + 1) * a.B;
+    pipe = true;
+    launch_kind = kind;
+    grid = (int)std::min<long long>((items + 5) / 6,
+                                    pl->sm_cap > 0 ? pl->sm_cap : pl->sm_count);
   }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (pl->profiling) {
@@ -3957,6 +3966,8 @@ pf_plan_create(const pf_desc* desc, pf_plan** out)
                          pl->device);
   if (const char* env = getenv("PF_PIPE"))
     pl->pipe_mask = (unsigned)strtoul(env, nullptr, 0);
+  if (const char* env = getenv("PF_LONG_PIPE"))
+    pl->long_pipe = atoi(env) != 0;
   if (const char* env = getenv("PF_GEN3")) // "force": skip the size heuristic
     pl->gen3_force = std::string(env) == "force";
   if (const char* env = getenv("PF_SPLIT")) // SMs for pass A in the one-GPU pipeline

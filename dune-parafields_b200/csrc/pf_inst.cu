@@ -218,6 +218,12 @@ extern "C" int PF_CAT(pf_pipe_launch_n, PF_N)(int kind, const PassArgs* ap,
       e = launch_pipe(kp_c2r<N>, P::THREADS - 32, P::SMEM_LINES, grid, st, a,
                       tw2);
       break;
+#if PF_N == 1024
+    case K_LONG_C2R1:
+      e = launch_pipe(kp_long_c2r1<N>, LC1Cfg<N>::THREADS, LC1Cfg<N>::SMEM, grid, st,
+                      a, tw2);
+      break;
+#endif
     default:
       break;
   }

@@ -700,4 +700,138 @@ kp_c2r(const PassArgs p, const cplx* __restrict__ tw2)
   }
 }
 
+// ===========================================================================
+// long c2r axis, step 1 (k_long_c2r1 of pf_kernels.cuh) as a persistent kernel:
+// the plain kernel leaves its loads exposed (3.2 TB/s at K4, ncu:
+// profiles/r2o).  Here a PAIR of warps takes the two mirror lines k1 and
+// N1 - k1 of one line pair (L0, L1): both are assembled from the same four rows
+// of the permuted half spectra, which arrive by bulk copies into a region that
+// afterwards serves as the two warps' exchange buffers; the next item's rows
+// are requested as soon as both warps hold their second-phase operands.
+// Six pairs (twelve 168-register warps) per SM.
+// ===========================================================================
+template <int N>
+struct LC1Cfg
+{
+  using C = LineCfg<N>;
+  static constexpr int PAIRS = 6;
+  static constexpr int THREADS = PAIRS * 64;
+  static constexpr int M = N / 2 + 1;
+  static constexpr int ROWB = M * 16;
+  static constexpr int XB = C::PITCH * 16;
+  static constexpr int REGION =
+    ((4 * ROWB > 2 * XB ? 4 * ROWB : 2 * XB) + 127) / 128 * 128;
+  static constexpr int SMEM = PAIRS * REGION + 64 + 128;
+  static_assert(C::TPL == 32, "one warp per line");
+};
+
+template <int N>
+__global__ void __launch_bounds__(LC1Cfg<N>::THREADS, 1)
+kp_long_c2r1(const PassArgs p, const cplx* __restrict__ tw2)
+{
+  using L = LC1Cfg<N>;
+  using C = LineCfg<N>;
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* base = reinterpret_cast<unsigned char*>(
+    (reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  const int warp = threadIdx.x >> 5, t = threadIdx.x & 31;
+  const int pair = warp >> 1, w = warp & 1;
+  unsigned char* region = base + pair * L::REGION;
+  cplx* xbuf = reinterpret_cast<cplx*>(region + w * L::XB);
+  const uint32_t bar = smem_u32(base + L::PAIRS * L::REGION) + 8u * pair;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < L::PAIRS; i++)
+      mbar_init(smem_u32(base + L::PAIRS * L::REGION) + 8u * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+  }
+  __syncthreads();
+  const int N1 = p.long_n1;
+  const int per_b = N1 / 2 + 1;                    // items per line pair
+  const long long nitems = (long long)per_b * p.B;
+  const cplx* in = reinterpret_cast<const cplx*>(p.in);
+  auto pair_sync = [&]() {
+    asm volatile("bar.sync %0, %1;" ::"r"(pair + 1), "r"(64) : "memory");
+  };
+  // rows 0, 1: line L0 at k1 and at kr; rows 2, 3: line L1
+  auto issue = [&](long long T) {
+    const long long b = T / per_b;
+    const int k1 = (int)(T % per_b), kr = (N1 - k1) % N1;
+    const long long L0 = 2 * b, L1 = L0 + 1;
+    const bool v1 = L1 < p.n_valid, two = kr != k1;
+    const uint32_t rows = (v1 ? 2u : 1u) * (two ? 2u : 1u);
+    fence_proxy_async();
+    mbar_expect_tx(bar, rows * (uint32_t)L::ROWB);
+    bulk_load(smem_u32(region), in + L0 * p.isa + (long long)k1 * L::M, L::ROWB, bar);
+    if (two)
+      bulk_load(smem_u32(region) + L::ROWB, in + L0 * p.isa + (long long)kr * L::M,
+                L::ROWB, bar);
+    if (v1) {
+      bulk_load(smem_u32(region) + 2 * L::ROWB, in + L1 * p.isa + (long long)k1 * L::M,
+                L::ROWB, bar);
+      if (two)
+        bulk_load(smem_u32(region) + 3 * L::ROWB,
+                  in + L1 * p.isa + (long long)kr * L::M, L::ROWB, bar);
+    }
+  };
+  uint32_t ph = 0;
+  long long T = (long long)blockIdx.x * L::PAIRS + pair;
+  const long long dT = (long long)gridDim.x * L::PAIRS;
+  if (T < nitems && w == 0 && t == 0)
+    issue(T);
+  for (; T < nitems; T += dT) {
+    const long long b = T / per_b;
+    const int k1 = (int)(T % per_b), kr = (N1 - k1) % N1;
+    const bool two = kr != k1;
+    const int k = w == 0 ? k1 : kr;       // this warp's line
+    const bool mine = w == 0 || two;      // self-mirror items have one line
+    const bool v1 = 2 * b + 1 < p.n_valid;
+    // direct rows hold k, mirror rows hold N1 - k
+    const cplx* a_dir = reinterpret_cast<const cplx*>(region + (w == 0 ? 0 : 1) * L::ROWB);
+    const cplx* a_mir =
+      reinterpret_cast<const cplx*>(region + ((w == 0 && two) ? 1 : 0) * L::ROWB);
+    const cplx* b_dir = a_dir + 2 * L::M;
+    const cplx* b_mir = a_mir + 2 * L::M;
+    cplx v[C::E];
+    mbar_wait(bar, ph);
+    ph ^= 1;
+    if (mine) {
+#pragma unroll
+      for (int q = 0; q < C::E; q++) {
+        const int e = t + C::TPL * q;
+        const bool direct = (2 * e < N) || (k == 0 && 2 * e == N);
+        const int col = direct ? e : (k == 0 ? N - e : N - 1 - e);
+        const cplx xa = (direct ? a_dir : a_mir)[col];
+        const cplx xb = v1 ? (direct ? b_dir : b_mir)[col] : make_double2(0., 0.);
+        if (k == 0 && (e == 0 || 2 * e == N))
+          v[q] = make_double2(xa.x, xb.x);
+        else if (direct)
+          v[q] = make_double2(xa.x - xb.y, xa.y + xb.x);
+        else
+          v[q] = make_double2(xa.x + xb.y, xb.x - xa.y);
+      }
+    }
+    pair_sync(); // both warps hold their lines: the rows become exchange space
+    if (mine) {
+      line_fft_phase1<N, +1>(v, xbuf, t);
+      __syncwarp();
+      line_fft_phase2_load<N>(v, xbuf, t);
+    }
+    fence_proxy_async(); // generic accesses of the region before the bulk copies
+    pair_sync();         // the region is free for the next item's rows
+    if (w == 0 && t == 0 && T + dT < nitems)
+      issue(T + dT);
+    if (mine) {
+      line_fft_phase2_compute<N, +1, false>(v, t, tw2);
+      cplx* out = reinterpret_cast<cplx*>(p.out) + (b * N1 + k) * N;
+      const cplx* ltw = p.long_tw + (long long)k * N;
+#pragma unroll
+      for (int q = 0; q < C::E; q++) {
+        const int j2 = t + C::TPL * q;
+        out[j2] = cmulc(v[q], __ldg(ltw + j2));
+      }
+    }
+  }
+}
+
 } // namespace pf
