@@ -25,6 +25,10 @@ CASES = [
     dict(cells=[8192, 4], covariance="spherical", corr_length=0.1),
     dict(cells=[4, 8192], covariance="matern32", corr_length=0.02),
     dict(cells=[4096, 16], **GEO),
+    # a single line (the second line of the c2r pair is absent) and embedding factor 4
+    # (a quarter of the line kept: the kernels without compile-time pruning)
+    dict(cells=[2048, 1], covariance="exponential", corr_length=0.05),
+    dict(cells=[1024, 2], covariance="exponential", corr_length=0.05, factor=4, approximate=True),
 ]
 
 
@@ -76,6 +80,8 @@ OP_CASES = [
     dict(cells=[2048, 1024], covariance="exponential", corr_length=0.05),
     dict(cells=[1024, 1024], **GEO),  # half-spectrum table (geometric anisotropy)
     dict(cells=[8192, 4], covariance="spherical", corr_length=0.1),
+    dict(cells=[4096, 1], covariance="spherical", corr_length=0.1),
+    dict(cells=[1024, 2], covariance="exponential", corr_length=0.05, factor=4, approximate=True),
 ]
 
 
