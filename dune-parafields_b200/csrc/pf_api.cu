@@ -1038,6 +1038,8 @@ struct pf_plan
   bool long2d = false;
   long long LN1[2] = { 1, 1 }, LN2[2] = { 1, 1 };
   long long mcols = 0;            // columns of Z: LN1[0] * (LN2[0]/2 + 1)
+  int ly_batch = 1;               // realizations LY holds (generate_long2d)
+  int long_batch = 1;             // realizations per generate_long2d call (batch API)
   std::map<long long, cplx*> twl; // [a][b] = exp(-2 pi i a b / n) per long line length
   cplx *LY = nullptr, *LU = nullptr; // step buffers of the long passes
   cplx* Y = nullptr;
@@ -1768,7 +1770,7 @@ long_twiddles(pf_plan* pl, long long n, const cplx** out)
   return 0;
 }
 
-template <int SRC, int DIR>
+template <int SRC, int DIR, bool BATCH = false>
 int
 launch_long1(pf_plan* pl, int N1, const pf::LongArgs& g, const PassArgs& p,
              long long lines)
@@ -1776,19 +1778,19 @@ launch_long1(pf_plan* pl, int N1, const pf::LongArgs& g, const PassArgs& p,
   const dim3 grid((unsigned)((g.N2 + 255) / 256), (unsigned)lines);
   switch (N1) {
     case 1:
-      pf::k_long1<1, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      pf::k_long1<1, SRC, DIR, BATCH><<<grid, 256, 0, pl->stream>>>(g, p);
       break;
     case 2:
-      pf::k_long1<2, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      pf::k_long1<2, SRC, DIR, BATCH><<<grid, 256, 0, pl->stream>>>(g, p);
       break;
     case 4:
-      pf::k_long1<4, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      pf::k_long1<4, SRC, DIR, BATCH><<<grid, 256, 0, pl->stream>>>(g, p);
       break;
     case 8:
-      pf::k_long1<8, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      pf::k_long1<8, SRC, DIR, BATCH><<<grid, 256, 0, pl->stream>>>(g, p);
       break;
     case 16:
-      pf::k_long1<16, SRC, DIR><<<grid, 256, 0, pl->stream>>>(g, p);
+      pf::k_long1<16, SRC, DIR, BATCH><<<grid, 256, 0, pl->stream>>>(g, p);
       break;
     default:
       return fail(PF_ERR_INVALID, "long line: unsupported split");
@@ -2497,14 +2499,24 @@ inverse_tail(pf_plan* pl, const cplx* Yin, long long layers, double* out_dev,
 // generateField for a 2D plan with long lines (pf_long.cuh); `a` carries the
 // noise source, keys and sigma table as prepared by generate_dev
 int
-generate_long2d(pf_plan* pl, PassArgs a, double* out_dev, int transform)
+generate_long2d(pf_plan* pl, PassArgs a, double* out_dev, int transform,
+                int batch = 1)
 {
   const long long* n = pl->n;
   const long long* c = pl->c;
   const long long m0 = pl->m0;
   const int N1a = (int)pl->LN1[1], N2a = (int)pl->LN2[1]; // pass A axis (k1)
   const int N1c = (int)pl->LN1[0], N2c = (int)pl->LN2[0]; // c2r axis (k0)
-  PF_TRY(dev_alloc(&pl->LY, (size_t)pl->mcols * n[1]));
+  // `batch` realizations (a.realization + r) share step 1: the sigma table is
+  // read once for all of them (BASELINE config K4 is a batch of realizations);
+  // the later steps run per realization on its Y
+  const size_t ysize = (size_t)pl->mcols * n[1];
+  if (pl->ly_batch < batch) {
+    PF_CUDA(cudaStreamSynchronize(pl->stream));
+    dev_free(&pl->LY);
+    pl->ly_batch = batch;
+  }
+  PF_TRY(dev_alloc(&pl->LY, ysize * (size_t)pl->ly_batch));
   // ---- pass A, step 1: noise * sigma -> DFT over k1 -> twiddle -> Y --------
   a.cma = 1; // counter / injected index of (k0, e): k0 + m0 * e
   a.cmb = 0;
@@ -2525,72 +2537,85 @@ generate_long2d(pf_plan* pl, PassArgs a, double* out_dev, int transform)
   g.perm_m = N2c / 2 + 1;
   g.k0_max = n[0] / 2;
   g.out = pl->LY;
-  if (a.noise_kind == pf::NOISE_PHILOX_FAST)
+  g.batch = batch;
+  g.batch_stride = (long long)ysize;
+  if (batch > 1 && a.noise_kind == pf::NOISE_PHILOX_FAST)
+    PF_TRY((launch_long1<pf::LSRC_NOISE_FAST, +1, true>(pl, N1a, g, a, pl->mcols)));
+  else if (batch > 1 && a.noise_kind == pf::NOISE_PHILOX_F64)
+    PF_TRY((launch_long1<pf::LSRC_NOISE_F64, +1, true>(pl, N1a, g, a, pl->mcols)));
+  else if (batch > 1)
+    return fail(PF_ERR_INVALID, "long lines: batches need device noise");
+  else if (a.noise_kind == pf::NOISE_PHILOX_FAST)
     PF_TRY((launch_long1<pf::LSRC_NOISE_FAST, +1>(pl, N1a, g, a, pl->mcols)));
   else if (a.noise_kind == pf::NOISE_PHILOX_F64)
     PF_TRY((launch_long1<pf::LSRC_NOISE_F64, +1>(pl, N1a, g, a, pl->mcols)));
   else
     PF_TRY((launch_long1<pf::LSRC_NOISE_INJECTED, +1>(pl, N1a, g, a, pl->mcols)));
-  // ---- pass A, step 2: sub-lines (a = column, b = j1) -> Z[x1][column],
-  //      x1 = j1 + N1a * e, restricted to x1 < c1 -----------------------------
-  PassArgs b = blank_args();
-  b.A = (int)pl->mcols;
-  b.B = N1a;
-  b.in = pl->LY;
-  b.isa = n[1];
-  b.isb = N2a;
-  b.n_valid = N2a;
-  b.out = pl->Z;
-  b.osb = pl->m0p;
-  b.ose = (long long)N1a * pl->m0p;
-  b.keep = (int)((c[1] + N1a - 1) / N1a);
-  PF_TRY(run_pass(pl, N2a, pf::K_C2T_INV, b));
-  // ---- pass C ---------------------------------------------------------------
-  if (N1c == 1) {
-    PassArgs cc = blank_args(); // natural column order: the short-line kernel
-    cc.A = (int)c[1];
-    cc.B = 1;
-    cc.in = pl->Z;
-    cc.isa = pl->m0p;
-    cc.out = out_dev;
-    cc.out_pitch = c[0];
-    cc.keep = (int)c[0];
-    cc.transform = transform;
-    cc.tparam = pl->d.boxcox_lambda;
-    return run_pass(pl, n[0], pf::K_C2R, cc);
-  }
-  const long long pairs = (c[1] + 1) / 2;
-  PF_TRY(dev_alloc(&pl->LU, (size_t)pairs * n[0]));
-  PassArgs u = blank_args();
-  u.A = N1c;
-  u.B = (int)pairs;
-  u.in = pl->Z;
-  u.isa = pl->m0p;
-  u.n_valid = (int)c[1];
-  u.out = pl->LU;
-  u.long_n1 = N1c;
-  PF_TRY(long_twiddles(pl, n[0], &u.long_tw));
-  PF_TRY(run_pass(pl, N2c, pf::K_LONG_C2R1, u));
-  const dim3 grid((unsigned)((N2c + 255) / 256), (unsigned)pairs);
-  const double tp = pl->d.boxcox_lambda;
-  switch (N1c) {
-    case 2:
-      pf::k_long_c2r2<2><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
-      break;
-    case 4:
-      pf::k_long_c2r2<4><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
-      break;
-    case 8:
-      pf::k_long_c2r2<8><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
-      break;
-    case 16:
-      pf::k_long_c2r2<16><<<grid, 256, 0, pl->stream>>>(pl->LU, out_dev, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
-      break;
-    default:
-      return fail(PF_ERR_INVALID, "long line: unsupported split");
-  }
-  PF_CUDA(cudaGetLastError());
-  pl->launches++;
+  auto later_steps = [&](const cplx* Yr, double* out_r) -> int {
+    // ---- pass A, step 2: sub-lines (a = column, b = j1) -> Z[x1][column],
+    //      x1 = j1 + N1a * e, restricted to x1 < c1 -----------------------------
+    PassArgs b = blank_args();
+    b.A = (int)pl->mcols;
+    b.B = N1a;
+    b.in = Yr;
+    b.isa = n[1];
+    b.isb = N2a;
+    b.n_valid = N2a;
+    b.out = pl->Z;
+    b.osb = pl->m0p;
+    b.ose = (long long)N1a * pl->m0p;
+    b.keep = (int)((c[1] + N1a - 1) / N1a);
+    PF_TRY(run_pass(pl, N2a, pf::K_C2T_INV, b));
+    // ---- pass C ---------------------------------------------------------------
+    if (N1c == 1) {
+      PassArgs cc = blank_args(); // natural column order: the short-line kernel
+      cc.A = (int)c[1];
+      cc.B = 1;
+      cc.in = pl->Z;
+      cc.isa = pl->m0p;
+      cc.out = out_r;
+      cc.out_pitch = c[0];
+      cc.keep = (int)c[0];
+      cc.transform = transform;
+      cc.tparam = pl->d.boxcox_lambda;
+      return run_pass(pl, n[0], pf::K_C2R, cc);
+    }
+    const long long pairs = (c[1] + 1) / 2;
+    PF_TRY(dev_alloc(&pl->LU, (size_t)pairs * n[0]));
+    PassArgs u = blank_args();
+    u.A = N1c;
+    u.B = (int)pairs;
+    u.in = pl->Z;
+    u.isa = pl->m0p;
+    u.n_valid = (int)c[1];
+    u.out = pl->LU;
+    u.long_n1 = N1c;
+    PF_TRY(long_twiddles(pl, n[0], &u.long_tw));
+    PF_TRY(run_pass(pl, N2c, pf::K_LONG_C2R1, u));
+    const dim3 grid((unsigned)((N2c + 255) / 256), (unsigned)pairs);
+    const double tp = pl->d.boxcox_lambda;
+    switch (N1c) {
+      case 2:
+        pf::k_long_c2r2<2><<<grid, 256, 0, pl->stream>>>(pl->LU, out_r, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+        break;
+      case 4:
+        pf::k_long_c2r2<4><<<grid, 256, 0, pl->stream>>>(pl->LU, out_r, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+        break;
+      case 8:
+        pf::k_long_c2r2<8><<<grid, 256, 0, pl->stream>>>(pl->LU, out_r, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+        break;
+      case 16:
+        pf::k_long_c2r2<16><<<grid, 256, 0, pl->stream>>>(pl->LU, out_r, N2c, c[1], c[0], (int)c[0], 1.0, transform, tp);
+        break;
+      default:
+        return fail(PF_ERR_INVALID, "long line: unsupported split");
+    }
+    PF_CUDA(cudaGetLastError());
+    pl->launches++;
+    return 0;
+  };
+  for (int r = 0; r < batch; r++)
+    PF_TRY(later_steps(pl->LY + (size_t)r * ysize, out_dev + (size_t)r * pl->Dl));
   return 0;
 }
 
@@ -2989,7 +3014,7 @@ generate_dev(pf_plan* pl, int noise_kind, unsigned long long seed,
     if (pl->gen_phase != 1)
       PF_TRY(inverse_tail(pl, Yb, c[2], out_dev, transform));
   } else if (pl->dim == 2 && pl->long2d) {
-    PF_TRY(generate_long2d(pl, a, out_dev, transform));
+    PF_TRY(generate_long2d(pl, a, out_dev, transform, pl->long_batch));
   } else if (pl->dim == 2) {
     a.A = (int)m0; // a = k0, e = k1
     a.B = 1;
@@ -4568,6 +4593,17 @@ pf_generate_batch(pf_plan* pl, uint64_t seed, uint64_t first, size_t count,
   }
   if (dev && pl->dim == 2 && !pl->long2d && !pl->generic && count > 1 && pl->c[1] * (long long)count < 0x7fffffffLL)
     return generate2d_batch(pl, nk, seed, first, count, out, tr);
+  if (dev && pl->dim == 2 && pl->long2d && !pl->generic && nk != pf::NOISE_INJECTED) {
+    // long lines: step 1 of pass A serves up to four realizations from one read
+    // of the sigma table (BASELINE config K4 is a batch of realizations)
+    int rc = 0;
+    for (size_t r = 0; r < count && rc == 0; r += 4) {
+      pl->long_batch = (int)std::min<size_t>(4, count - r);
+      rc = generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->Dl, nullptr, tr);
+    }
+    pl->long_batch = 1;
+    return rc;
+  }
   if (dev) {
     for (size_t r = 0; r < count; r++)
       PF_TRY(generate_dev(pl, nk, seed, first + r, nullptr, out + r * pl->Dl,

@@ -40,6 +40,10 @@ struct LongArgs
   long long in_valid;
   int in_real;
   cplx* out;         // Y[line][j1][k2]
+  // noise sources: `batch` realizations (p.realization + r) from ONE read of the
+  // sigma row, written to out + r * batch_stride (0 / 1: a single realization)
+  int batch;
+  long long batch_stride;
 };
 
 enum
@@ -59,10 +63,11 @@ long_sigma(const PassArgs& p, const double* row, long long e, long long n)
 }
 
 // step 1 of decomposition (I); grid = (ceil(N2 / 256), lines)
-template <int N1, int SRC, int DIR>
 // three blocks per SM (85 registers; measured at K4: 2.10 -> 2.02 ms per
-// realization; four blocks spill and lose, 2.19 ms)
-__global__ void __launch_bounds__(256, 3)
+// realization; four blocks spill and lose, 2.19 ms).  BATCH: g.batch
+// realizations from one read of the sigma row (more registers: two blocks)
+template <int N1, int SRC, int DIR, bool BATCH = false>
+__global__ void __launch_bounds__(256, BATCH ? 2 : 3)
 k_long1(const LongArgs g, const PassArgs p)
 {
   constexpr double SQRT2 = 1.41421356237309504880168872420969808;
@@ -81,16 +86,84 @@ k_long1(const LongArgs g, const PassArgs p)
       return;
     cplx v[N1 > 1 ? N1 : 2];
     if (k0 > g.k0_max) {
-      if constexpr (N1 > 1) {
+      for (int r = 0; r < (g.batch > 1 ? g.batch : 1); r++) {
+        cplx* o = out + (long long)r * g.batch_stride;
+        if constexpr (N1 > 1) {
 #pragma unroll
-        for (int j = 0; j < N1; j++)
-          out[(long long)j * N2 + k2] = make_double2(0., 0.);
-      } else {
-        out[k2] = make_double2(0., 0.);
-        out[k2 + N2 / 2] = make_double2(0., 0.);
+          for (int j = 0; j < N1; j++)
+            o[(long long)j * N2 + k2] = make_double2(0., 0.);
+        } else {
+          o[k2] = make_double2(0., 0.);
+          o[k2 + N2 / 2] = make_double2(0., 0.);
+        }
       }
       return;
     }
+    if constexpr (BATCH) {
+    const double* row = table_row(p, (int)k0, 0);
+    const unsigned long long cbase = (unsigned long long)k0 * p.cma;
+    const long long ibase = k0 * p.ima;
+    double s1[H], s2[H];
+#pragma unroll
+    for (int k1 = 0; k1 < H; k1++) {
+      const long long e = (long long)k1 * N2 + k2; // < n / 2
+      s1[k1] = long_sigma(p, row, e, g.n);
+      s2[k1] = long_sigma(p, row, e + g.n_half, g.n);
+    }
+    const int nbatch = g.batch > 1 ? g.batch : 1;
+    for (int r = 0; r < nbatch; r++) {
+      const unsigned long long rea = p.realization + (unsigned long long)r;
+#pragma unroll
+      for (int k1 = 0; k1 < H; k1++) {
+        const long long e = (long long)k1 * N2 + k2;
+        double2 n1, n2;
+        if constexpr (NOISE == NOISE_INJECTED) {
+          n1 = __ldg(p.noise + ibase + e * p.ime);
+          n2 = __ldg(p.noise + ibase + (e + g.n_half) * p.ime);
+        } else {
+          const unsigned long long ctr = cbase + (unsigned long long)e * p.cme;
+          if constexpr (NOISE == NOISE_PHILOX_FAST) {
+            const uint4 w = philox4x32_r<7>(ctr, rea, p.keys);
+            n1 = box_muller_fast(w.x, w.y);
+            n2 = box_muller_fast(w.z, w.w);
+          } else {
+            const uint4 w = philox4x32_r<10>(ctr, rea, p.keys);
+            n1 = box_muller_f64(w.x, w.y);
+            n2 = box_muller_f64(w.z, w.w);
+          }
+        }
+        v[k1] = make_double2(s1[k1] * n1.x, s1[k1] * n1.y);
+        v[k1 + H] = make_double2(s2[k1] * n2.x, s2[k1] * n2.y);
+      }
+      if (p.hermitian) {
+        // FieldBackend::set, r2cfieldbackend.hh:305-325 (2D: a = k0, e = k1)
+        const bool a_self = (2 * k0) % p.na_self == 0;
+        const bool plane = p.corrected && a_self;
+        if (plane) {
+#pragma unroll
+          for (int j = 0; j < 2 * H; j++)
+            v[j] = make_double2(v[j].x * SQRT2, v[j].y * SQRT2);
+        }
+        if (k2 == 0 && a_self) {
+          const double f = plane ? 1.0 : SQRT2;
+          v[0] = make_double2(v[0].x * f, 0.);
+          v[H] = make_double2(v[H].x * f, 0.);
+        }
+      }
+      cplx* o = out + (long long)r * g.batch_stride;
+      if constexpr (N1 > 1) {
+        Dft<N1, DIR, 1>::run(v);
+#pragma unroll
+        for (int j = 0; j < N1; j++) {
+          const cplx w = __ldg(g.tw + (long long)j * N2 + k2);
+          o[(long long)j * N2 + k2] = DIR < 0 ? cmul(v[j], w) : cmulc(v[j], w);
+        }
+      } else {
+        o[k2] = v[0];
+        o[k2 + N2 / 2] = v[1];
+      }
+    }
+    } else {
     const double* row = table_row(p, (int)k0, 0);
     const unsigned long long cbase = (unsigned long long)k0 * p.cma;
     const long long ibase = k0 * p.ima;
@@ -143,6 +216,7 @@ k_long1(const LongArgs g, const PassArgs p)
     } else {
       out[k2] = v[0];
       out[k2 + N2 / 2] = v[1];
+    }
     }
   } else {
     if (k2 >= N2)

@@ -119,3 +119,24 @@ def test_long_3d_limits(m):
         assert p.extended_size == 2048 * 8 * 8
     with pytest.raises(m.PfError, match="unsupported"):
         m.Plan([4096, 4, 4], covariance="exponential", corr_length=0.05)
+
+
+def test_long_batch_equals_single_calls(m):
+    """pf_generate_batch on long lines: step 1 of pass A takes up to four
+    realizations from one read of the sigma table -- same fields as one call
+    per realization, bit for bit (5 = one full group + a remainder)"""
+    import torch
+
+    for case in (dict(cells=[2048, 64], covariance="exponential", corr_length=0.05),
+                 dict(cells=[64, 1024], covariance="cubic", corr_length=[0.08, 0.03, 0.03, 0.05], anisotropy="geometric", approximate=True, transform="logNormal")):
+        with m.Plan(**case) as p:
+            D = p.domain_size
+            batch = torch.empty((5, D), dtype=torch.float64, device="cuda")
+            one = torch.empty(D, dtype=torch.float64, device="cuda")
+            tr = "transform" in case
+            p.generate_batch(9, 100, 5, out=batch, apply_transform=tr)
+            p.synchronize()
+            for r in range(5):
+                p.generate(9, 100 + r, out=one, apply_transform=tr)
+                p.synchronize()
+                assert torch.equal(batch[r], one), r
