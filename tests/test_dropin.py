@@ -21,6 +21,19 @@ def test_reference_randomfield_with_cuda_matrix():
     assert "FAIL" not in out.stdout
 
 
+BIN_HOST = os.path.join(ROOT, "oracle", "_ref", "dropin_test_host")
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(BIN_HOST), reason="oracle/_ref/dropin_test_host not built (no /root/reference)")
+def test_reference_randomfield_with_the_reference_host_stochastic_part():
+    """the same program with PARAFIELDS_CUDA_HOST_STOCHASTIC: CudaMatrix under the
+    reference's own host StochasticPart (values staged per call)"""
+    out = subprocess.run([BIN_HOST], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout
+    assert "DROP-IN OK" in out.stdout and "FAIL" not in out.stdout
+
+
 @pytest.mark.gpu
 @pytest.mark.skipif(not os.path.exists(BIN), reason="oracle/_ref/dropin_test not built (no /root/reference)")
 def test_operator_chain_keeps_fields_on_the_device():
