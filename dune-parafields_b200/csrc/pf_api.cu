@@ -1810,7 +1810,7 @@ int
 long_fft_forward(pf_plan* pl, int axis, bool from_cov, const cplx* in,
                  long long in_pitch, long long lines, cplx* Y, cplx* out,
                  long long out_pitch, long long keep, int dir = -1,
-                 long long in_valid = 0, int in_real = 0)
+                 long long in_valid = 0, int in_real = 0, long long herm_n = 0)
 {
   const long long n = pl->n[axis];
   const int N1 = (int)pl->LN1[axis], N2 = (int)pl->LN2[axis];
@@ -1823,6 +1823,7 @@ long_fft_forward(pf_plan* pl, int axis, bool from_cov, const cplx* in,
   g.in_pitch = in_pitch;
   g.in_valid = in_valid;
   g.in_real = in_real;
+  g.herm_n = herm_n;
   g.out = Y;
   PassArgs p = blank_args();
   p.cov = pl->cov;
@@ -1859,9 +1860,14 @@ apply_long2d(pf_plan* pl, const double* tab, const double* in_dev, double* out_d
   const long long m0 = pl->m0;
   const long long N1a = pl->LN1[0], N2a = pl->LN2[0]; // axis 0: n0 = N1a * N2a
   const long long N1b = pl->LN1[1], N2b = pl->LN2[1];
+  // the field is real: after the transform along axis 0 only k0 <= n0 / 2 is
+  // kept (sub-line outputs e <= N2a / 2, i.e. w0 >= m0 columns) and carried
+  // through axis 1, the multiplication and back; the last transform rebuilds
+  // the other half as conjugates while it loads (LongArgs::herm_n)
+  const long long h0 = N2a / 2 + 1, w0 = N1a * h0;
   const long long keep0 = (c[0] + N1a - 1) / N1a, p0 = N1a * keep0; // >= c0
   const long long keep1 = (c[1] + N1b - 1) / N1b, p1 = N1b * keep1; // >= c1
-  // scratch kept with the plan (13 GB at K4's size: a PCG would otherwise pay
+  // scratch kept with the plan (7 GB at K4's size: a PCG would otherwise pay
   // the allocations on every product)
   cplx *&Y = pl->LO[0], *&A = pl->LO[1], *&At = pl->LO[2], *&S = pl->LO[3];
   auto transpose = [&](const cplx* in, long long ipitch, cplx* out, long long opitch,
@@ -1872,24 +1878,25 @@ apply_long2d(pf_plan* pl, const double* tab, const double* in_dev, double* out_d
     pl->launches++;
     return cudaGetLastError() == cudaSuccess ? 0 : fail(PF_ERR_CUDA, "transpose");
   };
-  int rc = dev_alloc(&Y, (size_t)n[0] * n[1]);
+  int rc = dev_alloc(&Y, (size_t)std::max(c[1] * n[0], w0 * n[1]));
   if (rc == 0)
-    rc = dev_alloc(&A, (size_t)c[1] * n[0]);
+    rc = dev_alloc(&A, (size_t)c[1] * w0);
   if (rc == 0)
-    rc = dev_alloc(&At, (size_t)n[0] * std::max(c[1], p1));
+    rc = dev_alloc(&At, (size_t)w0 * std::max(c[1], p1));
   if (rc == 0)
-    rc = dev_alloc(&S, (size_t)n[0] * n[1]);
-  // forward: rows x1 < c1 along axis 0 (real input, zero padded beyond c0)
+    rc = dev_alloc(&S, (size_t)std::max(w0 * n[1], c[1] * p0));
+  // forward: rows x1 < c1 along axis 0 (real input, zero padded beyond c0),
+  // half spectrum kept
   if (rc == 0)
     rc = long_fft_forward(pl, 0, false, reinterpret_cast<const cplx*>(in_dev), c[0],
-                          c[1], Y, A, n[0], N2a, -1, c[0], 1);
+                          c[1], Y, A, w0, h0, -1, c[0], 1);
   if (rc == 0)
-    rc = transpose(A, n[0], At, c[1], c[1], n[0]); // At[k0][x1 < c1]
-  // rows k0 along axis 1 (zero padded beyond c1)
+    rc = transpose(A, w0, At, c[1], c[1], w0); // At[k0 < w0][x1 < c1]
+  // rows k0 <= n0 / 2 along axis 1 (zero padded beyond c1)
   if (rc == 0)
-    rc = long_fft_forward(pl, 1, false, At, c[1], n[0], Y, S, n[1], N2b, -1, c[1], 0);
+    rc = long_fft_forward(pl, 1, false, At, c[1], m0, Y, S, n[1], N2b, -1, c[1], 0);
   if (rc == 0) {
-    const long long total = n[0] * n[1];
+    const long long total = m0 * n[1];
     pf::k_long_spec<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(
       S, n[0], n[1], tab, m0, pl->P, pl->compact ? 1 : 0, 1.0 / (double)pl->Next);
     pl->launches++;
@@ -1897,12 +1904,12 @@ apply_long2d(pf_plan* pl, const double* tab, const double* in_dev, double* out_d
   }
   // backward along axis 1, kept x1 < p1 (>= c1)
   if (rc == 0)
-    rc = long_fft_forward(pl, 1, false, S, n[1], n[0], Y, At, p1, keep1, +1);
+    rc = long_fft_forward(pl, 1, false, S, n[1], m0, Y, At, p1, keep1, +1);
   if (rc == 0)
-    rc = transpose(At, p1, A, n[0], n[0], c[1]); // A[x1 < c1][k0]
-  // backward along axis 0, kept x0 < p0; S is free again
+    rc = transpose(At, p1, A, w0, m0, c[1]); // A[x1 < c1][k0 < m0]
+  // backward along axis 0 from the half spectrum, kept x0 < p0
   if (rc == 0)
-    rc = long_fft_forward(pl, 0, false, A, n[0], c[1], Y, S, p0, keep0, +1);
+    rc = long_fft_forward(pl, 0, false, A, w0, c[1], Y, S, p0, keep0, +1, 0, 0, n[0]);
   if (rc == 0) {
     const long long total = c[1] * c[0];
     pf::k_long_real<<<(unsigned)((total + 255) / 256), 256, 0, pl->stream>>>(

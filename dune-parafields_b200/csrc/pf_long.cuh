@@ -39,6 +39,9 @@ struct LongArgs
   long long in_pitch;
   long long in_valid;
   int in_real;
+  // herm_n = n: the line holds the half spectrum x <= n / 2 of a real signal,
+  // entries beyond are conj(in[n - x]) (0: a full complex line)
+  long long herm_n;
   cplx* out;         // Y[line][j1][k2]
   // noise sources: `batch` realizations (p.realization + r) from ONE read of the
   // sigma row, written to out + r * batch_stride (0 / 1: a single realization)
@@ -226,7 +229,10 @@ k_long1(const LongArgs g, const PassArgs p)
     for (int k1 = 0; k1 < N1; k1++) {
       const long long x = (long long)k1 * N2 + k2;
       if constexpr (SRC == LSRC_CPLX) {
-        if (g.in_valid > 0 && x >= g.in_valid)
+        if (g.herm_n > 0 && 2 * x > g.herm_n) {
+          const cplx h = __ldg(g.in + line * g.in_pitch + (g.herm_n - x));
+          v[k1] = make_double2(h.x, -h.y);
+        } else if (g.in_valid > 0 && x >= g.in_valid)
           v[k1] = make_double2(0., 0.);
         else if (g.in_real)
           v[k1] = make_double2(
