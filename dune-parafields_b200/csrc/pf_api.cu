@@ -707,21 +707,7 @@ k_cg_init(double* S)
   S[7] = sqrt(fabs(S[1])) < 1e-6 ? 1. : 0.;
   S[8] = 0.;
 }
-// x += alpha d, Mx += alpha Md with alpha = (z.r) / (d.Md)
-__global__ void
-k_cg_update(size_t n, const double* __restrict__ S, const double* __restrict__ d,
-            const double* __restrict__ Md, double* __restrict__ x,
-            double* __restrict__ Mx)
-{
-  if (S[7] != 0.)
-    return;
-  const double alpha = S[0] / S[3];
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (size_t)gridDim.x * blockDim.x) {
-    x[i] += alpha * d[i];
-    Mx[i] += alpha * Md[i];
-  }
-}
+// x += alpha d, Mx += alpha Md with alpha = (z.r) / (d.Md): k_cg_update_fused
 // d = z + beta d with beta = (1 / old z.r) * new z.r  (the reference's order)
 __global__ void
 k_cg_direction(size_t n, const double* __restrict__ S,
@@ -818,6 +804,47 @@ k_reduce1(size_t n, const double* __restrict__ x, const double* __restrict__ y,
     partial[blockIdx.x] = r;
   }
 }
+// k_cg_update, k_residual and the energy reduction x.(Mx/2 - b) that follows them
+// in ONE sweep (4 of the 22 vector passes of a PCG iteration less): same
+// expressions, same grid and summation order as the separate kernels, so the
+// iterates are bit-identical.  partial[] as in k_reduce1.
+__global__ void
+k_cg_update_fused(size_t n, const double* __restrict__ S,
+                  const double* __restrict__ d, const double* __restrict__ Md,
+                  double* __restrict__ x, double* __restrict__ Mx,
+                  const double* __restrict__ b, double* __restrict__ r,
+                  double* __restrict__ partial)
+{
+  const bool live = S[7] == 0.;
+  const double alpha = live ? S[0] / S[3] : 0.;
+  double acc = 0.;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    double xi = x[i], mi = Mx[i];
+    if (live) {
+      xi += alpha * d[i];
+      mi += alpha * Md[i];
+      x[i] = xi;
+      Mx[i] = mi;
+    }
+    const double bi = b[i];
+    r[i] = bi - mi;
+    acc += xi * (0.5 * mi - bi);
+  }
+  __shared__ double sh[RED_THREADS / 32];
+  for (int o = 16; o > 0; o >>= 1)
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0)
+    sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = sh[0];
+    for (int w = 1; w < RED_THREADS / 32; w++)
+      t += sh[w];
+    partial[blockIdx.x] = t;
+  }
+}
+
 __global__ void
 k_reduce2(int nb, const double* __restrict__ partial, int mode,
           double* __restrict__ result)
@@ -4807,11 +4834,20 @@ pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
       PF_TRY(apply_dev(pl, PF_OP_MATRIX, dir, Md));
       PF_TRY(reduce_to(pl, D, dir, Md, nullptr, 0, S + 3));
       PF_TRY(reduce_to(pl, D, x, Mx, b, 3, S + 4));
-      k_cg_update<<<g, 256, 0, pl->stream>>>(D, S, dir, Md, x, Mx);
-      pl->launches++;
-      PF_TRY(reduce_to(pl, D, x, Mx, b, 3, S + 5));
-      k_residual<<<g, 256, 0, pl->stream>>>(D, b, Mx, r);
-      pl->launches++;
+      { // update, residual and the new energy in one sweep
+        const int nb = (int)std::max<size_t>(
+          1, std::min<size_t>(RED_BLOCKS, (D + RED_THREADS - 1) / RED_THREADS));
+        k_cg_update_fused<<<nb, RED_THREADS, 0, pl->stream>>>(D, S, dir, Md, x, Mx, b, r,
+                                                             pl->red_partial);
+        k_reduce2<<<1, RED_THREADS, 0, pl->stream>>>(nb, pl->red_partial, 3, S + 5);
+        pl->launches += 2;
+        if (pl->nranks > 1) {
+          k_slab_reduce<<<1, 32, 0, pl->stream>>>(
+            pl->d_flagsA, slab_flags(pl, pl->slab_block, 0), pl->nranks, pl->rank,
+            ++pl->red_seq, 3, S + 5, pl->d_timeout, pl->slab_limit_ns);
+          pl->launches++;
+        }
+      }
       PF_TRY(apply_dev(pl, PF_OP_INVERSE_EXT, r, z));
       PF_TRY(reduce_to(pl, D, z, r, nullptr, 0, S + 6));
       k_cg_direction<<<g, 256, 0, pl->stream>>>(D, S, z, dir);
