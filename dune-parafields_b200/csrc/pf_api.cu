@@ -706,6 +706,9 @@ k_cg_init(double* S)
 {
   S[7] = sqrt(fabs(S[1])) < 1e-6 ? 1. : 0.;
   S[8] = 0.;
+  // the energy BEFORE an update is the energy after the previous one (same
+  // vectors, same reduction): carried over instead of being reduced again
+  S[4] = S[2];
 }
 // x += alpha d, Mx += alpha Md with alpha = (z.r) / (d.Md): k_cg_update_fused
 // d = z + beta d with beta = (1 / old z.r) * new z.r  (the reference's order)
@@ -732,6 +735,7 @@ k_cg_scalars(double* S)
   if (value != firstValue)
     if (fabs(value - oldValue) / fabs(value - firstValue) < 1e-16)
       S[7] = 1.;
+  S[4] = value; // "old energy" of the next iteration
   S[8] += 1.;
 }
 
@@ -4833,7 +4837,6 @@ pf_solve(pf_plan* pl, const double* in, double* out, unsigned* iterations)
     while (!converged && enq < maxit) {
       PF_TRY(apply_dev(pl, PF_OP_MATRIX, dir, Md));
       PF_TRY(reduce_to(pl, D, dir, Md, nullptr, 0, S + 3));
-      PF_TRY(reduce_to(pl, D, x, Mx, b, 3, S + 4));
       { // update, residual and the new energy in one sweep
         const int nb = (int)std::max<size_t>(
           1, std::min<size_t>(RED_BLOCKS, (D + RED_THREADS - 1) / RED_THREADS));
