@@ -467,7 +467,7 @@ def other_workloads(torch, pfb, stream, peak):
         if t[12][1] > t[2][1]:
             ms_it = 1e3 * (t[12][0] - t[2][0]) / (t[12][1] - t[2][1])
             D8 = 8 * int(np.prod(wl["cells"]))
-            entry("K5", "one PCG iteration of timesInverseMatrix (2 matvecs + 22 vector passes)", ms_it, 2 * nbytes + 22 * D8, label=WORKLOADS["K5"]["label"])
+            entry("K5", "one PCG iteration of timesInverseMatrix (2 matvecs + 15 vector passes)", ms_it, 2 * nbytes + 15 * D8, label=WORKLOADS["K5"]["label"])
     except Exception as e:
         out.append(dict(workload="K5", error="%s: %s" % (type(e).__name__, e)))
     return out
